@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""bench.py -- pod-node score evals/sec (and reconcile decisions/sec) on 1/2/4/8 B200.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload c3|c4|c5]
+
+One "step" = one whole placement of the workload's synthetic snapshot (every round: filter,
+score, admit) starting from tables already resident in HBM.  Workloads (BASELINE.json configs,
+instantiated as SURVEY.md 8(d)):  c3 = 10k nodes x 100k pods (N=1 default),
+c4 = 100k nodes x 1M pods sharded over the ranks (N>1 default), c2 = 1k pools x 100k VMs
+(reported beside the headline as `reconcile`).  Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NODE_REC_BYTES = 32  # algorithmic bytes per pod-node eval: one packed node record
+WORKLOADS = {
+    "c3": dict(n=10_000, m=100_000, config_id=3, desc="config3: 10k nodes x 100k pods"),
+    "c4": dict(n=100_000, m=1_000_000, config_id=4, desc="config4: 100k nodes x 1M pods"),
+    "c5": dict(n=10_000, m=1_000_000, config_id=5, desc="config5: 10k nodes x 1M pods (sweep top)"),
+    "tiny": dict(n=1_000, m=5_000, config_id=3, desc="tiny: 1k nodes x 5k pods (dev only)"),
+}
+C2 = dict(p=1_000, v=100_000)
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic():
+    """DRAM bytes per scoring-kernel launch from the committed ncu --set full capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "score_kernel_traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    """Samples SM clocks / throttle reasons during the timed region (NVML, else nvidia-smi)."""
+
+    def __init__(self, index=0, period=0.1):
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        self._nvml = None
+
+    def start(self):
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self._nvml = None
+        self._thr = threading.Thread(target=self._run, daemon=True)
+        self._thr.start()
+        return self
+
+    def _run(self):
+        names = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40,
+                 "hw_power_brake_slowdown": 0x80, "sw_power_cap": 0x4}
+        while not self._stop.is_set():
+            try:
+                if self._nvml:
+                    n = self._nvml
+                    self.samples.append(n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM))
+                    r = n.nvmlDeviceGetCurrentClocksEventReasons(self._h) if hasattr(
+                        n, "nvmlDeviceGetCurrentClocksEventReasons") else n.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+                    for k, bit in names.items():
+                        if r & bit:
+                            self.reasons.add(k)
+                else:
+                    out = subprocess.run(
+                        ["nvidia-smi", f"--id={self.index}", "--query-gpu=clocks.sm,clocks.max.sm,"
+                         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap",
+                         "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout.strip()
+                    f = [x.strip() for x in out.split(",")]
+                    self.samples.append(int(f[0]))
+                    self.max_mhz = int(f[1])
+                    for k, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:]):
+                        if v.lower().startswith("active"):
+                            self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def stop(self):
+        self._stop.set()
+        if self._thr:
+            self._thr.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def gen_workload(name):
+    import k8sgpu_b200  # noqa: F401
+    from k8sgpu_b200 import synth
+
+    w = WORKLOADS[name]
+    return synth.gen_nodes(w["n"], w["config_id"]), synth.gen_pods(w["m"], w["config_id"])
+
+
+def cpu_port(nodes, pods, frac, threads):
+    """The CPU oracle (a port: the reference has no runnable code) on the first `frac` of the pods,
+    every round, all host threads.  Returns (evals_per_s, evals, seconds, sample text)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as orc
+
+    m = max(1, int(len(pods["req_gpu"]) * frac))
+    sub = {k: np.ascontiguousarray(v[:m]) for k, v in pods.items()}
+    t0 = time.perf_counter()
+    r = orc.place(nodes, sub, nthreads=threads)
+    dt = time.perf_counter() - t0
+    return r["evals"] / dt, r["evals"], dt, f"all {r['rounds']} rounds of the first {m} pods x {len(nodes['flags'])} nodes"
+
+
+def reference_arm(args, rank, world):
+    """--impl reference: the reference's own CPU implementation of the path.  The reference is
+    Markdown only (no code to run), so this times the oracle port on the host cores."""
+    if rank != 0:
+        return
+    wl = args.workload or ("c3" if args.gpus == 1 else "c4")
+    nodes, pods = gen_workload(wl)
+    threads = os.cpu_count() or 1
+    # size the per-step sample so that steps+warmup end within a few minutes
+    frac = {"c3": 0.10, "c4": 0.0004, "c5": 0.004, "tiny": 1.0}[wl]
+    for _ in range(args.warmup):
+        cpu_port(nodes, pods, frac / 4, threads)
+    ev, secs, sample = 0, 0.0, ""
+    for _ in range(args.steps):
+        _, e, dt, sample = cpu_port(nodes, pods, frac, threads)
+        ev += e
+        secs += dt
+    v = ev / secs
+    line = {
+        "impl": "reference", "metric": "pod_node_score_evals_per_sec", "value": v, "unit": "evals/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
+        "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "u32",
+        "data": "synthetic",
+        "config": {"workload": WORKLOADS[wl]["desc"], "nodes": WORKLOADS[wl]["n"], "pods": WORKLOADS[wl]["m"],
+                   "note": "reference is Markdown only; CPU oracle port timed on host cores"},
+        "cpu_baseline": {"value": v, "unit": "evals/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-reconcile", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank, world)
+        return
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run "
+                         f"--nproc-per-node {args.gpus}")
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU path for --impl ours")
+    import k8sgpu_b200  # noqa: F401
+    from k8sgpu_b200 import capi, placement
+
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    wl = args.workload or ("c3" if world == 1 else "c4")
+    nodes, pods = gen_workload(wl)
+    N, M = len(nodes["flags"]), len(pods["req_gpu"])
+
+    ctx = capi.Context(local_rank)
+    placer = placement.ShardedPlacer(ctx, dist, rank, world)
+    placer.upload(nodes, pods)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        placer.run()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    tot_ms = tot_score_ms = 0.0
+    tot_evals = tot_score_evals = launches = score_launches = 0
+    barrier()
+    wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.zero_()  # evict the tables from L2 between timed steps (untimed)
+        barrier()
+        st = placer.run()
+        ms = st["step_ms"]  # CUDA events on the stream the kernels run on
+        if dist is not None:  # max over ranks, measured on the device
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        tot_ms += ms
+        tot_evals += st["evals"]
+        tot_score_ms += st["score_ms"]
+        tot_score_evals += st["score_evals"]
+        score_launches += st["score_launches"]
+        launches += st["kernel_launches"]
+    barrier()
+    wall = time.perf_counter() - wall0
+    clocks = sampler.stop() if sampler else None
+    rounds = st["rounds"]
+    placed = st["placed"]
+
+    # end to end through the drop-in call: pinned host tables -> H2D -> rounds -> D2H of results
+    e2e = None
+    if world == 1:
+        pin = lambda d: {k: torch.from_numpy(v).pin_memory().numpy() for k, v in d.items()}
+        hn, hp = pin(nodes), pin(pods)
+        ctx.place(hn, hp)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e_evals = 0
+        for _ in range(args.steps):
+            r = ctx.place(hn, hp)
+            e_evals += r["evals"]
+        e_dt = time.perf_counter() - t0
+        e2e = {"value": e_evals / e_dt, "unit": "evals/s", "h2d_bytes_per_step": int(r["h2d_bytes"]),
+               "d2h_bytes_per_step": int(r["d2h_bytes"]), "ms_per_step": 1e3 * e_dt / args.steps}
+        launches_e2e = int(r["kernel_launches"])
+    else:
+        pin = lambda d: {k: torch.from_numpy(v).pin_memory().numpy() for k, v in d.items()}
+        hn, hp = pin(nodes), pin(pods)
+        placer.upload(hn, hp)
+        placer.run()
+        barrier()
+        t0 = time.perf_counter()
+        e_evals = 0
+        for _ in range(args.steps):
+            placer.upload(hn, hp)
+            h2d = ctx.stats()["h2d_bytes"]
+            r = placer.run()
+            placer.download()
+            d2h = ctx.stats()["d2h_bytes"]
+            e_evals += r["evals"]
+        barrier()
+        e_dt = torch.tensor([time.perf_counter() - t0], device="cuda")
+        dist.all_reduce(e_dt, op=dist.ReduceOp.MAX)
+        e_dt = float(e_dt.item())
+        e2e = {"value": e_evals / e_dt, "unit": "evals/s", "h2d_bytes_per_step": int(h2d) * world,
+               "d2h_bytes_per_step": int(d2h) * world, "ms_per_step": 1e3 * e_dt / args.steps,
+               "note": "every rank uploads the replicated tables and downloads the full result"}
+        launches_e2e = None
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = peaks()
+    achieved = tot_score_evals * NODE_REC_BYTES / (tot_score_ms * 1e-3) / 1e9 if tot_score_ms > 0 else 0.0
+    traffic = ncu_traffic()
+    line = {
+        "metric": "pod_node_score_evals_per_sec", "value": tot_evals / (tot_ms * 1e-3), "unit": "evals/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
+        "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
+        "dtype": "u32", "data": "synthetic",
+        "config": {"workload": WORKLOADS[wl]["desc"], "nodes": N, "pods": M, "rounds": rounds, "placed": placed,
+                   "evals_per_step": tot_evals // args.steps, "parallelism": f"pods sharded x{world}, nodes replicated",
+                   "l2": "flushed between timed steps (256 MB write)", "wall_s_timed_region": wall},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic["dram_bytes_per_launch"] if traffic else None, "peak_source": peak_src,
+                     "kernel": "score_kernel", "algorithmic_bytes_per_eval": NODE_REC_BYTES,
+                     "evals_per_launch": tot_score_evals // max(score_launches, 1),
+                     "avg_launch_ms": tot_score_ms / max(score_launches, 1),
+                     "share_of_step": tot_score_ms / tot_ms if tot_ms else None,
+                     "note": "node records are re-read from shared memory/L2, not DRAM: frac > 1 is on-chip reuse "
+                             "(DESIGN.md 'roofline')"},
+        "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+    }
+    if launches_e2e is not None:
+        line["config"]["launches_per_e2e_step"] = launches_e2e
+
+    if not args.no_reconcile and world == 1:
+        from k8sgpu_b200 import synth
+
+        t = synth.gen_reconcile(C2["p"], C2["v"])
+        rargs = (t["desired"], t["pool_owner_id"], t["vm_owner_id"], t["vm_flags"], t["n_owner_ids"], t["vm_ordinal"])
+        ctx.reconcile_upload(*rargs)
+        for _ in range(args.warmup):
+            ctx.reconcile_run()
+        rms = 0.0
+        for _ in range(args.steps):
+            flush.zero_()
+            torch.cuda.synchronize()
+            rms += ctx.reconcile_run()["device_ms"]
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            ctx.reconcile_batch(*rargs)
+        rdt = time.perf_counter() - t0
+        alg = 12 * C2["v"] + 16 * C2["p"]
+        line["reconcile"] = {
+            "workload": f"config2: {C2['p']} pools x {C2['v']} VMs", "decisions_per_s": C2["p"] * args.steps / (rms * 1e-3),
+            "vm_rows_per_s": C2["v"] * args.steps / (rms * 1e-3), "ms_per_step": rms / args.steps,
+            "e2e_decisions_per_s": C2["p"] * args.steps / rdt, "algorithmic_bytes": alg,
+            "achieved_gbs": alg * args.steps / (rms * 1e-3) / 1e9,
+        }
+
+    if not args.no_cpu_baseline and world == 1:
+        threads = os.cpu_count() or 1
+        frac = {"c3": 0.25, "c4": 0.001, "c5": 0.01, "tiny": 1.0}[wl]
+        v, ev, dt, sample = cpu_port(nodes, pods, frac, threads)
+        line["cpu_baseline"] = {"value": v, "unit": "evals/s", "cores": threads, "kind": "port", "sample": sample,
+                                "seconds": dt}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,191 @@
+/*
+ * k8sgpu.h -- C-ABI of libk8sgpu.so: the batch form of the AzureVmPool operator's decision
+ * logic and GPU pod->node placement, computed on one B200 (sm_100a) per process.
+ *
+ * This is the boundary a cgo shim binds (INTEGRATION.md shows it).  Plain C types, caller-
+ * owned host buffers, no callbacks, no thread-local state; every entry point selects its CUDA
+ * device itself, so it may be called from any OS thread (goroutines migrate between threads).
+ * A context is NOT re-entrant: one call at a time per context.  There is NO CPU fallback: if
+ * no CUDA device can be opened every call fails with K8SGPU_E_CUDA.
+ *
+ * Citations are file:line under the reference tree (Andy-ckm/K8S-GPU-).  The reference has no
+ * FFI of its own (it is Go text inside Markdown); each entry point names the reference
+ * statements it replaces.
+ */
+#ifndef K8SGPU_H
+#define K8SGPU_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define K8SGPU_ABI_VERSION 1
+
+/* error codes: every export returns 0 or one of these; text via k8sgpu_last_error */
+#define K8SGPU_OK 0
+#define K8SGPU_E_ARG (-1)      /* NULL pointer, table outside the input domain, duplicate owner id */
+#define K8SGPU_E_CUDA (-2)     /* CUDA runtime error or no device */
+#define K8SGPU_E_NCCL (-3)     /* reserved: collective layer */
+#define K8SGPU_E_CAPACITY (-4) /* a caller-sized output buffer is too small */
+
+#define K8SGPU_NONE_U32 0xFFFFFFFFu
+#define K8SGPU_ASSIGN_NONE (-1)    /* pod has no feasible node                       */
+#define K8SGPU_ASSIGN_PENDING (-2) /* pod still proposing when max_rounds was reached */
+#define K8SGPU_POLICY_ROT_ZERO 1u  /* rot(p) = 0: plain lowest-index tie-break        */
+
+typedef struct k8sgpu_ctx k8sgpu_ctx;
+
+/* ------------------------------------------------------------------ tables (SoA, host) */
+
+/* One row per AzureVmPool.  desired = Spec.Replicas (README.md:93-95,196).  owner_id = the
+ * interned id of the pool's owner tag value "<namespace>-<name>" (README.md:238). */
+typedef struct {
+    uint32_t p;
+    const int32_t *desired;
+    const uint32_t *owner_id;
+} k8sgpu_pool_table;
+
+/* One row per VM observed in the resource group, in list order (README.md:189,214).
+ * owner_id: interned value of the VM's `owner` tag, K8SGPU_NONE_U32 if absent.
+ * flags bit0: tag managed-by == "azurevmpool-operator" (README.md:238).
+ * ordinal: k when the VM is named "<pool-name>-<k>", else K8SGPU_NONE_U32; may be NULL. */
+typedef struct {
+    uint32_t v;
+    const uint32_t *owner_id;
+    const uint32_t *flags;
+    const uint32_t *ordinal;
+} k8sgpu_vm_table;
+
+/* Caller-sized outputs.  Capacities: pool_of V; current/delta/ready/create_count P;
+ * *_off P+1; victim_vm and member_vm V; create_ordinal create_capacity.
+ * member_*, create_off/create_ordinal may be NULL (then they are not produced). */
+typedef struct {
+    int32_t *pool_of;         /* listManagedVMs tag filter, README.md:188-189,238              */
+    int32_t *current;         /* currentCount := len(existingVMs), README.md:195               */
+    int32_t *delta;           /* desired - current, README.md:199-201,210-212                  */
+    int32_t *ready;           /* Status.ReadyReplicas = currentCount (pre-action), :225        */
+    int32_t *create_count;    /* scaleUpCount, README.md:201                                   */
+    int32_t *victim_off;      /* CSR over pools                                                */
+    uint32_t *victim_vm;      /* existingVMs[:scaleDownCount] as VM rows, README.md:214        */
+    int32_t *member_off;      /* CSR of existingVMs per pool (Status.VMs, README.md:124-125)   */
+    uint32_t *member_vm;
+    int32_t *create_off;      /* CSR of the ordinals createVM would pick, README.md:204-205    */
+    uint32_t *create_ordinal;
+    uint64_t create_capacity; /* elements available in create_ordinal                          */
+} k8sgpu_reconcile_out;
+
+/* Node and pod records: 8 u32 columns each (DESIGN.md "tables").  The reference holds no
+ * scheduler source; the pod shape comes from GPU调度平台搭建.md:665-667 (nvidia.com/gpu: 1)
+ * and :534 (gpu-1x-16c-32g-1gpu), the node attributes from README.md:99-100 (location, vmSize).
+ * Input domain (else K8SGPU_E_ARG): free_gpu <= 0x7FFF, cap_gpu <= 255, sku_id < 32,
+ * zone_id < 32, every free_* and req_* < 2^31, pref_zone < 32 or K8SGPU_NONE_U32,
+ * n < 2^31 - 4096, m < 2^31. */
+typedef struct {
+    uint32_t n;
+    const uint32_t *free_gpu, *free_mcpu, *free_mib, *cap_gpu, *sku_id, *zone_id, *taint_mask, *flags;
+} k8sgpu_node_table;
+
+typedef struct {
+    uint32_t m;
+    const uint32_t *req_gpu, *req_mcpu, *req_mib, *sku_mask, *zone_mask, *tol_mask, *pref_zone, *priority;
+} k8sgpu_pod_table;
+
+typedef struct {
+    uint32_t flags;      /* K8SGPU_POLICY_* */
+    uint32_t max_rounds; /* 0 = run until no pod is active */
+} k8sgpu_policy;
+
+typedef struct {
+    int32_t *assign;     /* [m] node row, K8SGPU_ASSIGN_NONE or K8SGPU_ASSIGN_PENDING */
+    uint32_t *free_gpu;  /* [n] free columns after placement; each may be NULL */
+    uint32_t *free_mcpu;
+    uint32_t *free_mib;
+} k8sgpu_place_out;
+
+typedef struct {
+    uint32_t rounds;          /* placement rounds of the last place call                         */
+    uint32_t placed;          /* pods with assign >= 0                                           */
+    uint64_t evals;           /* sum over rounds of active pods x nodes                          */
+    uint64_t kernel_launches; /* kernels this library launched in the last call                  */
+    uint64_t h2d_bytes;       /* bytes copied host->device / device->host in the last call       */
+    uint64_t d2h_bytes;
+    float device_ms;          /* CUDA-event time of the device portion (no H2D/D2H) of last call */
+    float score_ms;           /* CUDA-event time spent in the scoring kernel (sum over rounds)   */
+    uint64_t score_evals;     /* evals covered by score_ms                                       */
+    uint32_t score_launches;  /* scoring-kernel launches covered by score_ms                     */
+    uint32_t reserved;
+} k8sgpu_stats;
+
+/* ------------------------------------------------------------------ context */
+
+/* Opens devices[0] (ndev must be 1: one process per GPU; several processes cooperate through
+ * the k8sgpu_place_round_* entry points below).  Replaces nothing in the reference; it is
+ * what SetupWithManager would call once. */
+int k8sgpu_create(const int *devices, int ndev, k8sgpu_ctx **out);
+int k8sgpu_destroy(k8sgpu_ctx *ctx);
+/* Message of the last failing call on ctx (ctx may be NULL: creation errors). */
+const char *k8sgpu_last_error(const k8sgpu_ctx *ctx);
+int k8sgpu_get_stats(const k8sgpu_ctx *ctx, k8sgpu_stats *out);
+int k8sgpu_abi_version(void);
+
+/* ------------------------------------------------------------------ batch reconcile */
+
+/* Steps 3 and 4 of Reconcile for every pool at once (README.md:187-222): tag-filtered list,
+ * currentCount, the desired-vs-actual diff, the scale-down victim slice and the scale-up
+ * count, plus the status fields of step 5 (README.md:225).  n_owner_ids bounds the interned
+ * owner ids (ids >= n_owner_ids are foreign).  Host buffers in, host buffers out. */
+int k8sgpu_reconcile_batch(k8sgpu_ctx *ctx, const k8sgpu_pool_table *pools, const k8sgpu_vm_table *vms,
+                           uint32_t n_owner_ids, k8sgpu_reconcile_out *out);
+
+/* The same split in three: tables stay resident in HBM between calls (bench `value`). */
+int k8sgpu_reconcile_upload(k8sgpu_ctx *ctx, const k8sgpu_pool_table *pools, const k8sgpu_vm_table *vms,
+                            uint32_t n_owner_ids);
+int k8sgpu_reconcile_run(k8sgpu_ctx *ctx, int want_members, int want_ordinals);
+int k8sgpu_reconcile_download(k8sgpu_ctx *ctx, k8sgpu_reconcile_out *out);
+
+/* ------------------------------------------------------------------ placement */
+
+/* Filter / score / bin-pack of every pending pod onto the node table, round based
+ * (DESIGN.md policy v0).  Stands where the reference hands pods to a third-party scheduler
+ * (schedulerName: volcano, GPU调度平台搭建.md:649; helm installs :275-298). */
+int k8sgpu_place(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods,
+                 const k8sgpu_policy *policy, k8sgpu_place_out *out);
+
+/* Resident form: upload once, run any number of times (each run restarts from the uploaded
+ * tables), download results. */
+int k8sgpu_place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods);
+int k8sgpu_place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy);
+int k8sgpu_place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out);
+
+/* One scoring pass of all pods against the uploaded node table (no admission):
+ * best_node[m] = argmax node per pod, -1 if none.  Host buffer out. */
+int k8sgpu_score_once(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, int32_t *best_node);
+
+/* Round-at-a-time form for several cooperating processes (one per GPU): every process
+ * uploads the same tables, scores its own slice [lo,hi) of the active list into a DEVICE
+ * buffer, the caller exchanges the slices (all-gather), and every process then runs the
+ * admission step on the full proposal list, which keeps all replicas identical.
+ * `stream` is a cudaStream_t (0 = the context's own stream).
+ *   begin : reset state from the uploaded tables; *n_active = m
+ *   score : d_best[i - lo] = best node of active[i], lo <= i < hi        (asynchronous)
+ *   admit : d_best_all[i] for 0 <= i < n_active; returns the next active count (synchronises)
+ *   end   : fills rounds / placed / evals of k8sgpu_get_stats */
+int k8sgpu_place_round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, void *stream, uint32_t *n_active);
+int k8sgpu_place_round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, void *stream);
+int k8sgpu_place_round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, void *stream, uint32_t *n_active);
+int k8sgpu_place_round_end(k8sgpu_ctx *ctx, void *stream);
+
+/* ------------------------------------------------------------------ primitives (tests) */
+
+/* Stable LSD radix sort of (key,val) pairs on `bits` low key bits, and an exclusive u32
+ * prefix sum: the two device primitives victim order and admission order are built on.
+ * Host buffers in and out.  No reference counterpart. */
+int k8sgpu_debug_sort_pairs(k8sgpu_ctx *ctx, const uint32_t *keys, const uint32_t *vals, uint32_t n, int bits,
+                            uint32_t *out_keys, uint32_t *out_vals);
+int k8sgpu_debug_exclusive_scan(k8sgpu_ctx *ctx, const uint32_t *in, uint32_t n, uint32_t *out, uint32_t *total);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

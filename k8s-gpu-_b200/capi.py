@@ -1,0 +1,324 @@
+"""ctypes binding of libk8sgpu.so (include/k8sgpu.h).  Every call goes to the CUDA library;
+there is no Python or CPU fallback: a missing library or a missing GPU raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libk8sgpu.so")
+
+OK, E_ARG, E_CUDA, E_NCCL, E_CAPACITY = 0, -1, -2, -3, -4
+NONE_U32 = 0xFFFFFFFF
+ASSIGN_NONE, ASSIGN_PENDING = -1, -2
+POLICY_ROT_ZERO = 1
+
+NODE_COLS = ("free_gpu", "free_mcpu", "free_mib", "cap_gpu", "sku_id", "zone_id", "taint_mask", "flags")
+POD_COLS = ("req_gpu", "req_mcpu", "req_mib", "sku_mask", "zone_mask", "tol_mask", "pref_zone", "priority")
+
+# every symbol include/k8sgpu.h declares (tests check the library exports all of them)
+EXPORTS = (
+    "k8sgpu_abi_version", "k8sgpu_create", "k8sgpu_destroy", "k8sgpu_last_error", "k8sgpu_get_stats",
+    "k8sgpu_reconcile_batch", "k8sgpu_reconcile_upload", "k8sgpu_reconcile_run", "k8sgpu_reconcile_download",
+    "k8sgpu_place", "k8sgpu_place_upload", "k8sgpu_place_run", "k8sgpu_place_download", "k8sgpu_score_once",
+    "k8sgpu_place_round_begin", "k8sgpu_place_round_score", "k8sgpu_place_round_admit", "k8sgpu_place_round_end",
+    "k8sgpu_debug_sort_pairs", "k8sgpu_debug_exclusive_scan",
+)
+
+u32p = C.POINTER(C.c_uint32)
+i32p = C.POINTER(C.c_int32)
+
+
+class PoolTable(C.Structure):
+    _fields_ = [("p", C.c_uint32), ("desired", i32p), ("owner_id", u32p)]
+
+
+class VmTable(C.Structure):
+    _fields_ = [("v", C.c_uint32), ("owner_id", u32p), ("flags", u32p), ("ordinal", u32p)]
+
+
+class ReconcileOut(C.Structure):
+    _fields_ = [("pool_of", i32p), ("current", i32p), ("delta", i32p), ("ready", i32p), ("create_count", i32p),
+                ("victim_off", i32p), ("victim_vm", u32p), ("member_off", i32p), ("member_vm", u32p),
+                ("create_off", i32p), ("create_ordinal", u32p), ("create_capacity", C.c_uint64)]
+
+
+class NodeTable(C.Structure):
+    _fields_ = [("n", C.c_uint32)] + [(c, u32p) for c in NODE_COLS]
+
+
+class PodTable(C.Structure):
+    _fields_ = [("m", C.c_uint32)] + [(c, u32p) for c in POD_COLS]
+
+
+class Policy(C.Structure):
+    _fields_ = [("flags", C.c_uint32), ("max_rounds", C.c_uint32)]
+
+
+class PlaceOut(C.Structure):
+    _fields_ = [("assign", i32p), ("free_gpu", u32p), ("free_mcpu", u32p), ("free_mib", u32p)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("rounds", C.c_uint32), ("placed", C.c_uint32), ("evals", C.c_uint64),
+                ("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+                ("device_ms", C.c_float), ("score_ms", C.c_float), ("score_evals", C.c_uint64),
+                ("score_launches", C.c_uint32), ("reserved", C.c_uint32)]
+
+    def as_dict(self):
+        return {f: getattr(self, f) for f, _ in self._fields_ if f != "reserved"}
+
+
+class K8sGpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"k8sgpu error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """dlopen libk8sgpu.so (built in-tree by __graft_entry__.build / csrc/Makefile)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(there is no fallback path)")
+        L = C.CDLL(LIB_PATH)
+        vp = C.c_void_p
+        L.k8sgpu_abi_version.restype = C.c_int
+        L.k8sgpu_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
+        L.k8sgpu_destroy.argtypes = [vp]
+        L.k8sgpu_last_error.argtypes = [vp]
+        L.k8sgpu_last_error.restype = C.c_char_p
+        L.k8sgpu_get_stats.argtypes = [vp, C.POINTER(Stats)]
+        L.k8sgpu_reconcile_batch.argtypes = [vp, C.POINTER(PoolTable), C.POINTER(VmTable), C.c_uint32,
+                                             C.POINTER(ReconcileOut)]
+        L.k8sgpu_reconcile_upload.argtypes = [vp, C.POINTER(PoolTable), C.POINTER(VmTable), C.c_uint32]
+        L.k8sgpu_reconcile_run.argtypes = [vp, C.c_int, C.c_int]
+        L.k8sgpu_reconcile_download.argtypes = [vp, C.POINTER(ReconcileOut)]
+        L.k8sgpu_place.argtypes = [vp, C.POINTER(NodeTable), C.POINTER(PodTable), C.POINTER(Policy),
+                                   C.POINTER(PlaceOut)]
+        L.k8sgpu_place_upload.argtypes = [vp, C.POINTER(NodeTable), C.POINTER(PodTable)]
+        L.k8sgpu_place_run.argtypes = [vp, C.POINTER(Policy)]
+        L.k8sgpu_place_download.argtypes = [vp, C.POINTER(PlaceOut)]
+        L.k8sgpu_score_once.argtypes = [vp, C.POINTER(Policy), i32p]
+        L.k8sgpu_place_round_begin.argtypes = [vp, C.POINTER(Policy), vp, u32p]
+        L.k8sgpu_place_round_score.argtypes = [vp, C.c_uint32, C.c_uint32, vp, vp]
+        L.k8sgpu_place_round_admit.argtypes = [vp, vp, vp, u32p]
+        L.k8sgpu_place_round_end.argtypes = [vp, vp]
+        L.k8sgpu_debug_sort_pairs.argtypes = [vp, u32p, u32p, C.c_uint32, C.c_int, u32p, u32p]
+        L.k8sgpu_debug_exclusive_scan.argtypes = [vp, u32p, C.c_uint32, u32p, u32p]
+        for name in EXPORTS:
+            if name != "k8sgpu_last_error":
+                getattr(L, name).restype = C.c_int
+        _lib = L
+    return _lib
+
+
+def _u32(a):
+    a = np.ascontiguousarray(a, dtype=np.uint32)
+    return a, a.ctypes.data_as(u32p)
+
+
+def _i32(a):
+    a = np.ascontiguousarray(a, dtype=np.int32)
+    return a, a.ctypes.data_as(i32p)
+
+
+def node_table(nodes: dict):
+    t, keep = NodeTable(), []
+    t.n = len(nodes[NODE_COLS[0]])
+    for c in NODE_COLS:
+        a, p = _u32(nodes[c])
+        keep.append(a)
+        setattr(t, c, p)
+    return t, keep
+
+
+def pod_table(pods: dict):
+    t, keep = PodTable(), []
+    t.m = len(pods[POD_COLS[0]])
+    for c in POD_COLS:
+        a, p = _u32(pods[c])
+        keep.append(a)
+        setattr(t, c, p)
+    return t, keep
+
+
+class Context:
+    """One k8sgpu_ctx on one GPU.  Not re-entrant: one call at a time."""
+
+    def __init__(self, device: int = 0):
+        self._L = load()
+        self._h = C.c_void_p()
+        dev = (C.c_int * 1)(device)
+        rc = self._L.k8sgpu_create(dev, 1, C.byref(self._h))
+        if rc != OK:
+            raise K8sGpuError(rc, self._L.k8sgpu_last_error(None).decode())
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.k8sgpu_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc):
+        if rc != OK:
+            raise K8sGpuError(rc, self._L.k8sgpu_last_error(self._h).decode())
+
+    def stats(self) -> dict:
+        s = Stats()
+        self._check(self._L.k8sgpu_get_stats(self._h, C.byref(s)))
+        return s.as_dict()
+
+    # ------------------------------------------------------------ placement
+    def place(self, nodes: dict, pods: dict, flags: int = 0, max_rounds: int = 0) -> dict:
+        """Host tables in, host results out (the drop-in call)."""
+        nt, k1 = node_table(nodes)
+        pt, k2 = pod_table(pods)
+        out, res = self._place_out(nt.n, pt.m)
+        pol = Policy(flags, max_rounds)
+        self._check(self._L.k8sgpu_place(self._h, C.byref(nt), C.byref(pt), C.byref(pol), C.byref(out)))
+        res.update(self.stats())
+        return res
+
+    def _place_out(self, n, m):
+        res = {"assign": np.empty(m, np.int32), "free_gpu": np.empty(n, np.uint32),
+               "free_mcpu": np.empty(n, np.uint32), "free_mib": np.empty(n, np.uint32)}
+        out = PlaceOut(res["assign"].ctypes.data_as(i32p), res["free_gpu"].ctypes.data_as(u32p),
+                       res["free_mcpu"].ctypes.data_as(u32p), res["free_mib"].ctypes.data_as(u32p))
+        return out, res
+
+    def place_upload(self, nodes: dict, pods: dict):
+        nt, k1 = node_table(nodes)
+        pt, k2 = pod_table(pods)
+        self._n, self._m = nt.n, pt.m
+        self._check(self._L.k8sgpu_place_upload(self._h, C.byref(nt), C.byref(pt)))
+
+    def place_run(self, flags: int = 0, max_rounds: int = 0) -> dict:
+        pol = Policy(flags, max_rounds)
+        self._check(self._L.k8sgpu_place_run(self._h, C.byref(pol)))
+        return self.stats()
+
+    def place_download(self) -> dict:
+        out, res = self._place_out(self._n, self._m)
+        self._check(self._L.k8sgpu_place_download(self._h, C.byref(out)))
+        return res
+
+    def score_once(self, flags: int = 0) -> np.ndarray:
+        best = np.empty(self._m, np.int32)
+        pol = Policy(flags, 0)
+        self._check(self._L.k8sgpu_score_once(self._h, C.byref(pol), best.ctypes.data_as(i32p)))
+        return best
+
+    # round-at-a-time form (device pointers; see placement.ShardedPlacer)
+    def round_begin(self, flags: int = 0, max_rounds: int = 0, stream: int = 0) -> int:
+        pol = Policy(flags, max_rounds)
+        na = C.c_uint32()
+        self._check(self._L.k8sgpu_place_round_begin(self._h, C.byref(pol), C.c_void_p(stream), C.byref(na)))
+        return na.value
+
+    def round_score(self, lo: int, hi: int, d_best_ptr: int, stream: int = 0):
+        self._check(self._L.k8sgpu_place_round_score(self._h, lo, hi, C.c_void_p(d_best_ptr), C.c_void_p(stream)))
+
+    def round_admit(self, d_best_all_ptr: int, stream: int = 0) -> int:
+        na = C.c_uint32()
+        self._check(self._L.k8sgpu_place_round_admit(self._h, C.c_void_p(d_best_all_ptr), C.c_void_p(stream),
+                                                     C.byref(na)))
+        return na.value
+
+    def round_end(self, stream: int = 0) -> dict:
+        self._check(self._L.k8sgpu_place_round_end(self._h, C.c_void_p(stream)))
+        return self.stats()
+
+    # ------------------------------------------------------------ reconcile
+    @staticmethod
+    def _rec_tables(desired, pool_owner_id, vm_owner_id, vm_flags, vm_ordinal):
+        d, dp = _i32(desired)
+        po, pop = _u32(pool_owner_id)
+        vo, vop = _u32(vm_owner_id)
+        vf, vfp = _u32(vm_flags)
+        if vm_ordinal is not None:
+            vr, vrp = _u32(vm_ordinal)
+        else:
+            vr, vrp = None, u32p()
+        return PoolTable(len(d), dp, pop), VmTable(len(vo), vop, vfp, vrp), (d, po, vo, vf, vr)
+
+    @staticmethod
+    def _rec_out(P, V, create_cap, members=True, ordinals=True):
+        o = {"pool_of": np.empty(V, np.int32), "current": np.empty(P, np.int32), "delta": np.empty(P, np.int32),
+             "ready": np.empty(P, np.int32), "create_count": np.empty(P, np.int32),
+             "victim_off": np.zeros(P + 1, np.int32), "victim_vm": np.zeros(V + 1, np.uint32)}
+        if members:
+            o["member_off"] = np.zeros(P + 1, np.int32)
+            o["member_vm"] = np.zeros(V + 1, np.uint32)
+        if ordinals:
+            o["create_off"] = np.zeros(P + 1, np.int32)
+            o["create_ordinal"] = np.zeros(create_cap + 1, np.uint32)
+        out = ReconcileOut()
+        for k, v in o.items():
+            setattr(out, k, v.ctypes.data_as(i32p if v.dtype == np.int32 else u32p))
+        out.create_capacity = create_cap + 1 if ordinals else 0
+        return out, o
+
+    @staticmethod
+    def _rec_trim(o, P):
+        o["victim_vm"] = o["victim_vm"][: o["victim_off"][P]].copy()
+        if "member_vm" in o:
+            o["member_vm"] = o["member_vm"][: o["member_off"][P]].copy()
+        if "create_ordinal" in o:
+            o["create_ordinal"] = o["create_ordinal"][: o["create_off"][P]].copy()
+        return o
+
+    def reconcile_batch(self, desired, pool_owner_id, vm_owner_id, vm_flags, n_owner_ids, vm_ordinal=None,
+                        members=True, ordinals=True, create_capacity=None) -> dict:
+        pools, vms, keep = self._rec_tables(desired, pool_owner_id, vm_owner_id, vm_flags, vm_ordinal)
+        cap = int(np.maximum(keep[0].astype(np.int64), 0).sum()) if create_capacity is None else create_capacity
+        out, o = self._rec_out(pools.p, vms.v, cap, members, ordinals)
+        self._check(self._L.k8sgpu_reconcile_batch(self._h, C.byref(pools), C.byref(vms), n_owner_ids, C.byref(out)))
+        o = self._rec_trim(o, pools.p)
+        o.update(self.stats())
+        return o
+
+    def reconcile_upload(self, desired, pool_owner_id, vm_owner_id, vm_flags, n_owner_ids, vm_ordinal=None):
+        pools, vms, keep = self._rec_tables(desired, pool_owner_id, vm_owner_id, vm_flags, vm_ordinal)
+        self._rp, self._rv = pools.p, vms.v
+        self._rcap = int(np.maximum(keep[0].astype(np.int64), 0).sum())
+        self._check(self._L.k8sgpu_reconcile_upload(self._h, C.byref(pools), C.byref(vms), n_owner_ids))
+
+    def reconcile_run(self, members=True, ordinals=True) -> dict:
+        self._check(self._L.k8sgpu_reconcile_run(self._h, int(members), int(ordinals)))
+        return self.stats()
+
+    def reconcile_download(self, members=True, ordinals=True) -> dict:
+        out, o = self._rec_out(self._rp, self._rv, self._rcap, members, ordinals)
+        self._check(self._L.k8sgpu_reconcile_download(self._h, C.byref(out)))
+        return self._rec_trim(o, self._rp)
+
+    # ------------------------------------------------------------ primitives
+    def sort_pairs(self, keys, vals, bits: int):
+        k, kp = _u32(keys)
+        v, vp_ = _u32(vals)
+        ok, ov = np.empty_like(k), np.empty_like(v)
+        self._check(self._L.k8sgpu_debug_sort_pairs(self._h, kp, vp_, len(k), bits, ok.ctypes.data_as(u32p),
+                                                    ov.ctypes.data_as(u32p)))
+        return ok, ov
+
+    def exclusive_scan(self, a):
+        x, xp = _u32(a)
+        out = np.empty_like(x)
+        tot = C.c_uint32()
+        self._check(self._L.k8sgpu_debug_exclusive_scan(self._h, xp, len(x), out.ctypes.data_as(u32p), C.byref(tot)))
+        return out, tot.value

@@ -1,0 +1,150 @@
+// capi.cu -- context lifetime, errors, statistics and the primitive test hooks of libk8sgpu.so.
+#include <new>
+
+#include "common.cuh"
+
+using namespace k8sgpu;
+
+static char g_create_err[512] = "";
+
+extern "C" int k8sgpu_abi_version(void) { return K8SGPU_ABI_VERSION; }
+
+extern "C" const char *k8sgpu_last_error(const k8sgpu_ctx *ctx) { return ctx ? ctx->err : g_create_err; }
+
+extern "C" int k8sgpu_create(const int *devices, int ndev, k8sgpu_ctx **out) {
+    if (!out) return K8SGPU_E_ARG;
+    *out = nullptr;
+    if (ndev != 1 || !devices) {
+        snprintf(g_create_err, sizeof g_create_err,
+                 "k8sgpu_create: ndev must be 1 (one process per GPU; see k8sgpu_place_round_*)");
+        return K8SGPU_E_ARG;
+    }
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0) {  // no CPU fallback: this is an error, not a mode
+        snprintf(g_create_err, sizeof g_create_err, "k8sgpu_create: no CUDA device (%s)",
+                 e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+        return K8SGPU_E_CUDA;
+    }
+    if (devices[0] < 0 || devices[0] >= count) {
+        snprintf(g_create_err, sizeof g_create_err, "k8sgpu_create: device %d out of range [0,%d)", devices[0], count);
+        return K8SGPU_E_ARG;
+    }
+    k8sgpu_ctx *ctx = new (std::nothrow) k8sgpu_ctx();
+    if (!ctx) return K8SGPU_E_CUDA;
+    ctx->device = devices[0];
+#define CREATE_TRY(expr)                                                                             \
+    if ((e = (expr)) != cudaSuccess) {                                                               \
+        snprintf(g_create_err, sizeof g_create_err, "k8sgpu_create: %s: %s", #expr, cudaGetErrorString(e)); \
+        k8sgpu_destroy(ctx);                                                                         \
+        return K8SGPU_E_CUDA;                                                                        \
+    }
+    CREATE_TRY(cudaSetDevice(ctx->device));
+    cudaDeviceProp prop;
+    CREATE_TRY(cudaGetDeviceProperties(&prop, ctx->device));
+    if (prop.major < 10) {
+        snprintf(g_create_err, sizeof g_create_err, "k8sgpu_create: device %d is sm_%d%d; this library is sm_100a only",
+                 ctx->device, prop.major, prop.minor);
+        k8sgpu_destroy(ctx);
+        return K8SGPU_E_CUDA;
+    }
+    ctx->sm_count = prop.multiProcessorCount;
+    CREATE_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CREATE_TRY(cudaEventCreate(&ctx->ev_begin));
+    CREATE_TRY(cudaEventCreate(&ctx->ev_end));
+    for (int i = 0; i < 2 * kMaxTimedRounds; ++i) CREATE_TRY(cudaEventCreate(&ctx->ev_score[i]));
+    CREATE_TRY(cudaMallocHost((void **)&ctx->h_pinned, 64 * sizeof(uint32_t)));
+#undef CREATE_TRY
+    *out = ctx;
+    return K8SGPU_OK;
+}
+
+static void release_sort(SortScratch &s) {
+    s.keys_alt.release();
+    s.vals_alt.release();
+    s.hist.release();
+    s.scan_tmp.release();
+}
+
+extern "C" int k8sgpu_destroy(k8sgpu_ctx *ctx) {
+    if (!ctx) return K8SGPU_OK;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    PlaceState &p = ctx->place;
+    DevBuf *pb[] = {&p.node_cols, &p.pod_cols, &p.free_cols, &p.nodeq,     &p.podq,      &p.assign, &p.active[0],
+                    &p.active[1], &p.best_key, &p.best,      &p.sort_keys, &p.sort_vals, &p.seg,    &p.flags,
+                    &p.counters,  &p.scan_tmp};
+    for (DevBuf *b : pb) b->release();
+    release_sort(p.sort);
+    ReconcileState &r = ctx->rec;
+    DevBuf *rb[] = {&r.desired,    &r.pool_owner, &r.vm_owner,  &r.vm_flags,  &r.vm_ordinal,     &r.lut,    &r.pool_of,
+                    &r.current,    &r.delta,      &r.create_count, &r.kvict,  &r.victim_off,     &r.member_off,
+                    &r.create_off, &r.span_off,   &r.sort_keys, &r.sort_vals, &r.victim_vm,      &r.create_ordinal,
+                    &r.bitmap,     &r.counters,   &r.scan_tmp};
+    for (DevBuf *b : rb) b->release();
+    release_sort(r.sort);
+    for (DevBuf &b : ctx->dbg) b.release();
+    release_sort(ctx->dbg_sort);
+    if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    for (int i = 0; i < 2 * kMaxTimedRounds; ++i)
+        if (ctx->ev_score[i]) cudaEventDestroy(ctx->ev_score[i]);
+    if (ctx->ev_begin) cudaEventDestroy(ctx->ev_begin);
+    if (ctx->ev_end) cudaEventDestroy(ctx->ev_end);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_get_stats(const k8sgpu_ctx *ctx, k8sgpu_stats *out) {
+    if (!ctx || !out) return K8SGPU_E_ARG;
+    *out = ctx->stats;
+    return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_debug_sort_pairs(k8sgpu_ctx *ctx, const uint32_t *keys, const uint32_t *vals, uint32_t n,
+                                       int bits, uint32_t *out_keys, uint32_t *out_vals) {
+    K8S_ENTER(ctx);
+    reset_call_stats(ctx);
+    if (n && (!keys || !vals || !out_keys || !out_vals)) return fail(ctx, K8SGPU_E_ARG, "sort_pairs: NULL buffer");
+    if (bits < 0 || bits > 32) return fail(ctx, K8SGPU_E_ARG, "sort_pairs: bits=%d", bits);
+    cudaStream_t s = ctx->stream;
+    K8S_CUDA(ctx, ctx->dbg[0].reserve((size_t)n * 4 + 16));
+    K8S_CUDA(ctx, ctx->dbg[1].reserve((size_t)n * 4 + 16));
+    if (n) {
+        K8S_CUDA(ctx, cudaMemcpyAsync(ctx->dbg[0].p, keys, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+        K8S_CUDA(ctx, cudaMemcpyAsync(ctx->dbg[1].p, vals, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    }
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
+    int rc = sort_pairs(ctx, s, ctx->dbg[0].as<uint32_t>(), ctx->dbg[1].as<uint32_t>(), n, bits, ctx->dbg_sort);
+    if (rc) return rc;
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_end, s));
+    if (n) {
+        K8S_CUDA(ctx, cudaMemcpyAsync(out_keys, ctx->dbg[0].p, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+        K8S_CUDA(ctx, cudaMemcpyAsync(out_vals, ctx->dbg[1].p, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    }
+    K8S_CUDA(ctx, cudaStreamSynchronize(s));
+    float ms = 0.f;
+    K8S_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
+    ctx->stats.device_ms = ms;
+    return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_debug_exclusive_scan(k8sgpu_ctx *ctx, const uint32_t *in, uint32_t n, uint32_t *out,
+                                           uint32_t *total) {
+    K8S_ENTER(ctx);
+    reset_call_stats(ctx);
+    if (n && (!in || !out)) return fail(ctx, K8SGPU_E_ARG, "exclusive_scan: NULL buffer");
+    cudaStream_t s = ctx->stream;
+    K8S_CUDA(ctx, ctx->dbg[2].reserve((size_t)n * 4 + 16));
+    K8S_CUDA(ctx, ctx->dbg[3].reserve((size_t)n * 4 + 16));
+    K8S_CUDA(ctx, ctx->dbg[4].reserve(64));
+    if (n) K8S_CUDA(ctx, cudaMemcpyAsync(ctx->dbg[2].p, in, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    int rc = exclusive_scan_u32(ctx, s, ctx->dbg[2].as<uint32_t>(), ctx->dbg[3].as<uint32_t>(), n, ctx->dbg[5],
+                                ctx->dbg[4].as<uint32_t>());
+    if (rc) return rc;
+    if (n) K8S_CUDA(ctx, cudaMemcpyAsync(out, ctx->dbg[3].p, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, ctx->dbg[4].p, 4, cudaMemcpyDeviceToHost, s));
+    K8S_CUDA(ctx, cudaStreamSynchronize(s));
+    if (total) *total = ctx->h_pinned[0];
+    return K8SGPU_OK;
+}

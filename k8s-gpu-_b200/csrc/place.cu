@@ -1,0 +1,725 @@
+// place.cu -- round-based pod->node placement on one B200 (DESIGN.md policy v0).
+//
+// The reference has no scheduler source: pods are handed to Volcano (schedulerName: volcano,
+// GPU调度平台搭建.md:649).  Per round:
+//   node_prep   : current free columns -> packed 32-B node records (one per node, padded to tiles)
+//   score       : every active pod x every node: filter (a11) + key (a12) + running argmax.
+//                 Node records are staged through shared memory in 8 KB tiles by TMA bulk copies
+//                 (cp.async.bulk + mbarrier, double buffered); each thread keeps its pods in
+//                 registers and reads the tile by warp-broadcast LDS.128.
+//   finalize    : packed best key -> node row
+//   admit       : stable sort of proposals by node, segmented prefix sums in pod order,
+//                 S <= free test (a13), free -= admitted, stable compaction of the active list.
+// Integer only; no atomics decide any result except commutative max / add.
+#include <cstdlib>
+
+#include "common.cuh"
+
+namespace k8sgpu {
+
+struct __align__(16) NodeQ {  // what the inner loop reads; rebuilt from the free columns each round
+    uint32_t free_gpu_s;  // free_gpu, or 0xFFFFFFFF (= -1 signed) when the node is not schedulable
+    uint32_t free_mcpu, free_mib;
+    uint32_t sku_bit;     // 1 << sku_id
+    uint32_t zone_bit;    // 1 << zone_id
+    uint32_t taint;
+    uint32_t khi;         // 1<<31 | (0x7FFF - free_gpu) << 16 | (255 - cap_gpu) << 8
+    uint32_t pad;
+};
+static_assert(sizeof(NodeQ) == 32, "node record is 32 B: the algorithmic bytes per eval");
+
+struct __align__(16) PodQ {
+    uint32_t req_gpu, req_mcpu, req_mib;
+    uint32_t nsku, nzone, ntol;  // complements of sku_mask / zone_mask / tol_mask
+    uint32_t pzb;                // 1 << pref_zone, or 0
+    uint32_t rot;                // rot(p), DESIGN.md a12
+};
+static_assert(sizeof(PodQ) == 32, "pod record is 32 B");
+
+constexpr uint32_t kErrNode = 1u, kErrPod = 2u;
+
+__device__ __forceinline__ uint64_t mix64(uint64_t z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+// ------------------------------------------------------------------ table preparation
+
+__global__ void pod_prep_kernel(const uint32_t *__restrict__ cols, uint32_t m, uint32_t n_nodes, uint32_t policy,
+                                PodQ *__restrict__ podq, int32_t *__restrict__ assign,
+                                uint32_t *__restrict__ active, uint32_t *__restrict__ err) {
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= m) return;
+    PodQ q;
+    q.req_gpu = cols[0 * (size_t)m + p];
+    q.req_mcpu = cols[1 * (size_t)m + p];
+    q.req_mib = cols[2 * (size_t)m + p];
+    q.nsku = ~cols[3 * (size_t)m + p];
+    q.nzone = ~cols[4 * (size_t)m + p];
+    q.ntol = ~cols[5 * (size_t)m + p];
+    uint32_t pz = cols[6 * (size_t)m + p];
+    q.pzb = pz < 32u ? (1u << pz) : 0u;
+    q.rot = ((policy & K8SGPU_POLICY_ROT_ZERO) || n_nodes == 0)
+                ? 0u
+                : (uint32_t)(mix64((uint64_t)p + 0x9E3779B97F4A7C15ull) % (uint64_t)n_nodes);
+    if ((q.req_gpu | q.req_mcpu | q.req_mib) & 0x80000000u) atomicOr(err, kErrPod);
+    if (pz >= 32u && pz != K8SGPU_NONE_U32) atomicOr(err, kErrPod);
+    podq[p] = q;
+    assign[p] = K8SGPU_ASSIGN_PENDING;
+    active[p] = p;
+}
+
+__global__ void node_prep_kernel(const uint32_t *__restrict__ cols, const uint32_t *__restrict__ freec, uint32_t n,
+                                 uint32_t n_pad, NodeQ *__restrict__ nodeq, uint32_t *__restrict__ err,
+                                 int validate) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pad) return;
+    NodeQ q;
+    if (i < n) {
+        uint32_t fg = freec[i], fc = freec[(size_t)n + i], fm = freec[2 * (size_t)n + i];
+        uint32_t cap = cols[3 * (size_t)n + i], sku = cols[4 * (size_t)n + i], zone = cols[5 * (size_t)n + i];
+        uint32_t taint = cols[6 * (size_t)n + i], flags = cols[7 * (size_t)n + i];
+        if (validate && (fg > 0x7FFFu || cap > 255u || sku >= 32u || zone >= 32u || ((fc | fm) & 0x80000000u)))
+            atomicOr(err, kErrNode);
+        q.free_gpu_s = (flags & 1u) ? fg : 0xFFFFFFFFu;
+        q.free_mcpu = fc;
+        q.free_mib = fm;
+        q.sku_bit = 1u << (sku & 31u);
+        q.zone_bit = 1u << (zone & 31u);
+        q.taint = taint;
+        q.khi = 0x80000000u | ((0x7FFFu - (fg & 0x7FFFu)) << 16) | ((255u - (cap & 255u)) << 8);
+        q.pad = 0;
+    } else {  // padding up to a whole tile: never feasible
+        q.free_gpu_s = 0xFFFFFFFFu;
+        q.free_mcpu = q.free_mib = 0;
+        q.sku_bit = q.zone_bit = q.taint = 0;
+        q.khi = 0;
+        q.pad = 0;
+    }
+    nodeq[i] = q;
+}
+
+// ------------------------------------------------------------------ TMA bulk copy + mbarrier
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// ------------------------------------------------------------------ scoring
+
+// grid.x: pod tiles of 256*PPT active positions; grid.y: node splits (runs of whole tiles).
+// best_key[pos] = (key32 << 32) | (0xFFFFFFFF - ((n - rot) mod N)), 0 when no node is feasible.
+// key32 orders nodes exactly like the spec's upper key bits for a fixed pod (the pod's req_gpu
+// only shifts the 15-bit field by a constant), and its bit 0 says "n >= rot", which together
+// with the ascending scan reproduces the rotated-index tie-break without a modulo per eval.
+template <int PPT>
+__global__ void __launch_bounds__(256) score_kernel(const NodeQ *__restrict__ nodeq, uint32_t n_tiles,
+                                                    uint32_t tiles_per_split, const PodQ *__restrict__ podq,
+                                                    const uint32_t *__restrict__ active, uint32_t lo, uint32_t hi,
+                                                    unsigned long long *__restrict__ best_key, uint32_t n_nodes,
+                                                    int use_atomic) {
+    __shared__ __align__(128) uint4 tile[2][kNodeTile * 2];
+    __shared__ __align__(8) uint64_t bar[2];
+    const int tid = threadIdx.x;
+    const uint32_t t0 = blockIdx.y * tiles_per_split;
+    const uint32_t t1 = min(t0 + tiles_per_split, n_tiles);
+    constexpr uint32_t kTileBytes = kNodeTile * sizeof(NodeQ);
+
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0 && t0 < t1) {
+        mbar_expect_tx(&bar[0], kTileBytes);
+        bulk_g2s(&tile[0][0], nodeq + (size_t)t0 * kNodeTile, kTileBytes, &bar[0]);
+    }
+
+    uint32_t pos[PPT], rg[PPT], rc[PPT], rm[PPT], nsku[PPT], nzone[PPT], ntol[PPT], pzb[PPT], rot[PPT];
+    uint32_t best[PPT], bestn[PPT];
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        pos[j] = lo + (blockIdx.x * PPT + j) * 256u + tid;
+        best[j] = 0;
+        bestn[j] = 0;
+        if (pos[j] < hi) {
+            const uint4 *q = reinterpret_cast<const uint4 *>(podq + active[pos[j]]);
+            uint4 a = __ldg(q), b = __ldg(q + 1);
+            rg[j] = a.x; rc[j] = a.y; rm[j] = a.z; nsku[j] = a.w;
+            nzone[j] = b.x; ntol[j] = b.y; pzb[j] = b.z; rot[j] = b.w;
+        } else {  // idle lane: nothing is ever feasible
+            rg[j] = 0x7FFFFFFFu; rc[j] = rm[j] = 0; nsku[j] = nzone[j] = ntol[j] = 0xFFFFFFFFu; pzb[j] = 0; rot[j] = 0;
+        }
+    }
+
+    for (uint32_t t = t0; t < t1; ++t) {
+        const uint32_t it = t - t0, buf = it & 1u;
+        if (tid == 0 && t + 1 < t1) {  // prefetch the next tile into the other buffer
+            mbar_expect_tx(&bar[buf ^ 1u], kTileBytes);
+            bulk_g2s(&tile[buf ^ 1u][0], nodeq + (size_t)(t + 1) * kNodeTile, kTileBytes, &bar[buf ^ 1u]);
+        }
+        for (uint32_t spins = 0; !mbar_try_wait(&bar[buf], (it >> 1) & 1u);)
+            if (++spins > (1u << 26)) __trap();  // a lost TMA completion must fail loudly, not hang the GPU
+        const uint32_t nbase = t * kNodeTile;
+        int rrel[PPT];
+#pragma unroll
+        for (int j = 0; j < PPT; ++j) rrel[j] = (int)(rot[j] - nbase);  // node k has n >= rot  <=>  k >= rrel
+        const uint4 *tl = tile[buf];
+#pragma unroll 8
+        for (int k = 0; k < (int)kNodeTile; ++k) {
+            const uint4 a = tl[2 * k], b = tl[2 * k + 1];
+#pragma unroll
+            for (int j = 0; j < PPT; ++j) {
+                const bool feas = ((int)a.x >= (int)rg[j]) & (a.y >= rc[j]) & (a.z >= rm[j]) &
+                                  (((a.w & nsku[j]) | (b.x & nzone[j]) | (b.y & ntol[j])) == 0u);
+                uint32_t key = b.z | ((b.x & pzb[j]) ? 0x80u : 0u) | (k >= rrel[j] ? 1u : 0u);
+                if (feas && key > best[j]) {
+                    best[j] = key;
+                    bestn[j] = nbase + k;
+                }
+            }
+        }
+        __syncthreads();  // everyone is done with tile[buf] before it is refilled
+    }
+
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        if (pos[j] >= hi) continue;
+        unsigned long long key64 = 0ull;
+        if (best[j] != 0u) {
+            uint32_t ridx = bestn[j] >= rot[j] ? bestn[j] - rot[j] : bestn[j] + (n_nodes - rot[j]);
+            key64 = ((unsigned long long)best[j] << 32) | (unsigned long long)(0xFFFFFFFFu - ridx);
+        }
+        if (use_atomic) {
+            if (key64) atomicMax(&best_key[pos[j]], key64);
+        } else {
+            best_key[pos[j]] = key64;
+        }
+    }
+}
+
+__global__ void score_finalize_kernel(const unsigned long long *__restrict__ best_key, const PodQ *__restrict__ podq,
+                                      const uint32_t *__restrict__ active, uint32_t lo, uint32_t cnt,
+                                      uint32_t n_nodes, int32_t *__restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cnt) return;
+    unsigned long long key = best_key[lo + i];
+    int32_t node = -1;
+    if (key != 0ull) {
+        uint32_t ridx = 0xFFFFFFFFu - (uint32_t)key;
+        uint32_t rot = podq[active[lo + i]].rot;
+        uint32_t n = ridx + rot;  // < 2N < 2^32
+        node = (int32_t)(n >= n_nodes ? n - n_nodes : n);
+    }
+    out[i] = node;
+}
+
+// ------------------------------------------------------------------ admission (a13)
+
+__global__ void admit_keys_kernel(const int32_t *__restrict__ best, const uint32_t *__restrict__ active,
+                                  uint32_t na, uint32_t n_nodes, int32_t *__restrict__ assign,
+                                  uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= na) return;
+    int32_t b = best[i];
+    if (b < 0) assign[active[i]] = K8SGPU_ASSIGN_NONE;  // no feasible node: final
+    keys[i] = b < 0 ? n_nodes : (uint32_t)b;           // non-proposers sort behind every node
+    vals[i] = i;
+}
+
+struct Seg {  // running (saturating) demand of one node's proposers, in pod order
+    uint32_t g, c, m, head;
+};
+__device__ __forceinline__ uint32_t sat_add(uint32_t a, uint32_t b) {
+    uint32_t s = a + b;
+    return s < a ? 0xFFFFFFFFu : s;
+}
+// segmented-scan operator: right operand wins outright if it starts a segment
+__device__ __forceinline__ Seg seg_combine(const Seg &l, const Seg &r) {
+    Seg o;
+    o.head = l.head | r.head;
+    o.g = r.head ? r.g : sat_add(l.g, r.g);
+    o.c = r.head ? r.c : sat_add(l.c, r.c);
+    o.m = r.head ? r.m : sat_add(l.m, r.m);
+    return o;
+}
+__device__ __forceinline__ Seg seg_shfl_up(const Seg &x, int d) {
+    Seg y;
+    y.g = __shfl_up_sync(0xFFFFFFFFu, x.g, d);
+    y.c = __shfl_up_sync(0xFFFFFFFFu, x.c, d);
+    y.m = __shfl_up_sync(0xFFFFFFFFu, x.m, d);
+    y.head = __shfl_up_sync(0xFFFFFFFFu, x.head, d);
+    return y;
+}
+__device__ __forceinline__ Seg seg_warp_scan(Seg x, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        Seg y = seg_shfl_up(x, d);
+        if (lane >= d) x = seg_combine(y, x);
+    }
+    return x;
+}
+
+constexpr int kSegThreads = 256;
+
+// Inclusive segmented scan of one 256-element block of the sorted proposal list.
+// Returns this thread's inclusive value (without any carry from earlier blocks).
+__device__ __forceinline__ Seg seg_block_scan(Seg x, Seg *block_total) {
+    __shared__ Seg wtot[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    Seg inc = seg_warp_scan(x, lane);
+    if (lane == 31) wtot[warp] = inc;
+    __syncthreads();
+    Seg pre;
+    pre.g = pre.c = pre.m = pre.head = 0;
+    for (int w = 0; w < warp; ++w) pre = seg_combine(pre, wtot[w]);
+    Seg out = seg_combine(pre, inc);
+    if (block_total && threadIdx.x == kSegThreads - 1) *block_total = out;
+    return out;
+}
+
+__device__ __forceinline__ Seg load_seg(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals,
+                                        const uint32_t *__restrict__ active, const PodQ *__restrict__ podq,
+                                        uint32_t i, uint32_t na, uint32_t *key_out) {
+    Seg x;
+    x.g = x.c = x.m = 0;
+    x.head = 1;  // out-of-range slots start their own (ignored) segment
+    *key_out = 0xFFFFFFFFu;
+    if (i < na) {
+        uint32_t k = keys[i];
+        const PodQ *q = podq + active[vals[i]];
+        x.g = q->req_gpu;
+        x.c = q->req_mcpu;
+        x.m = q->req_mib;
+        x.head = (i == 0 || keys[i - 1] != k) ? 1u : 0u;
+        *key_out = k;
+    }
+    return x;
+}
+
+__global__ void __launch_bounds__(kSegThreads) admit_seg_reduce_kernel(
+    const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals, const uint32_t *__restrict__ active,
+    const PodQ *__restrict__ podq, uint32_t na, Seg *__restrict__ block_tot) {
+    uint32_t i = blockIdx.x * kSegThreads + threadIdx.x, key;
+    Seg x = load_seg(keys, vals, active, podq, i, na, &key);
+    seg_block_scan(x, &block_tot[blockIdx.x]);
+}
+
+// One warp turns block totals into exclusive carries (carry[b] = everything before block b).
+__global__ void admit_seg_carry_kernel(Seg *__restrict__ block_tot, uint32_t nb) {
+    const int lane = threadIdx.x;
+    Seg run;
+    run.g = run.c = run.m = run.head = 0;
+    for (uint32_t base = 0; base < nb; base += 32) {
+        uint32_t b = base + lane;
+        Seg x;
+        x.g = x.c = x.m = 0;
+        x.head = 0;
+        if (b < nb) x = block_tot[b];
+        Seg inc = seg_warp_scan(x, lane);
+        Seg with = seg_combine(run, inc);            // inclusive through block b
+        Seg prev = seg_shfl_up(with, 1);             // exclusive = inclusive of b-1
+        if (lane == 0) prev = run;
+        if (b < nb) block_tot[b] = prev;
+        run.g = __shfl_sync(0xFFFFFFFFu, with.g, 31);
+        run.c = __shfl_sync(0xFFFFFFFFu, with.c, 31);
+        run.m = __shfl_sync(0xFFFFFFFFu, with.m, 31);
+        run.head = __shfl_sync(0xFFFFFFFFu, with.head, 31);
+    }
+}
+
+// S <= free test on the inclusive prefix sums; admitted pods get their node.
+__global__ void __launch_bounds__(kSegThreads) admit_apply_kernel(
+    const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals, const uint32_t *__restrict__ active,
+    const PodQ *__restrict__ podq, uint32_t na, uint32_t n_nodes, const Seg *__restrict__ carry,
+    const uint32_t *__restrict__ freec, int32_t *__restrict__ assign, uint32_t *__restrict__ admitted) {
+    uint32_t i = blockIdx.x * kSegThreads + threadIdx.x, key;
+    Seg x = load_seg(keys, vals, active, podq, i, na, &key);
+    Seg inc = seg_block_scan(x, nullptr);
+    Seg s = seg_combine(carry[blockIdx.x], inc);
+    if (i >= na) return;
+    uint32_t ok = 0;
+    if (key < n_nodes) {
+        ok = (s.g <= freec[key]) & (s.c <= freec[(size_t)n_nodes + key]) & (s.m <= freec[2 * (size_t)n_nodes + key]);
+        if (ok) assign[active[vals[i]]] = (int32_t)key;
+    }
+    admitted[i] = ok;
+}
+
+// free -= admitted requests.  Integer atomics commute, so the result is order independent;
+// it runs after admit_apply so no admission test can see a half-updated column.
+__global__ void admit_free_update_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals,
+                                         const uint32_t *__restrict__ active, const PodQ *__restrict__ podq,
+                                         const uint32_t *__restrict__ admitted, uint32_t na, uint32_t n_nodes,
+                                         uint32_t *__restrict__ freec) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= na || !admitted[i]) return;
+    uint32_t key = keys[i];
+    const PodQ *q = podq + active[vals[i]];
+    if (q->req_gpu) atomicSub(&freec[key], q->req_gpu);
+    if (q->req_mcpu) atomicSub(&freec[(size_t)n_nodes + key], q->req_mcpu);
+    if (q->req_mib) atomicSub(&freec[2 * (size_t)n_nodes + key], q->req_mib);
+}
+
+__global__ void pending_flags_kernel(const uint32_t *__restrict__ active, const int32_t *__restrict__ assign,
+                                     uint32_t na, uint32_t *__restrict__ flags) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < na) flags[i] = assign[active[i]] == K8SGPU_ASSIGN_PENDING ? 1u : 0u;
+}
+
+__global__ void compact_kernel(const uint32_t *__restrict__ active, const uint32_t *__restrict__ flags,
+                               const uint32_t *__restrict__ offs, uint32_t na, uint32_t *__restrict__ next) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < na && flags[i]) next[offs[i]] = active[i];
+}
+
+__global__ void count_placed_kernel(const int32_t *__restrict__ assign, uint32_t m, uint32_t *__restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t ok = (i < m && assign[i] >= 0) ? 1u : 0u;
+    uint32_t cnt = __popc(__ballot_sync(0xFFFFFFFFu, ok));
+    if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(out, cnt);
+}
+
+// ------------------------------------------------------------------ host side
+
+static int check_tables(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods) {
+    if (!nodes || !pods) return fail(ctx, K8SGPU_E_ARG, "place: NULL table");
+    if (nodes->n >= 0x80000000u - 4096u || pods->m >= 0x80000000u)
+        return fail(ctx, K8SGPU_E_ARG, "place: table too large (n=%u m=%u)", nodes->n, pods->m);
+    const uint32_t *nc[8] = {nodes->free_gpu, nodes->free_mcpu, nodes->free_mib, nodes->cap_gpu,
+                             nodes->sku_id,   nodes->zone_id,   nodes->taint_mask, nodes->flags};
+    const uint32_t *pc[8] = {pods->req_gpu,  pods->req_mcpu, pods->req_mib,   pods->sku_mask,
+                             pods->zone_mask, pods->tol_mask, pods->pref_zone, pods->priority};
+    for (int c = 0; c < 8; ++c) {
+        if (nodes->n && !nc[c]) return fail(ctx, K8SGPU_E_ARG, "place: node column %d is NULL", c);
+        if (pods->m && !pc[c]) return fail(ctx, K8SGPU_E_ARG, "place: pod column %d is NULL", c);
+    }
+    return K8SGPU_OK;
+}
+
+static int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods) {
+    int rc = check_tables(ctx, nodes, pods);
+    if (rc) return rc;
+    PlaceState &st = ctx->place;
+    cudaStream_t s = ctx->stream;
+    st.uploaded = false;
+    st.n = nodes->n;
+    st.m = pods->m;
+    st.n_pad = ceil_div(st.n ? st.n : 1u, kNodeTile) * kNodeTile;
+    const size_t n = st.n, m = st.m;
+    K8S_CUDA(ctx, st.node_cols.reserve(8 * n * 4 + 16));
+    K8S_CUDA(ctx, st.pod_cols.reserve(8 * m * 4 + 16));
+    const uint32_t *nc[8] = {nodes->free_gpu, nodes->free_mcpu, nodes->free_mib, nodes->cap_gpu,
+                             nodes->sku_id,   nodes->zone_id,   nodes->taint_mask, nodes->flags};
+    const uint32_t *pc[8] = {pods->req_gpu,  pods->req_mcpu, pods->req_mib,   pods->sku_mask,
+                             pods->zone_mask, pods->tol_mask, pods->pref_zone, pods->priority};
+    for (int c = 0; c < 8; ++c) {
+        if (n) K8S_CUDA(ctx, cudaMemcpyAsync(st.node_cols.as<uint32_t>() + c * n, nc[c], n * 4, cudaMemcpyHostToDevice, s));
+        if (m) K8S_CUDA(ctx, cudaMemcpyAsync(st.pod_cols.as<uint32_t>() + c * m, pc[c], m * 4, cudaMemcpyHostToDevice, s));
+    }
+    ctx->stats.h2d_bytes += 8 * (n + m) * 4;
+    // run-state buffers
+    K8S_CUDA(ctx, st.free_cols.reserve(3 * n * 4 + 16));
+    K8S_CUDA(ctx, st.nodeq.reserve((size_t)st.n_pad * sizeof(NodeQ)));
+    K8S_CUDA(ctx, st.podq.reserve(m * sizeof(PodQ) + 32));
+    K8S_CUDA(ctx, st.assign.reserve(m * 4 + 16));
+    K8S_CUDA(ctx, st.active[0].reserve(m * 4 + 16));
+    K8S_CUDA(ctx, st.active[1].reserve(m * 4 + 16));
+    K8S_CUDA(ctx, st.best_key.reserve(m * 8 + 16));
+    K8S_CUDA(ctx, st.best.reserve(m * 4 + 16));
+    K8S_CUDA(ctx, st.sort_keys.reserve(m * 4 + 16));
+    K8S_CUDA(ctx, st.sort_vals.reserve(m * 4 + 16));
+    K8S_CUDA(ctx, st.flags.reserve(2 * m * 4 + 16));
+    K8S_CUDA(ctx, st.seg.reserve(((size_t)ceil_div(st.m ? st.m : 1u, kSegThreads) + 1) * sizeof(Seg)));
+    K8S_CUDA(ctx, st.counters.reserve(64 * 4));
+    st.uploaded = true;
+    return K8SGPU_OK;
+}
+
+static int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
+    PlaceState &st = ctx->place;
+    if (!st.uploaded) return fail(ctx, K8SGPU_E_ARG, "place: no tables uploaded");
+    st.policy_flags = policy ? policy->flags : 0u;
+    st.max_rounds = policy ? policy->max_rounds : 0u;
+    st.cur = 0;
+    st.n_active = st.m;
+    st.rounds = 0;
+    st.evals = 0;
+    st.timed = 0;
+    st.timed_evals = 0;
+    K8S_CUDA(ctx, cudaMemsetAsync(st.counters.p, 0, 64 * 4, s));
+    if (st.n)
+        K8S_CUDA(ctx, cudaMemcpyAsync(st.free_cols.p, st.node_cols.p, 3 * (size_t)st.n * 4, cudaMemcpyDeviceToDevice, s));
+    if (st.m)
+        K8S_LAUNCH(ctx, pod_prep_kernel, ceil_div(st.m, 256), 256, 0, s, st.pod_cols.as<uint32_t>(), st.m, st.n,
+                   st.policy_flags, st.podq.as<PodQ>(), st.assign.as<int32_t>(), st.active[0].as<uint32_t>(),
+                   st.counters.as<uint32_t>());
+    return K8SGPU_OK;
+}
+
+// Scores active positions [lo,hi) into d_best[0 .. hi-lo).
+static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cudaStream_t s) {
+    PlaceState &st = ctx->place;
+    if (hi > st.n_active || lo > hi) return fail(ctx, K8SGPU_E_ARG, "score: bad slice [%u,%u) of %u", lo, hi, st.n_active);
+    // node records from the current free columns (validated on the first round)
+    K8S_LAUNCH(ctx, node_prep_kernel, ceil_div(st.n_pad, 256), 256, 0, s, st.node_cols.as<uint32_t>(),
+               st.free_cols.as<uint32_t>(), st.n, st.n_pad, st.nodeq.as<NodeQ>(), st.counters.as<uint32_t>(),
+               st.rounds == 0 ? 1 : 0);
+    const uint32_t cnt = hi - lo;
+    if (cnt == 0) return K8SGPU_OK;
+    const uint32_t n_tiles = st.n_pad / kNodeTile;
+    int ppt = cnt >= 256u * 2u * 4u * (uint32_t)ctx->sm_count ? 2 : 1;
+    if (const char *e = getenv("K8SGPU_PPT")) ppt = atoi(e) >= 2 ? 2 : 1;
+    const uint32_t xb = ceil_div(cnt, 256u * ppt);
+    uint32_t splits = ceil_div(4u * (uint32_t)ctx->sm_count, xb);
+    if (const char *e = getenv("K8SGPU_SPLITS")) splits = (uint32_t)atoi(e);
+    if (splits < 1) splits = 1;
+    if (splits > n_tiles) splits = n_tiles;
+    uint32_t tps = ceil_div(n_tiles, splits);
+    splits = ceil_div(n_tiles, tps);
+    if (splits > 65535u) {
+        splits = 65535u;
+        tps = ceil_div(n_tiles, splits);
+        splits = ceil_div(n_tiles, tps);
+    }
+    const int use_atomic = splits > 1;
+    unsigned long long *bk = st.best_key.as<unsigned long long>();
+    if (use_atomic) K8S_CUDA(ctx, cudaMemsetAsync(bk + lo, 0, (size_t)cnt * 8, s));
+    const bool timed = st.timed < kMaxTimedRounds;
+    if (timed) K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed], s));
+    dim3 grid(xb, splits);
+    if (ppt == 2)
+        K8S_LAUNCH(ctx, score_kernel<2>, grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(),
+                   st.active[st.cur].as<uint32_t>(), lo, hi, bk, st.n, use_atomic);
+    else
+        K8S_LAUNCH(ctx, score_kernel<1>, grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(),
+                   st.active[st.cur].as<uint32_t>(), lo, hi, bk, st.n, use_atomic);
+    if (timed) {
+        K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed + 1], s));
+        st.timed++;
+        st.timed_evals += (uint64_t)cnt * st.n;
+    }
+    K8S_LAUNCH(ctx, score_finalize_kernel, ceil_div(cnt, 256), 256, 0, s, bk, st.podq.as<PodQ>(),
+               st.active[st.cur].as<uint32_t>(), lo, cnt, st.n, d_best);
+    return K8SGPU_OK;
+}
+
+// Admission over all n_active proposals; leaves the next active list in active[cur^1] and its
+// length (device) in counters[1].  Synchronises the stream to read the count back.
+static int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t s, uint32_t *n_active_out) {
+    PlaceState &st = ctx->place;
+    const uint32_t na = st.n_active;
+    uint32_t *cnts = st.counters.as<uint32_t>();
+    if (na) {
+        uint32_t *keys = st.sort_keys.as<uint32_t>(), *vals = st.sort_vals.as<uint32_t>();
+        uint32_t *active = st.active[st.cur].as<uint32_t>(), *next = st.active[st.cur ^ 1].as<uint32_t>();
+        uint32_t *flags = st.flags.as<uint32_t>(), *offs = flags + st.m;
+        const uint32_t g = ceil_div(na, 256);
+        K8S_LAUNCH(ctx, admit_keys_kernel, g, 256, 0, s, d_best_all, active, na, st.n, st.assign.as<int32_t>(), keys, vals);
+        int rc = sort_pairs(ctx, s, keys, vals, na, key_bits(st.n), st.sort);
+        if (rc) return rc;
+        const uint32_t nb = ceil_div(na, kSegThreads);
+        Seg *seg = st.seg.as<Seg>();
+        K8S_LAUNCH(ctx, admit_seg_reduce_kernel, nb, kSegThreads, 0, s, keys, vals, active, st.podq.as<PodQ>(), na, seg);
+        K8S_LAUNCH(ctx, admit_seg_carry_kernel, 1, 32, 0, s, seg, nb);
+        K8S_LAUNCH(ctx, admit_apply_kernel, nb, kSegThreads, 0, s, keys, vals, active, st.podq.as<PodQ>(), na, st.n,
+                   seg, st.free_cols.as<uint32_t>(), st.assign.as<int32_t>(), flags);
+        K8S_LAUNCH(ctx, admit_free_update_kernel, g, 256, 0, s, keys, vals, active, st.podq.as<PodQ>(), flags, na,
+                   st.n, st.free_cols.as<uint32_t>());
+        K8S_LAUNCH(ctx, pending_flags_kernel, g, 256, 0, s, active, st.assign.as<int32_t>(), na, flags);
+        rc = exclusive_scan_u32(ctx, s, flags, offs, na, st.scan_tmp, cnts + 1);
+        if (rc) return rc;
+        K8S_LAUNCH(ctx, compact_kernel, g, 256, 0, s, active, flags, offs, na, next);
+    } else {
+        K8S_CUDA(ctx, cudaMemsetAsync(cnts + 1, 0, 4, s));
+    }
+    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, cnts, 8, cudaMemcpyDeviceToHost, s));
+    K8S_CUDA(ctx, cudaStreamSynchronize(s));
+    if (ctx->h_pinned[0] != 0u)
+        return fail(ctx, K8SGPU_E_ARG, "place: %s table outside the input domain (see k8sgpu.h)",
+                    (ctx->h_pinned[0] & kErrNode) ? "node" : "pod");
+    st.evals += (uint64_t)na * st.n;
+    st.rounds++;
+    st.cur ^= 1;
+    st.n_active = ctx->h_pinned[1];
+    if (n_active_out) *n_active_out = st.n_active;
+    return K8SGPU_OK;
+}
+
+static int round_end(k8sgpu_ctx *ctx, cudaStream_t s) {
+    PlaceState &st = ctx->place;
+    uint32_t *cnts = st.counters.as<uint32_t>();
+    K8S_CUDA(ctx, cudaMemsetAsync(cnts + 2, 0, 4, s));
+    if (st.m)
+        K8S_LAUNCH(ctx, count_placed_kernel, ceil_div(st.m, 256), 256, 0, s, st.assign.as<int32_t>(), st.m, cnts + 2);
+    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, cnts, 16, cudaMemcpyDeviceToHost, s));
+    K8S_CUDA(ctx, cudaStreamSynchronize(s));
+    if (ctx->h_pinned[0] != 0u)
+        return fail(ctx, K8SGPU_E_ARG, "place: %s table outside the input domain (see k8sgpu.h)",
+                    (ctx->h_pinned[0] & kErrNode) ? "node" : "pod");
+    ctx->stats.rounds = st.rounds;
+    ctx->stats.evals = st.evals;
+    ctx->stats.placed = ctx->h_pinned[2];
+    float ms = 0.f, tot = 0.f;
+    for (int i = 0; i < st.timed; ++i) {
+        if (cudaEventElapsedTime(&ms, ctx->ev_score[2 * i], ctx->ev_score[2 * i + 1]) == cudaSuccess) tot += ms;
+    }
+    ctx->stats.score_ms = tot;
+    ctx->stats.score_evals = st.timed_evals;
+    ctx->stats.score_launches = (uint32_t)st.timed;
+    return K8SGPU_OK;
+}
+
+static int place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy) {
+    PlaceState &st = ctx->place;
+    cudaStream_t s = ctx->stream;
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
+    int rc = round_begin(ctx, policy, s);
+    if (rc) return rc;
+    while (st.n_active > 0 && (st.max_rounds == 0 || st.rounds < st.max_rounds)) {
+        rc = round_score(ctx, 0, st.n_active, st.best.as<int32_t>(), s);
+        if (rc) return rc;
+        rc = round_admit(ctx, st.best.as<int32_t>(), s, nullptr);
+        if (rc) return rc;
+    }
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_end, s));
+    rc = round_end(ctx, s);
+    if (rc) return rc;
+    float ms = 0.f;
+    K8S_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
+    ctx->stats.device_ms = ms;
+    return K8SGPU_OK;
+}
+
+static int place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out) {
+    PlaceState &st = ctx->place;
+    cudaStream_t s = ctx->stream;
+    if (!out) return fail(ctx, K8SGPU_E_ARG, "place: NULL out");
+    if (st.m && !out->assign) return fail(ctx, K8SGPU_E_ARG, "place: out->assign is NULL");
+    if (st.m) {
+        K8S_CUDA(ctx, cudaMemcpyAsync(out->assign, st.assign.p, (size_t)st.m * 4, cudaMemcpyDeviceToHost, s));
+        ctx->stats.d2h_bytes += (uint64_t)st.m * 4;
+    }
+    uint32_t *dst[3] = {out->free_gpu, out->free_mcpu, out->free_mib};
+    for (int c = 0; c < 3; ++c)
+        if (dst[c] && st.n) {
+            K8S_CUDA(ctx, cudaMemcpyAsync(dst[c], st.free_cols.as<uint32_t>() + (size_t)c * st.n, (size_t)st.n * 4,
+                                          cudaMemcpyDeviceToHost, s));
+            ctx->stats.d2h_bytes += (uint64_t)st.n * 4;
+        }
+    K8S_CUDA(ctx, cudaStreamSynchronize(s));
+    return K8SGPU_OK;
+}
+
+}  // namespace k8sgpu
+
+using namespace k8sgpu;
+
+extern "C" int k8sgpu_place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods) {
+    K8S_ENTER(ctx);
+    reset_call_stats(ctx);
+    int rc = place_upload(ctx, nodes, pods);
+    if (rc) return rc;
+    K8S_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy) {
+    K8S_ENTER(ctx);
+    reset_call_stats(ctx);
+    return place_run(ctx, policy);
+}
+
+extern "C" int k8sgpu_place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out) {
+    K8S_ENTER(ctx);
+    ctx->stats.d2h_bytes = 0;
+    return place_download(ctx, out);
+}
+
+extern "C" int k8sgpu_place(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods,
+                            const k8sgpu_policy *policy, k8sgpu_place_out *out) {
+    K8S_ENTER(ctx);
+    reset_call_stats(ctx);
+    int rc = place_upload(ctx, nodes, pods);
+    if (rc) return rc;
+    rc = place_run(ctx, policy);
+    if (rc) return rc;
+    return place_download(ctx, out);
+}
+
+extern "C" int k8sgpu_score_once(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, int32_t *best_node) {
+    K8S_ENTER(ctx);
+    reset_call_stats(ctx);
+    PlaceState &st = ctx->place;
+    cudaStream_t s = ctx->stream;
+    if (!best_node && st.m) return fail(ctx, K8SGPU_E_ARG, "score_once: NULL output");
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
+    int rc = round_begin(ctx, policy, s);
+    if (rc) return rc;
+    rc = round_score(ctx, 0, st.n_active, st.best.as<int32_t>(), s);
+    if (rc) return rc;
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_end, s));
+    if (st.m) K8S_CUDA(ctx, cudaMemcpyAsync(best_node, st.best.p, (size_t)st.m * 4, cudaMemcpyDeviceToHost, s));
+    ctx->stats.d2h_bytes = (uint64_t)st.m * 4;
+    st.evals = (uint64_t)st.m * st.n;
+    st.rounds = 1;
+    rc = round_end(ctx, s);
+    if (rc) return rc;
+    float ms = 0.f;
+    K8S_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
+    ctx->stats.device_ms = ms;
+    return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_place_round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, void *stream,
+                                        uint32_t *n_active) {
+    K8S_ENTER(ctx);
+    reset_call_stats(ctx);
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    int rc = round_begin(ctx, policy, s);
+    if (rc) return rc;
+    if (n_active) *n_active = ctx->place.n_active;
+    return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_place_round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, void *stream) {
+    K8S_ENTER(ctx);
+    if (!d_best && hi > lo) return fail(ctx, K8SGPU_E_ARG, "round_score: NULL device buffer");
+    return round_score(ctx, lo, hi, d_best, stream ? (cudaStream_t)stream : ctx->stream);
+}
+
+extern "C" int k8sgpu_place_round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, void *stream,
+                                        uint32_t *n_active) {
+    K8S_ENTER(ctx);
+    if (!d_best_all && ctx->place.n_active) return fail(ctx, K8SGPU_E_ARG, "round_admit: NULL device buffer");
+    return round_admit(ctx, d_best_all, stream ? (cudaStream_t)stream : ctx->stream, n_active);
+}
+
+extern "C" int k8sgpu_place_round_end(k8sgpu_ctx *ctx, void *stream) {
+    K8S_ENTER(ctx);
+    return round_end(ctx, stream ? (cudaStream_t)stream : ctx->stream);
+}

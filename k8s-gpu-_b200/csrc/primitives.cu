@@ -1,0 +1,201 @@
+// primitives.cu -- device-wide exclusive scan and stable LSD radix sort of (key,val) pairs.
+//
+// These are the deterministic building blocks of scale-down victim order (README.md:214:
+// "the first k VMs in list order") and of placement admission order: both
+// need "rank among earlier rows of the same bucket", i.e. a STABLE partition by bucket id.
+// No atomics decide any output position, so results do not depend on scheduling order.
+#include "common.cuh"
+
+namespace k8sgpu {
+
+// ------------------------------------------------------------------ exclusive scan (u32)
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t x, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, d);
+        if (lane >= d) x += y;
+    }
+    return x;
+}
+
+// Scans one tile of kScanTile elements, 256 threads, rows of 256 (coalesced).
+// carry_in is added to every output.  Returns the tile total in *tile_total (thread 0).
+__device__ __forceinline__ uint32_t block_scan_tile(const uint32_t *in, uint32_t *out,  // may alias (in place)
+                                                    uint32_t base, uint32_t n, uint32_t carry_in, bool write) {
+    __shared__ uint32_t warp_tot[8];
+    __shared__ uint32_t row_carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) row_carry = carry_in;
+    __syncthreads();
+#pragma unroll 1
+    for (uint32_t r = 0; r < kScanTile / kScanThreads; ++r) {
+        uint32_t i = base + r * kScanThreads + tid;
+        uint32_t x = (i < n) ? in[i] : 0u;
+        uint32_t inc = warp_incl_scan(x, lane);
+        if (lane == 31) warp_tot[warp] = inc;
+        __syncthreads();
+        uint32_t woff = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w)
+            if (w < warp) woff += warp_tot[w];
+        uint32_t carry = row_carry;
+        if (write && i < n) out[i] = carry + woff + inc - x;
+        __syncthreads();
+        if (tid == kScanThreads - 1) row_carry = carry + woff + inc;
+        __syncthreads();
+    }
+    return row_carry;
+}
+
+__global__ void __launch_bounds__(kScanThreads) scan_reduce_kernel(const uint32_t *__restrict__ in, uint32_t n,
+                                                                   uint32_t *__restrict__ block_sums) {
+    uint32_t total = block_scan_tile(in, nullptr, blockIdx.x * kScanTile, n, 0u, false);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(kScanThreads) scan_down_kernel(const uint32_t *__restrict__ in,
+                                                                 uint32_t *__restrict__ out, uint32_t n,
+                                                                 const uint32_t *__restrict__ block_offs) {
+    block_scan_tile(in, out, blockIdx.x * kScanTile, n, block_offs[blockIdx.x], true);
+}
+
+// Single block: scans n <= any size by looping over tiles; writes total.
+__global__ void __launch_bounds__(kScanThreads) scan_single_kernel(const uint32_t *in,
+                                                                   uint32_t *out, uint32_t n,
+                                                                   uint32_t *__restrict__ total) {
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < n; base += kScanTile) carry = block_scan_tile(in, out, base, n, carry, true);
+    if (threadIdx.x == 0 && total) *total = carry;
+}
+
+int exclusive_scan_u32(k8sgpu_ctx *ctx, cudaStream_t s, const uint32_t *d_in, uint32_t *d_out, uint32_t n,
+                       DevBuf &tmp, uint32_t *d_total) {
+    if (n <= 8 * kScanTile) {  // small: one block walks it
+        K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanThreads, 0, s, d_in, d_out, n, d_total);
+        return K8SGPU_OK;
+    }
+    uint32_t nb = ceil_div(n, kScanTile);
+    // tmp holds the block sums of this level; deeper levels use the tail of the same buffer
+    K8S_CUDA(ctx, tmp.reserve(((size_t)nb * 2 + 64) * sizeof(uint32_t)));
+    uint32_t *sums = tmp.as<uint32_t>();
+    K8S_LAUNCH(ctx, scan_reduce_kernel, nb, kScanThreads, 0, s, d_in, n, sums);
+    // nb <= 2^31 / 2048 = 2^20 block sums: one block scans them in place
+    K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanThreads, 0, s, sums, sums, nb, d_total);
+    K8S_LAUNCH(ctx, scan_down_kernel, nb, kScanThreads, 0, s, d_in, d_out, n, sums);
+    return K8SGPU_OK;
+}
+
+// ------------------------------------------------------------------ stable LSD radix sort
+
+// Per-block digit histogram, written digit-major: hist[d * nblocks + block].
+__global__ void __launch_bounds__(kSortThreads) sort_hist_kernel(const uint32_t *__restrict__ keys, uint32_t n,
+                                                                 int shift, uint32_t mask,
+                                                                 uint32_t *__restrict__ hist, uint32_t nblocks) {
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * kSortTile;
+#pragma unroll
+    for (uint32_t r = 0; r < kSortTile / kSortThreads; ++r) {
+        uint32_t i = base + r * kSortThreads + threadIdx.x;
+        if (i < n) atomicAdd(&h[(keys[i] >> shift) & mask], 1u);  // counts only: order-free
+    }
+    __syncthreads();
+    hist[threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
+}
+
+// Stable scatter.  Warp w owns the contiguous 256-element chunk w of the tile and walks it in
+// 8 sub-rows of 32, so (warp, sub-row, lane) order == input order.  Ranks inside a sub-row come
+// from __match_any_sync; per-warp digit counters carry the rank across sub-rows.
+__global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(
+    const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals, uint32_t *__restrict__ out_keys,
+    uint32_t *__restrict__ out_vals, uint32_t n, int shift, uint32_t mask, const uint32_t *__restrict__ hist_scan,
+    uint32_t nblocks) {
+    __shared__ uint32_t cnt[8][256];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) cnt[w][tid] = 0;
+    __syncthreads();
+
+    const uint32_t chunk = blockIdx.x * kSortTile + warp * 256;
+    uint32_t k[8], v[8], rank[8];
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        uint32_t i = chunk + s * 32 + lane;
+        bool in = i < n;
+        k[s] = in ? keys[i] : 0u;
+        v[s] = in ? vals[i] : 0u;
+    }
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        uint32_t i = chunk + s * 32 + lane;
+        bool in = i < n;
+        uint32_t live = __ballot_sync(0xFFFFFFFFu, in);
+        rank[s] = 0;
+        if (in) {
+            uint32_t d = (k[s] >> shift) & mask;
+            uint32_t peers = __match_any_sync(live, d);
+            uint32_t before = cnt[warp][d];
+            rank[s] = before + __popc(peers & lt);
+            __syncwarp(live);
+            if ((peers & lt) == 0) cnt[warp][d] = before + __popc(peers);  // lowest peer updates
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    {  // thread d: turn per-warp counts of digit d into absolute output bases
+        uint32_t run = hist_scan[tid * nblocks + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            uint32_t t = cnt[w][tid];
+            cnt[w][tid] = run;
+            run += t;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        uint32_t i = chunk + s * 32 + lane;
+        if (i < n) {
+            uint32_t d = (k[s] >> shift) & mask;
+            uint32_t dst = cnt[warp][d] + rank[s];
+            out_keys[dst] = k[s];
+            out_vals[dst] = v[s];
+        }
+    }
+}
+
+int sort_pairs(k8sgpu_ctx *ctx, cudaStream_t s, uint32_t *keys, uint32_t *vals, uint32_t n, int bits,
+               SortScratch &scr) {
+    if (n <= 1 || bits <= 0) return K8SGPU_OK;
+    const uint32_t nb = ceil_div(n, kSortTile);
+    K8S_CUDA(ctx, scr.keys_alt.reserve((size_t)n * 4));
+    K8S_CUDA(ctx, scr.vals_alt.reserve((size_t)n * 4));
+    K8S_CUDA(ctx, scr.hist.reserve(((size_t)nb * 256 * 2 + 256) * 4));
+    uint32_t *hist = scr.hist.as<uint32_t>();
+    uint32_t *hist_scan = hist + (size_t)nb * 256;
+
+    uint32_t *src_k = keys, *src_v = vals, *dst_k = scr.keys_alt.as<uint32_t>(), *dst_v = scr.vals_alt.as<uint32_t>();
+    int passes = 0;
+    for (int shift = 0; shift < bits; shift += 8, ++passes) {
+        int w = bits - shift < 8 ? bits - shift : 8;
+        uint32_t mask = (1u << w) - 1u;
+        K8S_LAUNCH(ctx, sort_hist_kernel, nb, kSortThreads, 0, s, src_k, n, shift, mask, hist, nb);
+        int rc = exclusive_scan_u32(ctx, s, hist, hist_scan, nb * 256, scr.scan_tmp, nullptr);
+        if (rc) return rc;
+        K8S_LAUNCH(ctx, sort_scatter_kernel, nb, kSortThreads, 0, s, src_k, src_v, dst_k, dst_v, n, shift, mask,
+                   hist_scan, nb);
+        uint32_t *t;
+        t = src_k; src_k = dst_k; dst_k = t;
+        t = src_v; src_v = dst_v; dst_v = t;
+    }
+    if (passes & 1) {
+        K8S_CUDA(ctx, cudaMemcpyAsync(keys, src_k, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+        K8S_CUDA(ctx, cudaMemcpyAsync(vals, src_v, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+    }
+    return K8SGPU_OK;
+}
+
+}  // namespace k8sgpu

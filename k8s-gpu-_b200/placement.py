@@ -1,0 +1,120 @@
+"""Host-side driver of round-based placement across one process per GPU.
+
+Every rank holds the same node and pod tables (replicated) and the same active list.  Per round
+each rank scores only its contiguous slice of the active list on its own GPU, the slices are
+all-gathered (NCCL over NVLink through torch.distributed; gloo in the CPU tests), and every rank
+runs the admission step on the full proposal list, so all replicas stay bit-identical and the
+result cannot depend on the number of ranks (single-collective form).
+
+The engine does the computing.  `CudaEngine` is the product: it calls libk8sgpu.so through the
+C-ABI round entry points.  tests/ plug in a CPU stand-in to exercise this protocol with gloo.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+class CudaEngine:
+    """Round API of libk8sgpu.so on the caller's current torch CUDA stream."""
+
+    def __init__(self, ctx):
+        import torch
+
+        self.torch = torch
+        self.ctx = ctx
+        self.device = torch.device("cuda", ctx.device)
+        self._mine = None
+
+    def upload(self, nodes, pods):
+        self.ctx.place_upload(nodes, pods)
+        self.m = len(pods["req_gpu"])
+
+    def _stream(self):
+        return self.torch.cuda.current_stream(self.device).cuda_stream
+
+    def begin(self, flags, max_rounds):
+        return self.ctx.round_begin(flags, max_rounds, self._stream())
+
+    def score(self, lo, hi, slice_len):
+        if self._mine is None or self._mine.numel() < slice_len:
+            self._mine = self.torch.empty(max(slice_len, 1), dtype=self.torch.int32, device=self.device)
+        out = self._mine[:slice_len]
+        self.ctx.round_score(lo, hi, out.data_ptr(), self._stream())
+        return out
+
+    def new_gather_buffer(self, numel):
+        return self.torch.empty(max(numel, 1), dtype=self.torch.int32, device=self.device)
+
+    def admit(self, all_best):
+        return self.ctx.round_admit(all_best.data_ptr(), self._stream())
+
+    def end(self):
+        return self.ctx.round_end(self._stream())
+
+    def download(self):
+        return self.ctx.place_download()
+
+
+class ShardedPlacer:
+    def __init__(self, ctx=None, dist=None, rank=0, world=1, engine=None):
+        self.engine = engine if engine is not None else CudaEngine(ctx)
+        self.ctx = ctx
+        self.dist = dist if world > 1 else None
+        self.rank, self.world = rank, world
+        self._all = None
+
+    def upload(self, nodes, pods):
+        self.engine.upload(nodes, pods)
+
+    @staticmethod
+    def slice_of(n_active, rank, world):
+        """Contiguous slice [lo,hi) of the active list that `rank` scores; equal-length slots."""
+        slice_len = -(-n_active // world)
+        lo = min(rank * slice_len, n_active)
+        return lo, min(lo + slice_len, n_active), slice_len
+
+    def run(self, flags=0, max_rounds=0):
+        """One whole placement from the uploaded tables.  Returns the library's stats dict plus
+        step_ms (device time of the step on this rank)."""
+        if self.world == 1 and isinstance(self.engine, CudaEngine):
+            st = self.ctx.place_run(flags, max_rounds)  # the in-library loop: fewer host round trips
+            st["step_ms"] = st["device_ms"]
+            return st
+        eng = self.engine
+        torch = getattr(eng, "torch", None)
+        ev = None
+        if torch is not None and isinstance(eng, CudaEngine):
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record()
+        na = eng.begin(flags, max_rounds)
+        rounds = 0
+        while na and (max_rounds == 0 or rounds < max_rounds):
+            lo, hi, slice_len = self.slice_of(na, self.rank, self.world)
+            mine = eng.score(lo, hi, slice_len)
+            if self.dist is not None:
+                need = slice_len * self.world
+                if self._all is None or self._all.numel() < need:
+                    self._all = eng.new_gather_buffer(need)
+                allb = self._all[:need]
+                self.dist.all_gather_into_tensor(allb, mine)
+            else:
+                allb = mine
+            na = eng.admit(allb)
+            rounds += 1
+        st = eng.end()
+        if ev is not None:
+            ev[1].record()
+            ev[1].synchronize()
+            st["step_ms"] = ev[0].elapsed_time(ev[1])
+        return st
+
+    def download(self):
+        return self.engine.download()
+
+
+def place(nodes: dict, pods: dict, flags: int = 0, max_rounds: int = 0, device: int = 0) -> dict:
+    """Convenience: single-GPU placement of host tables (numpy uint32 columns)."""
+    from . import capi
+
+    with capi.Context(device) as ctx:
+        return ctx.place(nodes, pods, flags, max_rounds)

@@ -1,0 +1,315 @@
+"""Parity of the CUDA path (through the C-ABI, libk8sgpu.so) against the CPU oracle.
+Bit-exact: everything on this path is integer / index work.  Run on the B200 box:
+    python -m pytest tests -m gpu -x -q
+"""
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+spec = importlib.util.spec_from_file_location("make_golden", os.path.join(HERE, "golden", "make_golden.py"))
+mg = importlib.util.module_from_spec(spec)
+spec.loader.exec_module(mg)
+
+NONE = 0xFFFFFFFF
+NCPU = os.cpu_count() or 1
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import k8sgpu_b200  # noqa: F401
+    from k8sgpu_b200 import capi
+
+    c = capi.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def capi():
+    import k8sgpu_b200  # noqa: F401
+    from k8sgpu_b200 import capi as c
+
+    return c
+
+
+def same_placement(got, want):
+    for k in ("assign", "free_gpu", "free_mcpu", "free_mib"):
+        assert np.array_equal(got[k], want[k]), k
+    assert (got["rounds"], got["placed"], got["evals"]) == (want["rounds"], want["placed"], want["evals"])
+
+
+# ------------------------------------------------------------------ primitives
+@pytest.mark.parametrize("n", [0, 1, 31, 2047, 2048, 2049, 16384, 16385, 100_003, 1_200_000])
+def test_exclusive_scan(ctx, n):
+    rng = np.random.default_rng(n)
+    a = rng.integers(0, 1000, n, dtype=np.uint32)
+    out, tot = ctx.exclusive_scan(a)
+    want = np.concatenate([[0], np.cumsum(a, dtype=np.uint64)[:-1]]).astype(np.uint32) if n else a
+    assert np.array_equal(out, want) and tot == int(a.sum())
+
+
+@pytest.mark.parametrize("n,bits", [(0, 8), (1, 8), (33, 3), (2048, 8), (2049, 9), (5000, 1), (100_003, 17),
+                                    (1_000_000, 20), (300_000, 32)])
+def test_sort_pairs_is_stable(ctx, n, bits):
+    rng = np.random.default_rng(n + bits)
+    keys = rng.integers(0, 1 << min(bits, 31), n, dtype=np.uint32)
+    if n > 10:
+        keys[: n // 3] = keys[0]  # one very long bucket
+    vals = np.arange(n, dtype=np.uint32)
+    k, v = ctx.sort_pairs(keys, vals, bits)
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(k, keys[order]) and np.array_equal(v, vals[order])
+
+
+# ------------------------------------------------------------------ scoring kernel alone
+@pytest.mark.parametrize("ppt,splits", [(None, None), ("1", "1"), ("2", "1"), ("1", "3"), ("2", "7")])
+@pytest.mark.parametrize("flags", [0, 1])
+def test_score_once_matches_oracle(ctx, orc, synth, ppt, splits, flags, monkeypatch):
+    if ppt:
+        monkeypatch.setenv("K8SGPU_PPT", ppt)
+        monkeypatch.setenv("K8SGPU_SPLITS", splits)
+    nodes, pods = synth.gen_nodes(1500, config_id=5), synth.gen_pods(3333, config_id=5)
+    ctx.place_upload(nodes, pods)
+    got = ctx.score_once(flags)
+    want = orc.score_round(nodes, (nodes["free_gpu"], nodes["free_mcpu"], nodes["free_mib"]), pods,
+                           np.arange(3333, dtype=np.uint32), flags=flags, nthreads=NCPU)
+    assert np.array_equal(got, want)
+
+
+def test_score_once_identical_ties(ctx, orc, synth):
+    # every node ties on the upper key bits: the result is decided by the rotated index alone
+    nodes, pods = synth.gen_identical(777, 2000)
+    ctx.place_upload(nodes, pods)
+    free = (nodes["free_gpu"], nodes["free_mcpu"], nodes["free_mib"])
+    act = np.arange(2000, dtype=np.uint32)
+    assert np.array_equal(ctx.score_once(0), orc.score_round(nodes, free, pods, act, flags=0))
+    assert np.array_equal(ctx.score_once(1), np.zeros(2000, np.int32))
+
+
+# ------------------------------------------------------------------ whole placement
+@pytest.mark.parametrize("name", list(mg.PLACE_CASES) + list(mg.TIES_CASES))
+def test_place_matches_golden_and_oracle(ctx, orc, name):
+    nodes, pods, flags = mg.place_inputs(name)
+    g = np.load(os.path.join(HERE, "golden", f"place_{name}.npz"))
+    got = ctx.place(nodes, pods, flags=flags)
+    for k in ("assign", "free_gpu", "free_mcpu", "free_mib"):
+        assert np.array_equal(got[k], g[k]), k
+    assert (got["rounds"], got["placed"], got["evals"]) == (int(g["rounds"]), int(g["placed"]), int(g["evals"]))
+    same_placement(got, orc.place(nodes, pods, flags=flags, nthreads=NCPU))
+
+
+@pytest.mark.parametrize("h100,taint,m", [(0, 0, 10), (50, 5, 100), (100, 50, 1000), (30, 5, 10_000),
+                                          (50, 0, 40_000)])
+def test_place_heterogeneous_sweep(ctx, orc, synth, h100, taint, m):
+    # BASELINE.json config 5 at sizes the oracle finishes in seconds
+    nodes = synth.gen_nodes(2000, config_id=5, h100_pct=h100, taint_pct=taint)
+    pods = synth.gen_pods(m, config_id=5)
+    same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
+
+
+def test_k12_ties_rot_zero(ctx, synth):
+    nodes, pods = synth.gen_identical(5, 41)
+    r = ctx.place(nodes, pods, flags=1)
+    assert r["assign"].tolist() == [i // 8 for i in range(40)] + [-1]
+    assert r["rounds"] == 6 and r["free_gpu"].tolist() == [0] * 5
+
+
+def test_k13_k14_and_prefix_rule(ctx, orc):
+    def tab(rows, cols):
+        return {c: np.array([r[i] for r in rows], np.uint32) for i, c in enumerate(cols)}
+
+    ncols = ("free_gpu", "free_mcpu", "free_mib", "cap_gpu", "sku_id", "zone_id", "taint_mask", "flags")
+    pcols = ("req_gpu", "req_mcpu", "req_mib", "sku_mask", "zone_mask", "tol_mask", "pref_zone", "priority")
+    # K13: taint without toleration -> -1; with toleration -> placed
+    nodes = tab([(4, 48000, 900000, 8, 1, 2, 1, 1)], ncols)
+    pods = tab([(1, 4000, 28672, NONE, NONE, 0, NONE, 0), (1, 4000, 28672, NONE, NONE, 1, NONE, 0)], pcols)
+    assert ctx.place(nodes, pods)["assign"].tolist() == [-1, 0]
+    # K14: pod larger than any node -> -1 in one round
+    pods = tab([(9, 4000, 28672, NONE, NONE, 1, NONE, 0)], pcols)
+    r = ctx.place(nodes, pods)
+    assert r["assign"].tolist() == [-1] and r["rounds"] == 1
+    # a13: rejected proposers still count in the prefix sums
+    nodes = tab([(3, 48000, 900000, 8, 1, 2, 0, 1)], ncols)
+    pods = tab([(2, 1, 1, NONE, NONE, 0, NONE, 0), (2, 1, 1, NONE, NONE, 0, NONE, 0), (1, 1, 1, NONE, NONE, 0, NONE, 0)],
+               pcols)
+    assert ctx.place(nodes, pods, max_rounds=1)["assign"].tolist() == [0, -2, -2]
+    r = ctx.place(nodes, pods)
+    assert r["assign"].tolist() == [0, -1, 0] and r["rounds"] == 2
+    same_placement(r, orc.place(nodes, pods))
+
+
+def test_empty_tables(ctx, synth):
+    nodes, pods = synth.gen_nodes(10), synth.gen_pods(7)
+    e_nodes = {k: v[:0] for k, v in nodes.items()}
+    e_pods = {k: v[:0] for k, v in pods.items()}
+    r = ctx.place(e_nodes, pods)
+    assert r["assign"].tolist() == [-1] * 7 and r["rounds"] == 1
+    r = ctx.place(nodes, e_pods)
+    assert r["assign"].tolist() == [] and r["rounds"] == 0 and np.array_equal(r["free_gpu"], nodes["free_gpu"])
+
+
+def test_input_domain_is_enforced(ctx, capi, synth):
+    nodes, pods = synth.gen_nodes(100), synth.gen_pods(100)
+    bad = dict(nodes)
+    bad["cap_gpu"] = nodes["cap_gpu"].copy()
+    bad["cap_gpu"][7] = 256
+    with pytest.raises(capi.K8sGpuError) as e:
+        ctx.place(bad, pods)
+    assert e.value.code == capi.E_ARG
+    badp = dict(pods)
+    badp["pref_zone"] = pods["pref_zone"].copy()
+    badp["pref_zone"][3] = 40
+    with pytest.raises(capi.K8sGpuError) as e:
+        ctx.place(nodes, badp)
+    assert e.value.code == capi.E_ARG
+    ctx.place(nodes, pods)  # the context stays usable
+
+
+def test_resident_run_is_repeatable(ctx, orc, synth):
+    nodes, pods = synth.gen_nodes(900), synth.gen_pods(5000)
+    ctx.place_upload(nodes, pods)
+    want = orc.place(nodes, pods, nthreads=NCPU)
+    for _ in range(2):
+        st = ctx.place_run()
+        got = ctx.place_download()
+        got.update(st)
+        same_placement(got, want)
+    assert st["kernel_launches"] > 0 and st["score_launches"] == st["rounds"]
+
+
+def test_round_api_with_two_emulated_shards(ctx, orc, synth):
+    """The round-at-a-time entry points with the active list scored in two slices (what two
+    cooperating processes do) give the single-call result."""
+    import torch
+
+    nodes, pods = synth.gen_nodes(800), synth.gen_pods(4000)
+    ctx.place_upload(nodes, pods)
+    stream = torch.cuda.current_stream().cuda_stream
+    na = ctx.round_begin(stream=stream)
+    buf = torch.empty(4000, dtype=torch.int32, device="cuda:0")
+    while na:
+        half = (na + 1) // 2
+        ctx.round_score(0, half, buf.data_ptr(), stream)
+        ctx.round_score(half, na, buf.data_ptr() + 4 * half, stream)
+        na = ctx.round_admit(buf.data_ptr(), stream)
+    st = ctx.round_end(stream)
+    got = ctx.place_download()
+    got.update(st)
+    same_placement(got, orc.place(nodes, pods, nthreads=NCPU))
+
+
+def test_config3_full_size(ctx, orc, synth):
+    """BASELINE.json config 3 at full size: 10k nodes x 100k pods, bit-exact vs the oracle
+    (the oracle needs roughly 100 core-seconds; it is threaded over pods)."""
+    nodes, pods = synth.gen_nodes(10_000), synth.gen_pods(100_000)
+    got = ctx.place(nodes, pods)
+    same_placement(got, orc.place(nodes, pods, nthreads=NCPU))
+    # size-independent properties: no over-commit, free = initial - used
+    ok = got["assign"] >= 0
+    for col, req in (("free_gpu", "req_gpu"), ("free_mcpu", "req_mcpu"), ("free_mib", "req_mib")):
+        used = np.bincount(got["assign"][ok], weights=pods[req][ok].astype(np.float64), minlength=10_000)
+        assert (used <= nodes[col]).all()
+        assert np.array_equal(nodes[col] - used.astype(np.uint32), got[col])
+
+
+def test_config4_shape_properties(ctx, synth):
+    """BASELINE.json config 4 node count (100k) with 200k pods: too big for the oracle in test
+    time, so check the invariants the policy guarantees and idempotence of a second pass."""
+    nodes, pods = synth.gen_nodes(100_000, config_id=4), synth.gen_pods(200_000, config_id=4)
+    got = ctx.place(nodes, pods)
+    a = got["assign"]
+    ok = a >= 0
+    assert ((a >= 0) | (a == -1)).all()
+    for col, req in (("free_gpu", "req_gpu"), ("free_mcpu", "req_mcpu"), ("free_mib", "req_mib")):
+        used = np.bincount(a[ok], weights=pods[req][ok].astype(np.float64), minlength=100_000)
+        assert np.array_equal(nodes[col] - used.astype(np.uint32), got[col])
+    n = a[ok]
+    assert (nodes["flags"][n] & 1).all()
+    assert ((pods["sku_mask"][ok] >> nodes["sku_id"][n]) & 1).all()
+    assert ((pods["zone_mask"][ok] >> nodes["zone_id"][n]) & 1).all()
+    assert ((nodes["taint_mask"][n] & ~pods["tol_mask"][ok]) == 0).all()
+    # pods left unplaced stay unplaced against the final tables (nothing feasible remains)
+    left = {k: v[~ok] for k, v in pods.items()}
+    after = dict(nodes, free_gpu=got["free_gpu"], free_mcpu=got["free_mcpu"], free_mib=got["free_mib"])
+    again = ctx.place(after, left)
+    assert (again["assign"] == -1).all() and again["rounds"] == 1
+
+
+# ------------------------------------------------------------------ batch reconcile
+def same_reconcile(got, want):
+    for k in want:
+        assert np.array_equal(got[k], want[k]), k
+
+
+@pytest.mark.parametrize("name", list(mg.RECONCILE_CASES))
+def test_reconcile_matches_golden(ctx, synth, name):
+    c = mg.RECONCILE_CASES[name]
+    t = synth.gen_reconcile(c["p"], c["v"], c["config_id"])
+    got = ctx.reconcile_batch(t["desired"], t["pool_owner_id"], t["vm_owner_id"], t["vm_flags"], t["n_owner_ids"],
+                              t["vm_ordinal"])
+    g = np.load(os.path.join(HERE, "golden", f"reconcile_{name}.npz"))
+    for k in g.files:
+        assert np.array_equal(got[k], g[k]), k
+
+
+@pytest.mark.parametrize("p,v", [(1000, 100_000), (1, 1000), (7, 3), (5000, 1_000_003), (40_000, 400_000)])
+def test_reconcile_matches_oracle(ctx, orc, synth, p, v):
+    # (1000, 100000) is BASELINE.json config 2 at full size
+    t = synth.gen_reconcile(p, v)
+    args = (t["desired"], t["pool_owner_id"], t["vm_owner_id"], t["vm_flags"], t["n_owner_ids"], t["vm_ordinal"])
+    same_reconcile(ctx.reconcile_batch(*args), orc.reconcile_batch(*args, nthreads=NCPU))
+
+
+def test_reconcile_hand_vector_and_config1(ctx):
+    owner = [1, 0, 1, NONE, 0, 1, 9, 1, 0]
+    flags = [1, 1, 1, 1, 1, 0, 1, 1, 1]
+    out = ctx.reconcile_batch([1, 1, 4], [0, 1, 2], owner, flags, 16, [0, 0, 1, 0, 2, 5, 0, 3, 7])
+    assert out["pool_of"].tolist() == [1, 0, 1, -1, 0, -1, -1, 1, 0]
+    assert out["current"].tolist() == [3, 3, 0] and out["delta"].tolist() == [-2, -2, 4]
+    assert out["victim_off"].tolist() == [0, 2, 4, 4] and out["victim_vm"].tolist() == [1, 4, 0, 2]
+    assert out["member_vm"].tolist() == [1, 4, 8, 0, 2, 7]
+    assert out["create_ordinal"].tolist() == [0, 1, 2, 3]
+    # BASELINE.json config 1 as a batch of one pool: replicas 3 -> 5 -> 2 (K1, K2, K4)
+    one = lambda desired, ords: ctx.reconcile_batch([desired], [0], [0] * len(ords), [1] * len(ords), 1, ords)
+    k1 = one(3, [0, 1, 2])
+    assert (k1["delta"].tolist(), k1["ready"].tolist(), k1["victim_vm"].tolist()) == ([0], [3], [])
+    k2 = one(5, [0, 1, 2])
+    assert (k2["create_count"].tolist(), k2["create_ordinal"].tolist(), k2["ready"].tolist()) == ([2], [3, 4], [3])
+    k4 = one(2, [0, 1, 2, 3, 4])
+    assert (k4["delta"].tolist(), k4["victim_vm"].tolist(), k4["ready"].tolist()) == ([-3], [0, 1, 2], [5])
+
+
+def test_reconcile_errors_and_empty(ctx, capi):
+    with pytest.raises(capi.K8sGpuError) as e:
+        ctx.reconcile_batch([1, 1], [3, 3], [3], [1], 8)
+    assert e.value.code == capi.E_ARG
+    with pytest.raises(capi.K8sGpuError):
+        ctx.reconcile_batch([-1], [0], [0], [1], 8)
+    out = ctx.reconcile_batch([2, 0], [0, 1], [], [], 4)
+    assert out["delta"].tolist() == [2, 0] and out["victim_off"].tolist() == [0, 0, 0]
+    assert out["create_ordinal"].tolist() == [0, 1]
+    out = ctx.reconcile_batch([], [], [0, 1], [1, 1], 4)
+    assert out["pool_of"].tolist() == [-1, -1]
+    with pytest.raises(capi.K8sGpuError) as e:  # caller-sized buffer too small
+        ctx.reconcile_batch([5], [0], [], [], 1, create_capacity=1)
+    assert e.value.code == capi.E_CAPACITY
+
+
+def test_reconcile_random_small(ctx, orc):
+    rng = np.random.default_rng(7)
+    for _ in range(40):
+        P, V = int(rng.integers(1, 9)), int(rng.integers(0, 80))
+        desired = rng.integers(0, 12, P)
+        powner = rng.permutation(12)[:P].astype(np.uint32)
+        vowner = rng.integers(0, 14, V).astype(np.uint32)
+        vowner[rng.random(V) < 0.1] = NONE
+        vflags = (rng.random(V) < 0.85).astype(np.uint32)
+        ords = rng.integers(0, 16, V).astype(np.uint32)
+        ords[rng.random(V) < 0.1] = NONE
+        args = (desired, powner, vowner, vflags, 12, ords)
+        same_reconcile(ctx.reconcile_batch(*args), orc.reconcile_batch(*args))
