@@ -185,6 +185,27 @@ int k8sgpu_debug_sort_pairs(k8sgpu_ctx *ctx, const uint32_t *keys, const uint32_
                             uint32_t *out_keys, uint32_t *out_vals);
 int k8sgpu_debug_exclusive_scan(k8sgpu_ctx *ctx, const uint32_t *in, uint32_t n, uint32_t *out, uint32_t *total);
 
+/* Exclusive u32 prefix sum that allocates nothing.  This entry point has no counterpart in the
+ * reference.  It is for callers that may not allocate device memory once they are running: a
+ * controller that shares its GPU with the jobs it schedules and lives inside a memory slice
+ * fixed at start-up (a late cudaMalloc can fail there), and callers with GPU work in flight
+ * that a device-wide stall would hurt (cudaMalloc and cudaFree synchronise the device).
+ *
+ * d_in, d_out (n elements each) and d_total (one element, may be NULL) are DEVICE pointers the
+ * caller owns; d_out may equal d_in.  `stream` is a cudaStream_t (0 = the context's stream); the
+ * call only enqueues work and returns.  The block sums the scan needs live in a fixed 32 KiB
+ * array inside the library image on every GPU that loads it, which limits n to
+ * K8SGPU_SCAN_NOALLOC_MAX_N; a larger n returns K8SGPU_E_CAPACITY and launches nothing.
+ *
+ * The first call on each device also looks up the device address of that array, so make that
+ * first call before starting any stream capture.  All calls on a device share the one array
+ * and it keeps whatever the previous call wrote (the scan overwrites every slot before reading
+ * it, so no clearing is needed); two calls whose kernels may overlap on the GPU, e.g. on
+ * different streams, race on it and must be ordered by the caller. */
+#define K8SGPU_SCAN_NOALLOC_MAX_N (1u << 24)
+int k8sgpu_exclusive_scan_noalloc(k8sgpu_ctx *ctx, const uint32_t *d_in, uint32_t n, uint32_t *d_out,
+                                  uint32_t *d_total, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -24,8 +24,9 @@ EXPORTS = (
     "k8sgpu_reconcile_batch", "k8sgpu_reconcile_upload", "k8sgpu_reconcile_run", "k8sgpu_reconcile_download",
     "k8sgpu_place", "k8sgpu_place_upload", "k8sgpu_place_run", "k8sgpu_place_download", "k8sgpu_score_once",
     "k8sgpu_place_round_begin", "k8sgpu_place_round_score", "k8sgpu_place_round_admit", "k8sgpu_place_round_end",
-    "k8sgpu_debug_sort_pairs", "k8sgpu_debug_exclusive_scan",
+    "k8sgpu_debug_sort_pairs", "k8sgpu_debug_exclusive_scan", "k8sgpu_exclusive_scan_noalloc",
 )
+SCAN_NOALLOC_MAX_N = 1 << 24
 
 u32p = C.POINTER(C.c_uint32)
 i32p = C.POINTER(C.c_int32)
@@ -112,6 +113,7 @@ def load() -> C.CDLL:
         L.k8sgpu_place_round_end.argtypes = [vp, vp]
         L.k8sgpu_debug_sort_pairs.argtypes = [vp, u32p, u32p, C.c_uint32, C.c_int, u32p, u32p]
         L.k8sgpu_debug_exclusive_scan.argtypes = [vp, u32p, C.c_uint32, u32p, u32p]
+        L.k8sgpu_exclusive_scan_noalloc.argtypes = [vp, vp, C.c_uint32, vp, vp, vp]
         for name in EXPORTS:
             if name != "k8sgpu_last_error":
                 getattr(L, name).restype = C.c_int
@@ -322,3 +324,8 @@ class Context:
         tot = C.c_uint32()
         self._check(self._L.k8sgpu_debug_exclusive_scan(self._h, xp, len(x), out.ctypes.data_as(u32p), C.byref(tot)))
         return out, tot.value
+
+    def exclusive_scan_noalloc(self, d_in_ptr: int, n: int, d_out_ptr: int, d_total_ptr: int = 0, stream: int = 0):
+        """Device pointers in and out; enqueues on `stream` and returns (k8sgpu.h)."""
+        self._check(self._L.k8sgpu_exclusive_scan_noalloc(self._h, C.c_void_p(d_in_ptr), n, C.c_void_p(d_out_ptr),
+                                                          C.c_void_p(d_total_ptr), C.c_void_p(stream)))

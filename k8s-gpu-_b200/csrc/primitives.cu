@@ -4,6 +4,8 @@
 // "the first k VMs in list order") and of placement admission order: both
 // need "rank among earlier rows of the same bucket", i.e. a STABLE partition by bucket id.
 // No atomics decide any output position, so results do not depend on scheduling order.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace k8sgpu {
@@ -199,3 +201,73 @@ int sort_pairs(k8sgpu_ctx *ctx, cudaStream_t s, uint32_t *keys, uint32_t *vals, 
 }
 
 }  // namespace k8sgpu
+
+// ------------------------------------------------------------------ exclusive scan, no allocation
+//
+// Who this is for: a caller that must not allocate device memory while it works.  Two kinds
+// exist around this library.  One is a scheduler or controller process that shares its GPU with
+// the jobs it places and was given a fixed slice of device memory at start-up: a later
+// cudaMalloc may simply fail there.  The other is a caller in the middle of queued GPU work it
+// cannot afford to have stalled: cudaMalloc and cudaFree synchronise the whole device.
+//
+// The scan needs one word of scratch per 2048-element block (the block sums).  Here that scratch
+// is a fixed array in device global memory, part of the library image: every GPU that loads
+// libk8sgpu.so holds these 32 KiB until the process exits.  The size caps the input at
+// K8SGPU_SCAN_NOALLOC_MAX_N elements.
+namespace k8sgpu {
+
+constexpr uint32_t kNoAllocScanMaxN = K8SGPU_SCAN_NOALLOC_MAX_N;
+constexpr uint32_t kNoAllocScanBlocks = kNoAllocScanMaxN / kScanTile;  // 8192 block sums = 32 KiB
+static __device__ __align__(256) uint32_t g_noalloc_block_sums[kNoAllocScanBlocks];
+
+constexpr int kNoAllocMaxDevices = 64;
+// Device address of g_noalloc_block_sums on each GPU.  On the host the array's name is only a
+// handle for the runtime, not something a kernel can dereference, so the address is looked up
+// once per device (with that device current) and cached here.
+static uint32_t *g_noalloc_ptr[kNoAllocMaxDevices] = {};
+static std::mutex g_noalloc_mu;
+
+static int noalloc_scratch(k8sgpu_ctx *ctx, uint32_t **out) {
+    if (ctx->device < 0 || ctx->device >= kNoAllocMaxDevices)
+        return fail(ctx, K8SGPU_E_ARG, "scan_noalloc: device %d not supported (max %d)", ctx->device,
+                    kNoAllocMaxDevices - 1);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[ctx->device]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_block_sums);  // K8S_ENTER made ctx->device current
+        if (e != cudaSuccess || !p)
+            return fail(ctx, K8SGPU_E_CUDA, "scan_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        g_noalloc_ptr[ctx->device] = static_cast<uint32_t *>(p);
+    }
+    *out = g_noalloc_ptr[ctx->device];
+    return K8SGPU_OK;
+}
+
+}  // namespace k8sgpu
+
+extern "C" int k8sgpu_exclusive_scan_noalloc(k8sgpu_ctx *ctx, const uint32_t *d_in, uint32_t n, uint32_t *d_out,
+                                             uint32_t *d_total, void *stream) {
+    using namespace k8sgpu;
+    K8S_ENTER(ctx);
+    if (n > kNoAllocScanMaxN)
+        return fail(ctx, K8SGPU_E_CAPACITY,
+                    "scan_noalloc: n=%u exceeds the built-in scratch (at most %u elements); use the allocating "
+                    "entry points for larger inputs",
+                    n, kNoAllocScanMaxN);
+    if (n && (!d_in || !d_out)) return fail(ctx, K8SGPU_E_ARG, "scan_noalloc: NULL device buffer");
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    uint32_t *sums = nullptr;
+    int rc = noalloc_scratch(ctx, &sums);
+    if (rc) return rc;
+    if (n <= kScanTile) {  // one block, no scratch touched
+        K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanThreads, 0, s, d_in, d_out, n, d_total);
+        return K8SGPU_OK;
+    }
+    // Nothing in the scratch has to start at zero: the first kernel overwrites every block sum
+    // that the later two read, so whatever the previous call left behind is never seen.
+    const uint32_t nb = ceil_div(n, kScanTile);
+    K8S_LAUNCH(ctx, scan_reduce_kernel, nb, kScanThreads, 0, s, d_in, n, sums);
+    K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanThreads, 0, s, sums, sums, nb, d_total);
+    K8S_LAUNCH(ctx, scan_down_kernel, nb, kScanThreads, 0, s, d_in, d_out, n, sums);
+    return K8SGPU_OK;
+}
