@@ -24,7 +24,7 @@ struct __align__(16) NodeQ {  // what the inner loop reads; rebuilt from the fre
     uint32_t zone_bit;    // 1 << zone_id
     uint32_t taint;
     uint32_t khi;         // 1<<31 | (0x7FFF - free_gpu) << 16 | (255 - cap_gpu) << 8
-    uint32_t pad;
+    uint32_t zrot;        // (zone_id - 7) mod 32: rotates the pod's one-hot preferred zone onto bit 7
 };
 static_assert(sizeof(NodeQ) == 32, "node record is 32 B: the algorithmic bytes per eval");
 
@@ -89,13 +89,13 @@ __global__ void node_prep_kernel(const uint32_t *__restrict__ cols, const uint32
         q.zone_bit = 1u << (zone & 31u);
         q.taint = taint;
         q.khi = 0x80000000u | ((0x7FFFu - (fg & 0x7FFFu)) << 16) | ((255u - (cap & 255u)) << 8);
-        q.pad = 0;
+        q.zrot = (zone - 7u) & 31u;
     } else {  // padding up to a whole tile: never feasible
         q.free_gpu_s = 0xFFFFFFFFu;
         q.free_mcpu = q.free_mib = 0;
         q.sku_bit = q.zone_bit = q.taint = 0;
         q.khi = 0;
-        q.pad = 0;
+        q.zrot = 0;
     }
     nodeq[i] = q;
 }
@@ -130,11 +130,45 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
 
 // ------------------------------------------------------------------ scoring
 
+// One pod x one node: filter (a11), key (a12), running argmax.  Written as PTX so that the
+// feasibility clauses stay one predicate chain (mask test -> three resource compares -> key
+// compare) with no separate predicate-combine instruction: the loop is bound by the integer
+// ALU pipe, so every instruction removed here is throughput.
+//   a = {free_gpu or -1, free_mcpu, free_mib, sku_bit}   b = {zone_bit, taint, khi, zrot}
+//   key = khi | (rotr(pzb, zrot) & 0x80): bit 7 of the rotated one-hot preferred-zone word is
+//   set exactly when the node's zone is the preferred one (zrot = (zone_id - 7) mod 32).
+__device__ __forceinline__ void eval_pair(const uint4 &a, const uint4 &b, uint32_t rg, uint32_t rc, uint32_t rm,
+                                          uint32_t nsku, uint32_t nzone, uint32_t ntol, uint32_t pzb,
+                                          uint32_t &best, uint32_t &bestn, uint32_t idx) {
+    asm("{\n\t"
+        ".reg .pred pf;\n\t"
+        ".reg .b32 m, z, key;\n\t"
+        "and.b32 m, %2, %9;\n\t"
+        "lop3.b32 m, %6, %10, m, 0xEA;\n\t"
+        "lop3.b32 m, %7, %11, m, 0xEA;\n\t"
+        "setp.eq.u32 pf, m, 0;\n\t"
+        "setp.ge.and.u32 pf, %4, %14, pf;\n\t"
+        "setp.ge.and.u32 pf, %5, %15, pf;\n\t"
+        "setp.ge.and.s32 pf, %3, %13, pf;\n\t"
+        "shf.r.wrap.b32 z, %12, %12, %8;\n\t"
+        "lop3.b32 key, z, 0x80, %16, 0xEA;\n\t"
+        "setp.gt.and.u32 pf, key, %0, pf;\n\t"
+        "selp.u32 %0, key, %0, pf;\n\t"
+        "@pf mov.u32 %1, %17;\n\t"
+        "}"
+        : "+r"(best), "+r"(bestn)
+        : "r"(a.w), "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.x), "r"(b.y), "r"(b.w), "r"(nsku), "r"(nzone), "r"(ntol),
+          "r"(pzb), "r"(rg), "r"(rc), "r"(rm), "r"(b.z), "r"(idx));
+}
+
 // grid.x: pod tiles of 256*PPT active positions; grid.y: node splits (runs of whole tiles).
 // best_key[pos] = (key32 << 32) | (0xFFFFFFFF - ((n - rot) mod N)), 0 when no node is feasible.
 // key32 orders nodes exactly like the spec's upper key bits for a fixed pod (the pod's req_gpu
-// only shifts the 15-bit field by a constant), and its bit 0 says "n >= rot", which together
-// with the ascending scan reproduces the rotated-index tie-break without a modulo per eval.
+// only shifts the 15-bit field by a constant).  The rotated-index tie-break costs nothing per
+// eval: nodes are scanned in ascending n with a strict '>', so among equal keys the lowest n
+// wins; at the one point where the scan crosses n == rot(p) the running best is lowered by 1
+// (keys are even), which lets a later node with an EQUAL key take over -- exactly "nodes at or
+// after rot come first".  Only the 8-node chunk that contains rot takes the slow path.
 template <int PPT>
 __global__ void __launch_bounds__(256) score_kernel(const NodeQ *__restrict__ nodeq, uint32_t n_tiles,
                                                     uint32_t tiles_per_split, const PodQ *__restrict__ podq,
@@ -185,21 +219,35 @@ __global__ void __launch_bounds__(256) score_kernel(const NodeQ *__restrict__ no
         for (uint32_t spins = 0; !mbar_try_wait(&bar[buf], (it >> 1) & 1u);)
             if (++spins > (1u << 26)) __trap();  // a lost TMA completion must fail loudly, not hang the GPU
         const uint32_t nbase = t * kNodeTile;
-        int rrel[PPT];
+        uint32_t rrel[PPT];  // rot - nbase: the scan crosses rot inside this tile iff rrel < 256
 #pragma unroll
-        for (int j = 0; j < PPT; ++j) rrel[j] = (int)(rot[j] - nbase);  // node k has n >= rot  <=>  k >= rrel
+        for (int j = 0; j < PPT; ++j) rrel[j] = rot[j] - nbase;
         const uint4 *tl = tile[buf];
-#pragma unroll 8
-        for (int k = 0; k < (int)kNodeTile; ++k) {
-            const uint4 a = tl[2 * k], b = tl[2 * k + 1];
+#pragma unroll 1
+        for (uint32_t kb = 0; kb < kNodeTile; kb += 8) {
+            bool crossing = false;
 #pragma unroll
-            for (int j = 0; j < PPT; ++j) {
-                const bool feas = ((int)a.x >= (int)rg[j]) & (a.y >= rc[j]) & (a.z >= rm[j]) &
-                                  (((a.w & nsku[j]) | (b.x & nzone[j]) | (b.y & ntol[j])) == 0u);
-                uint32_t key = b.z | ((b.x & pzb[j]) ? 0x80u : 0u) | (k >= rrel[j] ? 1u : 0u);
-                if (feas && key > best[j]) {
-                    best[j] = key;
-                    bestn[j] = nbase + k;
+            for (int j = 0; j < PPT; ++j) crossing |= (rrel[j] - kb) < 8u;
+            const uint32_t idx0 = nbase + kb;
+            if (!crossing) {
+#pragma unroll
+                for (uint32_t i = 0; i < 8; ++i) {
+                    const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];
+#pragma unroll
+                    for (int j = 0; j < PPT; ++j)
+                        eval_pair(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j], bestn[j],
+                                  idx0 + i);
+                }
+            } else {  // rare: rot(p) falls inside this chunk for some pod of this thread
+#pragma unroll 1
+                for (uint32_t i = 0; i < 8; ++i) {
+                    const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];
+#pragma unroll
+                    for (int j = 0; j < PPT; ++j) {
+                        if (rrel[j] == kb + i && best[j] != 0u) best[j] -= 1u;  // entering n >= rot
+                        eval_pair(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j], bestn[j],
+                                  idx0 + i);
+                    }
                 }
             }
         }
@@ -211,8 +259,9 @@ __global__ void __launch_bounds__(256) score_kernel(const NodeQ *__restrict__ no
         if (pos[j] >= hi) continue;
         unsigned long long key64 = 0ull;
         if (best[j] != 0u) {
+            uint32_t key32 = (best[j] + 1u) & ~1u;  // undo the crossing decrement
             uint32_t ridx = bestn[j] >= rot[j] ? bestn[j] - rot[j] : bestn[j] + (n_nodes - rot[j]);
-            key64 = ((unsigned long long)best[j] << 32) | (unsigned long long)(0xFFFFFFFFu - ridx);
+            key64 = ((unsigned long long)key32 << 32) | (unsigned long long)(0xFFFFFFFFu - ridx);
         }
         if (use_atomic) {
             if (key64) atomicMax(&best_key[pos[j]], key64);
@@ -492,10 +541,18 @@ static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_bes
     const uint32_t cnt = hi - lo;
     if (cnt == 0) return K8SGPU_OK;
     const uint32_t n_tiles = st.n_pad / kNodeTile;
-    int ppt = cnt >= 256u * 2u * 4u * (uint32_t)ctx->sm_count ? 2 : 1;
+    // Grid shape.  The kernel is ALU bound, so what matters is an even spread over the 148 SMs:
+    // aim for ~20 CTAs per SM (the hardware scheduler then balances to a few percent) while each
+    // CTA still scans at least two node tiles.  Two pods per thread halves the shared-memory
+    // reads per eval; use it whenever that still leaves >= 8 CTAs per SM.
+    const uint32_t sms = (uint32_t)ctx->sm_count;
+    int ppt = (uint64_t)ceil_div(cnt, 512u) * n_tiles >= 8ull * sms ? 2 : 1;
     if (const char *e = getenv("K8SGPU_PPT")) ppt = atoi(e) >= 2 ? 2 : 1;
     const uint32_t xb = ceil_div(cnt, 256u * ppt);
-    uint32_t splits = ceil_div(4u * (uint32_t)ctx->sm_count, xb);
+    uint32_t splits = ceil_div(20u * sms, xb);
+    if (splits > n_tiles) splits = n_tiles;
+    if (splits > 1 && n_tiles / splits < 2 && (uint64_t)xb * ceil_div(n_tiles, 2u) >= 8ull * sms)
+        splits = ceil_div(n_tiles, 2u);
     if (const char *e = getenv("K8SGPU_SPLITS")) splits = (uint32_t)atoi(e);
     if (splits < 1) splits = 1;
     if (splits > n_tiles) splits = n_tiles;

@@ -21,33 +21,52 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t x, int lane) {
     return x;
 }
 
-// Scans one tile of kScanTile elements, 256 threads, rows of 256 (coalesced).
-// carry_in is added to every output.  Returns the tile total in *tile_total (thread 0).
+// Scans one tile of kScanTile elements with 256 threads: each thread owns 8 consecutive
+// elements (two 128-bit loads when the tile is whole and 16-byte aligned), scans them in
+// registers, and one warp-shuffle + shared-memory step combines the 256 thread totals.
+// carry_in is added to every output.  Returns carry_in + the tile total (all threads).
 __device__ __forceinline__ uint32_t block_scan_tile(const uint32_t *in, uint32_t *out,  // may alias (in place)
                                                     uint32_t base, uint32_t n, uint32_t carry_in, bool write) {
     __shared__ uint32_t warp_tot[8];
-    __shared__ uint32_t row_carry;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) row_carry = carry_in;
-    __syncthreads();
-#pragma unroll 1
-    for (uint32_t r = 0; r < kScanTile / kScanThreads; ++r) {
-        uint32_t i = base + r * kScanThreads + tid;
-        uint32_t x = (i < n) ? in[i] : 0u;
-        uint32_t inc = warp_incl_scan(x, lane);
-        if (lane == 31) warp_tot[warp] = inc;
-        __syncthreads();
-        uint32_t woff = 0;
+    const uint32_t i0 = base + (uint32_t)tid * 8u;
+    const bool vec = base + kScanTile <= n &&
+                     (((uintptr_t)in | (write ? (uintptr_t)out : (uintptr_t)0)) & 15u) == 0;
+    uint32_t x[8];
+    if (vec) {
+        const uint4 a = *reinterpret_cast<const uint4 *>(in + i0);
+        const uint4 b = *reinterpret_cast<const uint4 *>(in + i0 + 4);
+        x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
+        x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
+    } else {
 #pragma unroll
-        for (int w = 0; w < 8; ++w)
-            if (w < warp) woff += warp_tot[w];
-        uint32_t carry = row_carry;
-        if (write && i < n) out[i] = carry + woff + inc - x;
-        __syncthreads();
-        if (tid == kScanThreads - 1) row_carry = carry + woff + inc;
-        __syncthreads();
+        for (int k = 0; k < 8; ++k) x[k] = (i0 + k < n) ? in[i0 + k] : 0u;
     }
-    return row_carry;
+#pragma unroll
+    for (int k = 1; k < 8; ++k) x[k] += x[k - 1];
+    const uint32_t inc = warp_incl_scan(x[7], lane);
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    uint32_t woff = 0, all = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+        const uint32_t t = warp_tot[w];
+        if (w < warp) woff += t;
+        all += t;
+    }
+    if (write) {
+        const uint32_t e = carry_in + woff + inc - x[7];  // exclusive prefix of this thread's first element
+        if (vec) {
+            *reinterpret_cast<uint4 *>(out + i0) = make_uint4(e, e + x[0], e + x[1], e + x[2]);
+            *reinterpret_cast<uint4 *>(out + i0 + 4) = make_uint4(e + x[3], e + x[4], e + x[5], e + x[6]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                if (i0 + k < n) out[i0 + k] = e + (k ? x[k - 1] : 0u);
+        }
+    }
+    __syncthreads();  // warp_tot is reused by the next tile
+    return carry_in + all;
 }
 
 __global__ void __launch_bounds__(kScanThreads) scan_reduce_kernel(const uint32_t *__restrict__ in, uint32_t n,

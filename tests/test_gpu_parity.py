@@ -91,6 +91,24 @@ def test_score_once_identical_ties(ctx, orc, synth):
     assert np.array_equal(ctx.score_once(1), np.zeros(2000, np.int32))
 
 
+@pytest.mark.parametrize("n", [1, 7, 8, 9, 255, 256, 257, 511, 513, 1031])
+@pytest.mark.parametrize("splits", [None, "1", "5"])
+def test_rotation_tiebreak_at_chunk_and_tile_edges(ctx, orc, synth, n, splits, monkeypatch):
+    # identical nodes: only rot(p) decides, and rot(p) lands on every chunk/tile boundary case
+    if splits:
+        monkeypatch.setenv("K8SGPU_SPLITS", splits)
+    nodes, pods = synth.gen_identical(n, 700)
+    ctx.place_upload(nodes, pods)
+    free = (nodes["free_gpu"], nodes["free_mcpu"], nodes["free_mib"])
+    want = orc.score_round(nodes, free, pods, np.arange(700, dtype=np.uint32), flags=0)
+    assert np.array_equal(ctx.score_once(0), want)
+    # and with only every third node feasible (equal keys separated by infeasible nodes)
+    nodes["flags"] = (np.arange(n) % 3 == 0).astype(np.uint32)
+    ctx.place_upload(nodes, pods)
+    want = orc.score_round(nodes, free, pods, np.arange(700, dtype=np.uint32), flags=0)
+    assert np.array_equal(ctx.score_once(0), want)
+
+
 # ------------------------------------------------------------------ whole placement
 @pytest.mark.parametrize("name", list(mg.PLACE_CASES) + list(mg.TIES_CASES))
 def test_place_matches_golden_and_oracle(ctx, orc, name):
