@@ -33,6 +33,9 @@ extern "C" {
 #define K8SGPU_ASSIGN_NONE (-1)    /* pod has no feasible node                       */
 #define K8SGPU_ASSIGN_PENDING (-2) /* pod still proposing when max_rounds was reached */
 #define K8SGPU_POLICY_ROT_ZERO 1u  /* rot(p) = 0: plain lowest-index tie-break        */
+/* `stream` arguments are cudaStream_t values.  0 keeps its CUDA meaning (the legacy default
+ * stream); this sentinel selects the context's own internal non-blocking stream instead. */
+#define K8SGPU_STREAM_OWN ((void *)(uintptr_t)-1)
 
 typedef struct k8sgpu_ctx k8sgpu_ctx;
 
@@ -166,7 +169,9 @@ int k8sgpu_score_once(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, int32_t *bes
  * uploads the same tables, scores its own slice [lo,hi) of the active list into a DEVICE
  * buffer, the caller exchanges the slices (all-gather), and every process then runs the
  * admission step on the full proposal list, which keeps all replicas identical.
- * `stream` is a cudaStream_t (0 = the context's own stream).
+ * `stream` is a cudaStream_t, with CUDA's usual meaning of 0 (the legacy default stream, which is
+ * what torch.cuda.current_stream().cuda_stream is unless a side stream was entered);
+ * K8SGPU_STREAM_OWN selects the context's internal stream.
  *   begin : reset state from the uploaded tables; *n_active = m
  *   score : d_best[i - lo] = best node of active[i], lo <= i < hi        (asynchronous)
  *   admit : d_best_all[i] for 0 <= i < n_active; returns the next active count (synchronises)
@@ -192,7 +197,7 @@ int k8sgpu_debug_exclusive_scan(k8sgpu_ctx *ctx, const uint32_t *in, uint32_t n,
  * that a device-wide stall would hurt (cudaMalloc and cudaFree synchronise the device).
  *
  * d_in, d_out (n elements each) and d_total (one element, may be NULL) are DEVICE pointers the
- * caller owns; d_out may equal d_in.  `stream` is a cudaStream_t (0 = the context's stream); the
+ * caller owns; d_out may equal d_in.  `stream` is a cudaStream_t (0 = legacy default stream, K8SGPU_STREAM_OWN = the context's); the
  * call only enqueues work and returns.  The block sums the scan needs live in a fixed 32 KiB
  * array inside the library image on every GPU that loads it, which limits n to
  * K8SGPU_SCAN_NOALLOC_MAX_N; a larger n returns K8SGPU_E_CAPACITY and launches nothing.

@@ -150,6 +150,12 @@ inline void reset_call_stats(k8sgpu_ctx *ctx) {
     ctx->stats.d2h_bytes = 0;
 }
 
+// Stream arguments of the C-ABI: a cudaStream_t as is (0 = legacy default stream), or
+// K8SGPU_STREAM_OWN for the context's internal stream.
+inline cudaStream_t pick_stream(const k8sgpu_ctx *ctx, void *stream) {
+    return stream == K8SGPU_STREAM_OWN ? ctx->stream : (cudaStream_t)stream;
+}
+
 inline uint32_t ceil_div(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
 inline int key_bits(uint32_t max_key) {  // bits needed to hold values 0..max_key
     int b = 1;

@@ -23,7 +23,7 @@ struct __align__(16) NodeQ {  // what the inner loop reads; rebuilt from the fre
     uint32_t sku_bit;     // 1 << sku_id
     uint32_t zone_bit;    // 1 << zone_id
     uint32_t taint;
-    uint32_t khi;         // 1<<31 | (0x7FFF - free_gpu) << 16 | (255 - cap_gpu) << 8
+    uint32_t khi;         // 1<<31 | (0x7FFF - free_gpu) << 16 | (255 - cap_gpu) << 8 | (63 - n % 64) << 1
     uint32_t zrot;        // (zone_id - 7) mod 32: rotates the pod's one-hot preferred zone onto bit 7
 };
 static_assert(sizeof(NodeQ) == 32, "node record is 32 B: the algorithmic bytes per eval");
@@ -36,7 +36,7 @@ struct __align__(16) PodQ {
 };
 static_assert(sizeof(PodQ) == 32, "pod record is 32 B");
 
-constexpr uint32_t kErrNode = 1u, kErrPod = 2u;
+constexpr uint32_t kErrNode = 1u, kErrPod = 2u, kErrProposal = 4u;
 
 __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -88,7 +88,8 @@ __global__ void node_prep_kernel(const uint32_t *__restrict__ cols, const uint32
         q.sku_bit = 1u << (sku & 31u);
         q.zone_bit = 1u << (zone & 31u);
         q.taint = taint;
-        q.khi = 0x80000000u | ((0x7FFFu - (fg & 0x7FFFu)) << 16) | ((255u - (cap & 255u)) << 8);
+        q.khi = 0x80000000u | ((0x7FFFu - (fg & 0x7FFFu)) << 16) | ((255u - (cap & 255u)) << 8) |
+                ((63u - (i & 63u)) << 1);
         q.zrot = (zone - 7u) & 31u;
     } else {  // padding up to a whole tile: never feasible
         q.free_gpu_s = 0xFFFFFFFFu;
@@ -130,51 +131,84 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
 
 // ------------------------------------------------------------------ scoring
 
-// One pod x one node: filter (a11), key (a12), running argmax.  Written as PTX so that the
-// feasibility clauses stay one predicate chain (mask test -> three resource compares -> key
-// compare) with no separate predicate-combine instruction: the loop is bound by the integer
-// ALU pipe, so every instruction removed here is throughput.
+// One pod x one node: filter (a11), key (a12), running max.  Written as PTX so that the
+// feasibility clauses stay one predicate chain with no separate predicate-combine instruction:
+// the loop is bound by the integer ALU pipe (ncu: >90 % busy), so every ALU instruction removed
+// here is throughput.
 //   a = {free_gpu or -1, free_mcpu, free_mib, sku_bit}   b = {zone_bit, taint, khi, zrot}
 //   key = khi | (rotr(pzb, zrot) & 0x80): bit 7 of the rotated one-hot preferred-zone word is
 //   set exactly when the node's zone is the preferred one (zrot = (zone_id - 7) mod 32).
+//   khi carries 63 - (n mod 64) in bits 1..6, so inside a 64-node group the lowest n wins ties
+//   and no node index has to be tracked per eval.
+// RES = 0: three chained integer compares (ALU pipe).
+// RES = 1: three differences on the FMA pipe (mad by a runtime -1), OR-ed; the sign bit of the
+//          OR says "some resource is short".  One ALU instruction fewer per eval.
+template <int RES>
 __device__ __forceinline__ void eval_pair(const uint4 &a, const uint4 &b, uint32_t rg, uint32_t rc, uint32_t rm,
                                           uint32_t nsku, uint32_t nzone, uint32_t ntol, uint32_t pzb,
-                                          uint32_t &best, uint32_t &bestn, uint32_t idx) {
-    asm("{\n\t"
-        ".reg .pred pf;\n\t"
-        ".reg .b32 m, z, key;\n\t"
-        "and.b32 m, %2, %9;\n\t"
-        "lop3.b32 m, %6, %10, m, 0xEA;\n\t"
-        "lop3.b32 m, %7, %11, m, 0xEA;\n\t"
-        "setp.eq.u32 pf, m, 0;\n\t"
-        "setp.ge.and.u32 pf, %4, %14, pf;\n\t"
-        "setp.ge.and.u32 pf, %5, %15, pf;\n\t"
-        "setp.ge.and.s32 pf, %3, %13, pf;\n\t"
-        "shf.r.wrap.b32 z, %12, %12, %8;\n\t"
-        "lop3.b32 key, z, 0x80, %16, 0xEA;\n\t"
-        "setp.gt.and.u32 pf, key, %0, pf;\n\t"
-        "selp.u32 %0, key, %0, pf;\n\t"
-        "@pf mov.u32 %1, %17;\n\t"
-        "}"
-        : "+r"(best), "+r"(bestn)
-        : "r"(a.w), "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.x), "r"(b.y), "r"(b.w), "r"(nsku), "r"(nzone), "r"(ntol),
-          "r"(pzb), "r"(rg), "r"(rc), "r"(rm), "r"(b.z), "r"(idx));
+                                          uint32_t &best, uint32_t negone) {
+    if (RES == 0) {
+        asm("{\n\t"
+            ".reg .pred pf;\n\t"
+            ".reg .b32 m, z, key;\n\t"
+            "and.b32 m, %1, %8;\n\t"
+            "lop3.b32 m, %5, %9, m, 0xEA;\n\t"
+            "lop3.b32 m, %6, %10, m, 0xEA;\n\t"
+            "setp.eq.u32 pf, m, 0;\n\t"
+            "setp.ge.and.u32 pf, %3, %13, pf;\n\t"
+            "setp.ge.and.u32 pf, %4, %14, pf;\n\t"
+            "setp.ge.and.s32 pf, %2, %12, pf;\n\t"
+            "shf.r.wrap.b32 z, %11, %11, %7;\n\t"
+            "lop3.b32 key, z, 0x80, %15, 0xEA;\n\t"
+            "setp.gt.and.u32 pf, key, %0, pf;\n\t"
+            "selp.u32 %0, key, %0, pf;\n\t"
+            "}"
+            : "+r"(best)
+            : "r"(a.w), "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.x), "r"(b.y), "r"(b.w), "r"(nsku), "r"(nzone),
+              "r"(ntol), "r"(pzb), "r"(rg), "r"(rc), "r"(rm), "r"(b.z));
+    } else {
+        asm("{\n\t"
+            ".reg .pred pf;\n\t"
+            ".reg .b32 m, z, key, d1, d2, d3;\n\t"
+            "and.b32 m, %1, %8;\n\t"
+            "lop3.b32 m, %5, %9, m, 0xEA;\n\t"
+            "lop3.b32 m, %6, %10, m, 0xEA;\n\t"
+            "mad.lo.s32 d1, %12, %16, %2;\n\t"
+            "mad.lo.s32 d2, %13, %16, %3;\n\t"
+            "mad.lo.s32 d3, %14, %16, %4;\n\t"
+            "setp.eq.u32 pf, m, 0;\n\t"
+            "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t"
+            "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
+            "shf.r.wrap.b32 z, %11, %11, %7;\n\t"
+            "lop3.b32 key, z, 0x80, %15, 0xEA;\n\t"
+            "setp.gt.and.u32 pf, key, %0, pf;\n\t"
+            "selp.u32 %0, key, %0, pf;\n\t"
+            "}"
+            : "+r"(best)
+            : "r"(a.w), "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.x), "r"(b.y), "r"(b.w), "r"(nsku), "r"(nzone),
+              "r"(ntol), "r"(pzb), "r"(rg), "r"(rc), "r"(rm), "r"(b.z), "r"(negone));
+    }
 }
+
+constexpr uint32_t kGroup = 64;        // nodes per index group (index bits 1..6 of the key)
+constexpr uint32_t kIdxMask = 0x7Eu;   // those bits
 
 // grid.x: pod tiles of 256*PPT active positions; grid.y: node splits (runs of whole tiles).
 // best_key[pos] = (key32 << 32) | (0xFFFFFFFF - ((n - rot) mod N)), 0 when no node is feasible.
 // key32 orders nodes exactly like the spec's upper key bits for a fixed pod (the pod's req_gpu
 // only shifts the 15-bit field by a constant).  The rotated-index tie-break costs nothing per
 // eval: nodes are scanned in ascending n with a strict '>', so among equal keys the lowest n
-// wins; at the one point where the scan crosses n == rot(p) the running best is lowered by 1
-// (keys are even), which lets a later node with an EQUAL key take over -- exactly "nodes at or
-// after rot come first".  Only the 8-node chunk that contains rot takes the slow path.
-template <int PPT>
+// wins; after each 64-node group the index bits of the running best are saturated, so a later
+// group needs a strictly larger key; and at the one point where the scan crosses n == rot(p)
+// the running best is lowered to just below its own key, which lets a later node with an EQUAL
+// key take over -- exactly "nodes at or after rot come first".  Only the 8-node chunk that
+// contains rot takes the slow path.
+template <int PPT, int RES>
 __global__ void __launch_bounds__(256) score_kernel(const NodeQ *__restrict__ nodeq, uint32_t n_tiles,
                                                     uint32_t tiles_per_split, const PodQ *__restrict__ podq,
                                                     const uint32_t *__restrict__ active, uint32_t lo, uint32_t hi,
                                                     unsigned long long *__restrict__ best_key, uint32_t n_nodes,
-                                                    int use_atomic) {
+                                                    int use_atomic, uint32_t negone) {
     __shared__ __align__(128) uint4 tile[2][kNodeTile * 2];
     __shared__ __align__(8) uint64_t bar[2];
     const int tid = threadIdx.x;
@@ -224,32 +258,67 @@ __global__ void __launch_bounds__(256) score_kernel(const NodeQ *__restrict__ no
         for (int j = 0; j < PPT; ++j) rrel[j] = rot[j] - nbase;
         const uint4 *tl = tile[buf];
 #pragma unroll 1
-        for (uint32_t kb = 0; kb < kNodeTile; kb += 8) {
-            bool crossing = false;
+        for (uint32_t g = 0; g < kNodeTile; g += kGroup) {
+            uint32_t prev[PPT];
 #pragma unroll
-            for (int j = 0; j < PPT; ++j) crossing |= (rrel[j] - kb) < 8u;
-            const uint32_t idx0 = nbase + kb;
-            if (!crossing) {
+            for (int j = 0; j < PPT; ++j) prev[j] = best[j];
+            // Does rot(p) of ANY pod of this warp fall inside this 64-node group?  The vote keeps the
+            // choice warp-uniform, so the two code paths never both run for one warp.
+            bool gx = false;
 #pragma unroll
-                for (uint32_t i = 0; i < 8; ++i) {
-                    const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];
-#pragma unroll
-                    for (int j = 0; j < PPT; ++j)
-                        eval_pair(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j], bestn[j],
-                                  idx0 + i);
-                }
-            } else {  // rare: rot(p) falls inside this chunk for some pod of this thread
+            for (int j = 0; j < PPT; ++j) gx |= (rrel[j] - g) < kGroup;
+            if (!__any_sync(0xFFFFFFFFu, gx)) {  // common case: 64 evals per pod, no checks at all
 #pragma unroll 1
-                for (uint32_t i = 0; i < 8; ++i) {
-                    const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];
+                for (uint32_t kb = g; kb < g + kGroup; kb += 16) {
 #pragma unroll
-                    for (int j = 0; j < PPT; ++j) {
-                        if (rrel[j] == kb + i && best[j] != 0u) best[j] -= 1u;  // entering n >= rot
-                        eval_pair(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j], bestn[j],
-                                  idx0 + i);
+                    for (uint32_t i = 0; i < 16; ++i) {
+                        const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];
+#pragma unroll
+                        for (int j = 0; j < PPT; ++j)
+                            eval_pair<RES>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j],
+                                           negone);
+                    }
+                }
+            } else {
+#pragma unroll 1
+                for (uint32_t kb = g; kb < g + kGroup; kb += 8) {
+                    bool cx = false;
+#pragma unroll
+                    for (int j = 0; j < PPT; ++j) cx |= (rrel[j] - kb) < 8u;
+                    if (!__any_sync(0xFFFFFFFFu, cx)) {
+#pragma unroll
+                        for (uint32_t i = 0; i < 8; ++i) {
+                            const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];
+#pragma unroll
+                            for (int j = 0; j < PPT; ++j)
+                                eval_pair<RES>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j],
+                                               best[j], negone);
+                        }
+                    } else {  // rare: rot(p) of some pod of this warp falls inside this 8-node chunk
+#pragma unroll 1
+                        for (uint32_t i = 0; i < 8; ++i) {
+                            const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];
+#pragma unroll
+                            for (int j = 0; j < PPT; ++j) {
+                                if (rrel[j] == kb + i) {  // entering n >= rot: bank the winner so far, lower it
+                                    if (best[j] != prev[j])
+                                        bestn[j] = nbase + g + (kGroup - 1u) - ((best[j] & kIdxMask) >> 1);
+                                    if (best[j] != 0u) best[j] = (best[j] & ~(kIdxMask | 1u)) - 1u;
+                                    prev[j] = best[j];
+                                }
+                                eval_pair<RES>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j],
+                                               best[j], negone);
+                            }
+                        }
                     }
                 }
             }
+#pragma unroll
+            for (int j = 0; j < PPT; ++j)
+                if (best[j] != prev[j]) {  // a node of this group took the lead: decode it, saturate the index bits
+                    bestn[j] = nbase + g + (kGroup - 1u) - ((best[j] & kIdxMask) >> 1);
+                    best[j] |= kIdxMask;
+                }
         }
         __syncthreads();  // everyone is done with tile[buf] before it is refilled
     }
@@ -259,7 +328,8 @@ __global__ void __launch_bounds__(256) score_kernel(const NodeQ *__restrict__ no
         if (pos[j] >= hi) continue;
         unsigned long long key64 = 0ull;
         if (best[j] != 0u) {
-            uint32_t key32 = (best[j] + 1u) & ~1u;  // undo the crossing decrement
+            // strip the index bits and undo a crossing decrement: the spec's upper key bits
+            uint32_t key32 = (best[j] + 1u) & ~(kIdxMask | 1u);
             uint32_t ridx = bestn[j] >= rot[j] ? bestn[j] - rot[j] : bestn[j] + (n_nodes - rot[j]);
             key64 = ((unsigned long long)key32 << 32) | (unsigned long long)(0xFFFFFFFFu - ridx);
         }
@@ -291,10 +361,15 @@ __global__ void score_finalize_kernel(const unsigned long long *__restrict__ bes
 
 __global__ void admit_keys_kernel(const int32_t *__restrict__ best, const uint32_t *__restrict__ active,
                                   uint32_t na, uint32_t n_nodes, int32_t *__restrict__ assign,
-                                  uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+                                  uint32_t *__restrict__ keys, uint32_t *__restrict__ vals,
+                                  uint32_t *__restrict__ err) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= na) return;
     int32_t b = best[i];
+    if (b < -1 || b >= (int32_t)n_nodes) {  // not something score_kernel can produce: a stale or
+        atomicOr(err, kErrProposal);        // unsynchronised proposal buffer was handed in
+        b = -1;
+    }
     if (b < 0) assign[active[i]] = K8SGPU_ASSIGN_NONE;  // no feasible node: final
     keys[i] = b < 0 ? n_nodes : (uint32_t)b;           // non-proposers sort behind every node
     vals[i] = i;
@@ -543,10 +618,11 @@ static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_bes
     const uint32_t n_tiles = st.n_pad / kNodeTile;
     // Grid shape.  The kernel is ALU bound, so what matters is an even spread over the 148 SMs:
     // aim for ~20 CTAs per SM (the hardware scheduler then balances to a few percent) while each
-    // CTA still scans at least two node tiles.  Two pods per thread halves the shared-memory
-    // reads per eval; use it whenever that still leaves >= 8 CTAs per SM.
+    // CTA still scans at least two node tiles.
     const uint32_t sms = (uint32_t)ctx->sm_count;
-    int ppt = (uint64_t)ceil_div(cnt, 512u) * n_tiles >= 8ull * sms ? 2 : 1;
+    // One pod per thread: measured fastest on config 3 with the FMA-pipe resource test (two pods
+    // per thread halve the shared-memory reads but cost registers; profiles/r01_sweep_*.txt).
+    int ppt = 1;
     if (const char *e = getenv("K8SGPU_PPT")) ppt = atoi(e) >= 2 ? 2 : 1;
     const uint32_t xb = ceil_div(cnt, 256u * ppt);
     uint32_t splits = ceil_div(20u * sms, xb);
@@ -569,12 +645,16 @@ static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_bes
     const bool timed = st.timed < kMaxTimedRounds;
     if (timed) K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed], s));
     dim3 grid(xb, splits);
-    if (ppt == 2)
-        K8S_LAUNCH(ctx, score_kernel<2>, grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(),
-                   st.active[st.cur].as<uint32_t>(), lo, hi, bk, st.n, use_atomic);
-    else
-        K8S_LAUNCH(ctx, score_kernel<1>, grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(),
-                   st.active[st.cur].as<uint32_t>(), lo, hi, bk, st.n, use_atomic);
+    int res = 1;  // resource test on the FMA pipe (see eval_pair)
+    if (const char *e = getenv("K8SGPU_RES")) res = atoi(e) ? 1 : 0;
+#define K8S_SCORE(P, R)                                                                                         \
+    K8S_LAUNCH(ctx, (score_kernel<P, R>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
+               st.active[st.cur].as<uint32_t>(), lo, hi, bk, st.n, use_atomic, 0xFFFFFFFFu)
+    if (ppt == 2 && res) K8S_SCORE(2, 1);
+    else if (ppt == 2) K8S_SCORE(2, 0);
+    else if (res) K8S_SCORE(1, 1);
+    else K8S_SCORE(1, 0);
+#undef K8S_SCORE
     if (timed) {
         K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed + 1], s));
         st.timed++;
@@ -596,7 +676,8 @@ static int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t 
         uint32_t *active = st.active[st.cur].as<uint32_t>(), *next = st.active[st.cur ^ 1].as<uint32_t>();
         uint32_t *flags = st.flags.as<uint32_t>(), *offs = flags + st.m;
         const uint32_t g = ceil_div(na, 256);
-        K8S_LAUNCH(ctx, admit_keys_kernel, g, 256, 0, s, d_best_all, active, na, st.n, st.assign.as<int32_t>(), keys, vals);
+        K8S_LAUNCH(ctx, admit_keys_kernel, g, 256, 0, s, d_best_all, active, na, st.n, st.assign.as<int32_t>(), keys, vals,
+                   cnts);
         int rc = sort_pairs(ctx, s, keys, vals, na, key_bits(st.n), st.sort);
         if (rc) return rc;
         const uint32_t nb = ceil_div(na, kSegThreads);
@@ -616,9 +697,15 @@ static int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t 
     }
     K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, cnts, 8, cudaMemcpyDeviceToHost, s));
     K8S_CUDA(ctx, cudaStreamSynchronize(s));
+    if (ctx->h_pinned[0] & kErrProposal)
+        return fail(ctx, K8SGPU_E_ARG, "place: proposal buffer holds values outside [-1, n): was it written on "
+                                       "another stream than the one passed here?");
     if (ctx->h_pinned[0] != 0u)
         return fail(ctx, K8SGPU_E_ARG, "place: %s table outside the input domain (see k8sgpu.h)",
                     (ctx->h_pinned[0] & kErrNode) ? "node" : "pod");
+    if (na && ctx->h_pinned[1] >= na)  // every round with active pods settles at least one of them
+        return fail(ctx, K8SGPU_E_ARG, "place: round %u made no progress (%u pods still active): proposals are "
+                                       "inconsistent with the tables", st.rounds, na);
     st.evals += (uint64_t)na * st.n;
     st.rounds++;
     st.cur ^= 1;
@@ -756,7 +843,7 @@ extern "C" int k8sgpu_place_round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *po
                                         uint32_t *n_active) {
     K8S_ENTER(ctx);
     reset_call_stats(ctx);
-    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    cudaStream_t s = ::k8sgpu::pick_stream(ctx, stream);
     int rc = round_begin(ctx, policy, s);
     if (rc) return rc;
     if (n_active) *n_active = ctx->place.n_active;
@@ -766,17 +853,17 @@ extern "C" int k8sgpu_place_round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *po
 extern "C" int k8sgpu_place_round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, void *stream) {
     K8S_ENTER(ctx);
     if (!d_best && hi > lo) return fail(ctx, K8SGPU_E_ARG, "round_score: NULL device buffer");
-    return round_score(ctx, lo, hi, d_best, stream ? (cudaStream_t)stream : ctx->stream);
+    return round_score(ctx, lo, hi, d_best, ::k8sgpu::pick_stream(ctx, stream));
 }
 
 extern "C" int k8sgpu_place_round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, void *stream,
                                         uint32_t *n_active) {
     K8S_ENTER(ctx);
     if (!d_best_all && ctx->place.n_active) return fail(ctx, K8SGPU_E_ARG, "round_admit: NULL device buffer");
-    return round_admit(ctx, d_best_all, stream ? (cudaStream_t)stream : ctx->stream, n_active);
+    return round_admit(ctx, d_best_all, ::k8sgpu::pick_stream(ctx, stream), n_active);
 }
 
 extern "C" int k8sgpu_place_round_end(k8sgpu_ctx *ctx, void *stream) {
     K8S_ENTER(ctx);
-    return round_end(ctx, stream ? (cudaStream_t)stream : ctx->stream);
+    return round_end(ctx, ::k8sgpu::pick_stream(ctx, stream));
 }

@@ -274,7 +274,7 @@ extern "C" int k8sgpu_exclusive_scan_noalloc(k8sgpu_ctx *ctx, const uint32_t *d_
                     "entry points for larger inputs",
                     n, kNoAllocScanMaxN);
     if (n && (!d_in || !d_out)) return fail(ctx, K8SGPU_E_ARG, "scan_noalloc: NULL device buffer");
-    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    cudaStream_t s = ::k8sgpu::pick_stream(ctx, stream);
     uint32_t *sums = nullptr;
     int rc = noalloc_scratch(ctx, &sums);
     if (rc) return rc;
