@@ -291,6 +291,13 @@ def main():
     peak, peak_src = peaks()
     achieved = tot_score_evals * NODE_REC_BYTES / (tot_score_ms * 1e-3) / 1e9 if tot_score_ms > 0 else 0.0
     traffic = ncu_traffic()
+    if traffic and traffic.get("workload", "c3") != wl:
+        traffic = None  # the committed ncu capture is of another workload's launch
+    # second roofline, the one that actually binds: INT ALU pipe, 16 lanes/clk/SMSP on 592 SMSPs
+    alu_ops_per_eval = 9  # SASS of score_kernel<1,1>: 4 LOP3 + 2 ISETP + SHF + LOP3 + SEL per eval
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965
+    alu_peak = 148 * 4 * 16 * sm_mhz * 1e6 / alu_ops_per_eval  # evals/s if the ALU pipe never idled
+    alu_achieved = tot_score_evals / (tot_score_ms * 1e-3) if tot_score_ms > 0 else 0.0
     line = {
         "metric": "pod_node_score_evals_per_sec", "value": tot_evals / (tot_ms * 1e-3), "unit": "evals/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
@@ -307,6 +314,9 @@ def main():
                      "share_of_step": tot_score_ms / tot_ms if tot_ms else None,
                      "note": "node records are re-read from shared memory/L2, not DRAM: frac > 1 is on-chip reuse "
                              "(DESIGN.md 'roofline')"},
+        "roofline_alu": {"bound": "int32 ALU pipe", "achieved": alu_achieved, "peak": alu_peak, "unit": "evals/s",
+                         "frac": alu_achieved / alu_peak, "alu_ops_per_eval": alu_ops_per_eval,
+                         "note": "peak = 592 SMSPs x 16 lanes/clk x sm clock / ALU instructions per eval"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
     if launches_e2e is not None:
