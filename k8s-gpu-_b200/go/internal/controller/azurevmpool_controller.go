@@ -126,7 +126,108 @@ func (r *AzureVmPoolReconciler) Reconcile(ctx context.Context, req ctrl.Request)
 // same early returns.  See BatchReconciler::ReconcileAll in ../../host/reconciler.cpp for the
 // table construction, which this function repeats line for line.
 func (r *AzureVmPoolReconciler) ReconcileAll(ctx context.Context, reqs []ctrl.Request) ([]ctrl.Result, []error) {
-	panic("see ../../host/reconciler.cpp: BatchReconciler::ReconcileAll (compiled and tested); the Go body is row f1 of SURVEY.md section 8 and needs a Go toolchain to be written against")
+	results, errs := make([]ctrl.Result, len(reqs)), make([]error, len(reqs))
+	type live struct {
+		req  int
+		pool computev1alpha1.AzureVmPool
+	}
+	var pools []live
+	for i, req := range reqs { // step 1 per request (README.md:174-177)
+		var p computev1alpha1.AzureVmPool
+		if err := r.Get(ctx, req.NamespacedName, &p); err != nil {
+			errs[i] = client.IgnoreNotFound(err)
+			continue
+		}
+		pools = append(pools, live{i, p})
+	}
+	// step 3 once per resource group; a failed list fails every pool of that group (README.md:192)
+	listed, failed := map[string][]fakearm.VM{}, map[string]error{}
+	for _, l := range pools {
+		rg := l.pool.Spec.ResourceGroupName
+		if _, done := listed[rg]; !done && failed[rg] == nil {
+			if vms, err := r.ARM.ListVMs(rg); err != nil {
+				failed[rg] = err
+			} else {
+				listed[rg] = vms
+			}
+		}
+	}
+	// tables: pool row p has owner id p; a VM carries the row of the pool (of its group) it names
+	type key struct{ rg, owner string }
+	rowOf, rows := map[key]uint32{}, []int{}
+	var desired []int32
+	var poolOwner []uint32
+	for i, l := range pools {
+		if failed[l.pool.Spec.ResourceGroupName] != nil {
+			continue
+		}
+		rowOf[key{l.pool.Spec.ResourceGroupName, ownerTag(&l.pool)}] = uint32(len(rows))
+		poolOwner = append(poolOwner, uint32(len(rows)))
+		desired = append(desired, l.pool.Spec.Replicas)
+		rows = append(rows, i)
+	}
+	P := uint32(len(rows))
+	var vmOwner, vmFlags, vmOrdinal []uint32
+	var vmName []string
+	for rg, vms := range listed {
+		for _, vm := range vms {
+			oid, ord, flag := uint32(0xFFFFFFFF), uint32(0xFFFFFFFF), uint32(0)
+			if owner, ok := vm.Tags[fakearm.OwnerKey]; ok {
+				if row, mine := rowOf[key{rg, owner}]; mine {
+					oid = row
+					if k, ok := ordinalOf(*vm.Name, pools[rows[row]].pool.Name); ok {
+						ord = k
+					}
+				} else {
+					oid = P // somebody else's owner tag
+				}
+			}
+			if vm.Tags[fakearm.ManagedByKey] == fakearm.ManagedByValue {
+				flag = 1
+			}
+			vmOwner, vmFlags, vmOrdinal = append(vmOwner, oid), append(vmFlags, flag), append(vmOrdinal, ord)
+			vmName = append(vmName, *vm.Name)
+		}
+	}
+	var dec *k8sgpu.Decisions
+	var gpuErr error
+	if P > 0 {
+		dec, gpuErr = r.GPU.ReconcileBatch(desired, poolOwner, vmOwner, vmFlags, vmOrdinal, P)
+	}
+	for row, i := range rows { // README.md:203-230 per pool, driven by the GPU's decisions
+		l := &pools[i]
+		if gpuErr != nil {
+			results[l.req], errs[l.req] = ctrl.Result{RequeueAfter: 30 * time.Second}, gpuErr
+			continue
+		}
+		var err error
+		for j := dec.CreateOff[row]; j < dec.CreateOff[row+1] && err == nil; j++ {
+			err = r.createVMNamed(ctx, &l.pool, fmt.Sprintf("%s-%d", l.pool.Name, dec.CreateOrdinal[j]))
+		}
+		for j := dec.VictimOff[row]; j < dec.VictimOff[row+1] && err == nil; j++ {
+			err = r.deleteVM(ctx, &l.pool, vmName[dec.VictimVM[j]])
+		}
+		if err != nil {
+			results[l.req], errs[l.req] = ctrl.Result{RequeueAfter: 40 * time.Second}, err
+			continue
+		}
+		l.pool.Status.ReadyReplicas = dec.Ready[row]
+		l.pool.Status.VMs = l.pool.Status.VMs[:0]
+		for j := dec.MemberOff[row]; j < dec.MemberOff[row+1]; j++ {
+			l.pool.Status.VMs = append(l.pool.Status.VMs, vmName[dec.MemberVM[j]])
+		}
+		if err := r.Status().Update(ctx, &l.pool); err != nil {
+			results[l.req], errs[l.req] = ctrl.Result{}, err
+			continue
+		}
+		results[l.req] = ctrl.Result{RequeueAfter: time.Minute}
+	}
+	for _, l := range pools {
+		if err := failed[l.pool.Spec.ResourceGroupName]; err != nil {
+			results[l.req], errs[l.req] = ctrl.Result{RequeueAfter: 20 * time.Second}, err
+		}
+	}
+	return results, errs
 }
 
 func (r *AzureVmPoolReconciler) SetupWithManager(mgr ctrl.Manager) error {
