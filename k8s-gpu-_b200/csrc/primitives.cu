@@ -128,18 +128,24 @@ __global__ void __launch_bounds__(kSortThreads) sort_hist_kernel(const uint32_t 
 
 // Stable scatter.  Warp w owns the contiguous 256-element chunk w of the tile and walks it in
 // 8 sub-rows of 32, so (warp, sub-row, lane) order == input order.  Ranks inside a sub-row come
-// from __match_any_sync; per-warp digit counters carry the rank across sub-rows.
+// from __match_any_sync; per-warp digit counters carry the rank across sub-rows.  The tile is
+// then laid out digit-major in shared memory and written out by consecutive threads, so each
+// (block, digit) run leaves as one contiguous store instead of 4-byte scattered writes.
 __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(
     const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals, uint32_t *__restrict__ out_keys,
     uint32_t *__restrict__ out_vals, uint32_t n, int shift, uint32_t mask, const uint32_t *__restrict__ hist_scan,
     uint32_t nblocks) {
     __shared__ uint32_t cnt[8][256];
+    __shared__ uint32_t gdelta[256];  // global base of digit d minus its start inside the tile
+    __shared__ uint32_t wtot[8];
+    __shared__ uint32_t sk[kSortTile], sv[kSortTile];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 #pragma unroll
     for (int w = 0; w < 8; ++w) cnt[w][tid] = 0;
     __syncthreads();
 
-    const uint32_t chunk = blockIdx.x * kSortTile + warp * 256;
+    const uint32_t tile_base = blockIdx.x * kSortTile;
+    const uint32_t chunk = tile_base + warp * 256;
     uint32_t k[8], v[8], rank[8];
 #pragma unroll
     for (int s = 0; s < 8; ++s) {
@@ -166,14 +172,25 @@ __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(
         __syncwarp();
     }
     __syncthreads();
-    {  // thread d: turn per-warp counts of digit d into absolute output bases
-        uint32_t run = hist_scan[tid * nblocks + blockIdx.x];
+    {  // thread d: per-warp counts of digit d -> offsets inside the digit's run; run starts by block scan
+        uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < 8; ++w) {
             uint32_t t = cnt[w][tid];
             cnt[w][tid] = run;
             run += t;
         }
+        uint32_t inc = warp_incl_scan(run, lane);  // exclusive start of digit `tid` inside the tile
+        if (lane == 31) wtot[warp] = inc;
+        __syncthreads();
+        uint32_t woff = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w)
+            if (w < warp) woff += wtot[w];
+        const uint32_t dstart = woff + inc - run;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) cnt[w][tid] += dstart;
+        gdelta[tid] = hist_scan[tid * nblocks + blockIdx.x] - dstart;
     }
     __syncthreads();
 #pragma unroll
@@ -181,9 +198,21 @@ __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(
         uint32_t i = chunk + s * 32 + lane;
         if (i < n) {
             uint32_t d = (k[s] >> shift) & mask;
-            uint32_t dst = cnt[warp][d] + rank[s];
-            out_keys[dst] = k[s];
-            out_vals[dst] = v[s];
+            uint32_t p = cnt[warp][d] + rank[s];
+            sk[p] = k[s];
+            sv[p] = v[s];
+        }
+    }
+    __syncthreads();
+    const uint32_t count = min(kSortTile, n - tile_base);
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        uint32_t p = s * kSortThreads + tid;
+        if (p < count) {
+            uint32_t kk = sk[p];
+            uint32_t dst = gdelta[(kk >> shift) & mask] + p;
+            out_keys[dst] = kk;
+            out_vals[dst] = sv[p];
         }
     }
 }
