@@ -95,6 +95,7 @@ struct k8sgpu_ctx {
     cudaEvent_t ev_score[2 * k8sgpu::kMaxTimedRounds] = {};
     uint32_t *h_pinned = nullptr;  // 64 u32 of pinned host memory for small read-backs
     int sm_count = 148;
+    int coop_blocks_per_sm = 0;  // occupancy of admit_coop_kernel (0 = not queried yet, <0 = unusable)
     char err[512] = {0};
     k8sgpu_stats stats = {};
     k8sgpu::PlaceState place;
