@@ -294,7 +294,7 @@ def main():
     if traffic and traffic.get("workload", "c3") != wl:
         traffic = None  # the committed ncu capture is of another workload's launch
     # second roofline, the one that actually binds: INT ALU pipe, 16 lanes/clk/SMSP on 592 SMSPs
-    alu_ops_per_eval = 9  # SASS of score_kernel<1,1>: 4 LOP3 + 2 ISETP + SHF + LOP3 + SEL per eval
+    alu_ops_per_eval = 8  # SASS of score_kernel<1,2>: 4 LOP3 + SHF + LOP3 + 2 ISETP per eval (the rest is FMA pipe / LDS)
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965
     alu_peak = 148 * 4 * 16 * sm_mhz * 1e6 / alu_ops_per_eval  # evals/s if the ALU pipe never idled
     alu_achieved = tot_score_evals / (tot_score_ms * 1e-3) if tot_score_ms > 0 else 0.0

@@ -484,30 +484,28 @@ __global__ void __launch_bounds__(kSegThreads) admit_seg_reduce_kernel(
     seg_block_scan(x, &block_tot[blockIdx.x]);
 }
 
-// One warp turns block totals into exclusive carries (carry[b] = everything before block b).
-__device__ __forceinline__ void seg_carry_warp(Seg *__restrict__ block_tot, uint32_t nb) {
-    const int lane = threadIdx.x & 31;
+// One CTA turns block totals into exclusive carries (carry[b] = everything before block b),
+// 256 blocks per step.
+__device__ __forceinline__ void seg_carry_block(Seg *__restrict__ block_tot, uint32_t nb) {
+    __shared__ Seg buf[kSegThreads];
     Seg run;
     run.g = run.c = run.m = run.head = 0;
-    for (uint32_t base = 0; base < nb; base += 32) {
-        uint32_t b = base + lane;
+    for (uint32_t base = 0; base < nb; base += kSegThreads) {
+        const uint32_t b = base + threadIdx.x;
         Seg x;
-        x.g = x.c = x.m = 0;
-        x.head = 0;
+        x.g = x.c = x.m = x.head = 0;
         if (b < nb) x = block_tot[b];
-        Seg inc = seg_warp_scan(x, lane);
-        Seg with = seg_combine(run, inc);            // inclusive through block b
-        Seg prev = seg_shfl_up(with, 1);             // exclusive = inclusive of b-1
-        if (lane == 0) prev = run;
-        if (b < nb) block_tot[b] = prev;
-        run.g = __shfl_sync(0xFFFFFFFFu, with.g, 31);
-        run.c = __shfl_sync(0xFFFFFFFFu, with.c, 31);
-        run.m = __shfl_sync(0xFFFFFFFFu, with.m, 31);
-        run.head = __shfl_sync(0xFFFFFFFFu, with.head, 31);
+        Seg with = seg_combine(run, seg_block_scan(x, nullptr));  // inclusive through block b
+        buf[threadIdx.x] = with;
+        __syncthreads();
+        if (b < nb) block_tot[b] = threadIdx.x ? buf[threadIdx.x - 1] : run;  // exclusive
+        run = buf[kSegThreads - 1];
+        __syncthreads();
     }
 }
-
-__global__ void admit_seg_carry_kernel(Seg *__restrict__ block_tot, uint32_t nb) { seg_carry_warp(block_tot, nb); }
+__global__ void __launch_bounds__(kSegThreads) admit_seg_carry_kernel(Seg *__restrict__ block_tot, uint32_t nb) {
+    seg_carry_block(block_tot, nb);
+}
 
 // S <= free test on the inclusive prefix sums; admitted pods get their node.
 __global__ void __launch_bounds__(kSegThreads) admit_apply_kernel(
@@ -584,6 +582,7 @@ struct AdmitArgs {
     uint32_t *counters;                           // [1] <- next active count
     uint32_t na, n_nodes, n_pad;
     int bits;
+    unsigned long long *prof;  // optional: %globaltimer at each phase boundary (CTA 0), else null
 };
 
 // Exclusive scan of n u32 by the whole grid; every CTA must call it.  Ends with a grid barrier.
@@ -614,9 +613,18 @@ __device__ __forceinline__ void coop_exclusive_scan(cg::grid_group &grid, const 
     grid.sync();
 }
 
+__device__ __forceinline__ void prof_mark(const AdmitArgs &a, int slot) {
+    if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.prof[slot] = t;
+    }
+}
+
 __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = threadIdx.x, cta = blockIdx.x, G = gridDim.x;
+    prof_mark(a, 0);
     const uint32_t na = a.na, N = a.n_nodes;
     const uint32_t nb = (na + kSortTile - 1) / kSortTile;
 
@@ -642,6 +650,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
         sort_hist_tile(a.keys, na, 0, 0xFFu, a.hist, nb, vt);
     }
     grid.sync();
+    prof_mark(a, 1);
 
     // stable LSD radix sort by node, 8 bits a pass
     uint32_t *sk = a.keys, *sv = a.vals, *dk = a.keys_alt, *dv = a.vals_alt;
@@ -660,6 +669,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
         t = sk; sk = dk; dk = t;
         t = sv; sv = dv; dv = t;
     }
+    prof_mark(a, 2);
 
     // segmented prefix sums over the proposers of each node, in pod order
     const uint32_t nb2 = (na + kSegThreads - 1) / kSegThreads;
@@ -670,8 +680,10 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
         __syncthreads();
     }
     grid.sync();
-    if (cta == 0 && tid < 32) seg_carry_warp(a.seg, nb2);
+    prof_mark(a, 3);
+    if (cta == 0) seg_carry_block(a.seg, nb2);
     grid.sync();
+    prof_mark(a, 4);
     for (uint32_t vb = cta; vb < nb2; vb += G) {  // S <= free (a13); admitted flags go to offs[] for now
         const uint32_t i = vb * kSegThreads + tid;
         uint32_t key;
@@ -688,6 +700,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
         __syncthreads();
     }
     grid.sync();
+    prof_mark(a, 5);
     // free -= admitted (commutative integer atomics), pending flags in ORIGINAL active order
     for (uint32_t i = cta * 256 + tid; i < na; i += G * 256) {
         if (a.offs[i]) {
@@ -700,12 +713,15 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
         a.flags[i] = a.assign[a.active[i]] == K8SGPU_ASSIGN_PENDING ? 1u : 0u;
     }
     grid.sync();
+    prof_mark(a, 6);
     coop_exclusive_scan(grid, a.flags, a.offs, na, a.scan_sums, a.counters + 1);
+    prof_mark(a, 7);
     // stable compaction of the active list, and the next round's packed node records
     for (uint32_t i = cta * 256 + tid; i < na; i += G * 256)
         if (a.flags[i]) a.next_active[a.offs[i]] = a.active[i];
     for (uint32_t i = cta * 256 + tid; i < a.n_pad; i += G * 256)
         a.nodeq[i] = make_nodeq(a.node_cols, a.freec, N, i, nullptr, 0);
+    prof_mark(a, 8);
 }
 
 // ------------------------------------------------------------------ host side
@@ -877,7 +893,7 @@ static int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t 
         const uint32_t nb = ceil_div(na, kSegThreads);
         Seg *seg = st.seg.as<Seg>();
         K8S_LAUNCH(ctx, admit_seg_reduce_kernel, nb, kSegThreads, 0, s, keys, vals, active, st.podq.as<PodQ>(), na, seg);
-        K8S_LAUNCH(ctx, admit_seg_carry_kernel, 1, 32, 0, s, seg, nb);
+        K8S_LAUNCH(ctx, admit_seg_carry_kernel, 1, kSegThreads, 0, s, seg, nb);
         K8S_LAUNCH(ctx, admit_apply_kernel, nb, kSegThreads, 0, s, keys, vals, active, st.podq.as<PodQ>(), na, st.n,
                    seg, st.free_cols.as<uint32_t>(), st.assign.as<int32_t>(), flags);
         K8S_LAUNCH(ctx, admit_free_update_kernel, g, 256, 0, s, keys, vals, active, st.podq.as<PodQ>(), flags, na,
@@ -945,6 +961,9 @@ static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s) {
     a.n_nodes = st.n;
     a.n_pad = st.n_pad;
     a.bits = key_bits(st.n);
+    a.prof = nullptr;
+    static const bool want_prof = getenv("K8SGPU_COOP_PROF") != nullptr;
+    if (want_prof) a.prof = reinterpret_cast<unsigned long long *>(cnts + 16);  // counters[16..34)
     // enough CTAs to spread the tiles, few enough that the grid barriers stay cheap
     uint32_t want = ceil_div(na, 512u), prep = ceil_div(st.n_pad, 2048u);
     if (prep > want) want = prep;
@@ -960,6 +979,14 @@ static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s) {
                     (ctx->h_pinned[0] & kErrNode) ? "node" : "pod");
     if (ctx->h_pinned[1] >= na)
         return fail(ctx, K8SGPU_E_CUDA, "place: round %u made no progress (%u pods still active)", st.rounds, na);
+    if (want_prof) {  // developer aid: phase boundaries of this round's admission, microseconds
+        unsigned long long t[9];
+        K8S_CUDA(ctx, cudaMemcpy(t, cnts + 16, sizeof t, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "[coop round %u na=%u grid=%u] keys+hist %.1f sort %.1f segreduce %.1f carry %.1f apply %.1f "
+                        "free+flags %.1f scan %.1f compact+prep %.1f total %.1f us\n",
+                st.rounds, na, grid, (t[1] - t[0]) / 1e3, (t[2] - t[1]) / 1e3, (t[3] - t[2]) / 1e3, (t[4] - t[3]) / 1e3,
+                (t[5] - t[4]) / 1e3, (t[6] - t[5]) / 1e3, (t[7] - t[6]) / 1e3, (t[8] - t[7]) / 1e3, (t[8] - t[0]) / 1e3);
+    }
     st.evals += (uint64_t)na * st.n;
     st.rounds++;
     st.cur ^= 1;
@@ -997,11 +1024,10 @@ static int place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy) {
     K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
     int rc = round_begin(ctx, policy, s);
     if (rc) return rc;
-    // K8SGPU_COOP=1: admission as ONE cooperative launch per round (two launches per round in all).
-    // Measured on config 3 it is ~4 % slower than the chain of small kernels (a grid barrier costs
-    // about what a dependent launch costs, and the phases are latency bound either way), so the
-    // chain stays the default; both paths are tested and give identical results.
-    bool coop = false;
+    // Admission as ONE cooperative launch per round (two launches per round in all): measured
+    // ~3 % faster per config-3 step than the chain of ~20 small kernels.  K8SGPU_COOP=0 selects
+    // the chain (the round-at-a-time API always uses it); both give identical results.
+    bool coop = true;
     if (const char *e = getenv("K8SGPU_COOP")) coop = atoi(e) != 0;
     while (st.n_active > 0 && (st.max_rounds == 0 || st.rounds < st.max_rounds)) {
         if (coop) {

@@ -24,19 +24,20 @@ __global__ void __launch_bounds__(kScanThreads) scan_down_kernel(const uint32_t 
     block_scan_tile(in, out, blockIdx.x * kScanTile, n, block_offs[blockIdx.x], true);
 }
 
-// Single block: scans n <= any size by looping over tiles; writes total.
-__global__ void __launch_bounds__(kScanThreads) scan_single_kernel(const uint32_t *in,
-                                                                   uint32_t *out, uint32_t n,
-                                                                   uint32_t *__restrict__ total) {
+// Single block of 1024 threads: scans any n by looping over 8192-element tiles; writes total.
+constexpr int kScanSingleThreads = 1024;
+__global__ void __launch_bounds__(kScanSingleThreads) scan_single_kernel(const uint32_t *in, uint32_t *out, uint32_t n,
+                                                                         uint32_t *__restrict__ total) {
     uint32_t carry = 0;
-    for (uint32_t base = 0; base < n; base += kScanTile) carry = block_scan_tile(in, out, base, n, carry, true);
+    for (uint32_t base = 0; base < n; base += kScanSingleThreads * 8)
+        carry = block_scan_tile<kScanSingleThreads>(in, out, base, n, carry, true);
     if (threadIdx.x == 0 && total) *total = carry;
 }
 
 int exclusive_scan_u32(k8sgpu_ctx *ctx, cudaStream_t s, const uint32_t *d_in, uint32_t *d_out, uint32_t n,
                        DevBuf &tmp, uint32_t *d_total) {
     if (n <= 8 * kScanTile) {  // small: one block walks it
-        K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanThreads, 0, s, d_in, d_out, n, d_total);
+        K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanSingleThreads, 0, s, d_in, d_out, n, d_total);
         return K8SGPU_OK;
     }
     uint32_t nb = ceil_div(n, kScanTile);
@@ -45,7 +46,7 @@ int exclusive_scan_u32(k8sgpu_ctx *ctx, cudaStream_t s, const uint32_t *d_in, ui
     uint32_t *sums = tmp.as<uint32_t>();
     K8S_LAUNCH(ctx, scan_reduce_kernel, nb, kScanThreads, 0, s, d_in, n, sums);
     // nb <= 2^31 / 2048 = 2^20 block sums: one block scans them in place
-    K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanThreads, 0, s, sums, sums, nb, d_total);
+    K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanSingleThreads, 0, s, sums, sums, nb, d_total);
     K8S_LAUNCH(ctx, scan_down_kernel, nb, kScanThreads, 0, s, d_in, d_out, n, sums);
     return K8SGPU_OK;
 }
@@ -158,14 +159,14 @@ extern "C" int k8sgpu_exclusive_scan_noalloc(k8sgpu_ctx *ctx, const uint32_t *d_
     int rc = noalloc_scratch(ctx, &sums);
     if (rc) return rc;
     if (n <= kScanTile) {  // one block, no scratch touched
-        K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanThreads, 0, s, d_in, d_out, n, d_total);
+        K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanSingleThreads, 0, s, d_in, d_out, n, d_total);
         return K8SGPU_OK;
     }
     // Nothing in the scratch has to start at zero: the first kernel overwrites every block sum
     // that the later two read, so whatever the previous call left behind is never seen.
     const uint32_t nb = ceil_div(n, kScanTile);
     K8S_LAUNCH(ctx, scan_reduce_kernel, nb, kScanThreads, 0, s, d_in, n, sums);
-    K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanThreads, 0, s, sums, sums, nb, d_total);
+    K8S_LAUNCH(ctx, scan_single_kernel, 1, kScanSingleThreads, 0, s, sums, sums, nb, d_total);
     K8S_LAUNCH(ctx, scan_down_kernel, nb, kScanThreads, 0, s, d_in, d_out, n, sums);
     return K8SGPU_OK;
 }

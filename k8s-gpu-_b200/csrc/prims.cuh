@@ -19,12 +19,15 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t x, int lane) {
 // elements (two 128-bit loads when the tile is whole and 16-byte aligned), scans them in
 // registers, and one warp-shuffle + shared-memory step combines the 256 thread totals.
 // carry_in is added to every output.  Returns carry_in + the tile total (all threads).
+// THREADS is the CTA size (256, or 1024 for the one-CTA kernel); a tile is THREADS * 8 elements.
+template <int THREADS = 256>
 __device__ __forceinline__ uint32_t block_scan_tile(const uint32_t *in, uint32_t *out,  // may alias (in place)
                                                     uint32_t base, uint32_t n, uint32_t carry_in, bool write) {
-    __shared__ uint32_t warp_tot[8];
+    constexpr int NW = THREADS / 32;
+    __shared__ uint32_t warp_tot[NW];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t i0 = base + (uint32_t)tid * 8u;
-    const bool vec = base + kScanTile <= n &&
+    const bool vec = base + (uint32_t)THREADS * 8u <= n &&
                      (((uintptr_t)in | (write ? (uintptr_t)out : (uintptr_t)0)) & 15u) == 0;
     uint32_t x[8];
     if (vec) {
@@ -43,7 +46,7 @@ __device__ __forceinline__ uint32_t block_scan_tile(const uint32_t *in, uint32_t
     __syncthreads();
     uint32_t woff = 0, all = 0;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) {
+    for (int w = 0; w < NW; ++w) {
         const uint32_t t = warp_tot[w];
         if (w < warp) woff += t;
         all += t;

@@ -130,6 +130,19 @@ def test_place_heterogeneous_sweep(ctx, orc, synth, h100, taint, m):
     same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
 
 
+@pytest.mark.parametrize("name", ["c3_small", "ties_rot_zero", "c5_all_h100"])
+def test_place_single_launch_admission(ctx, name, monkeypatch):
+    """K8SGPU_COOP=1: the cooperative one-launch admission path gives the golden result too."""
+    monkeypatch.setenv("K8SGPU_COOP", "1")
+    nodes, pods, flags = mg.place_inputs(name)
+    g = np.load(os.path.join(HERE, "golden", f"place_{name}.npz"))
+    got = ctx.place(nodes, pods, flags=flags)
+    for k in ("assign", "free_gpu", "free_mcpu", "free_mib"):
+        assert np.array_equal(got[k], g[k]), k
+    assert (got["rounds"], got["placed"], got["evals"]) == (int(g["rounds"]), int(g["placed"]), int(g["evals"]))
+    assert got["kernel_launches"] <= 2 * got["rounds"] + 8
+
+
 def test_k12_ties_rot_zero(ctx, synth):
     nodes, pods = synth.gen_identical(5, 41)
     r = ctx.place(nodes, pods, flags=1)
