@@ -110,3 +110,96 @@ int khost_reconcile_batch(khost_world *w, int device, int n, const char *const *
 uint64_t khost_last_gpu_launches(khost_world *w) { return w->batch ? w->batch->LastStats().kernel_launches : 0; }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ snapshot ingestion (f2)
+#include "snapshot.hpp"
+
+struct khost_snap {
+    SnapshotBuilder b;
+    ReconcileTables rec;
+    NodeTable nodes;
+    PodTable pods;
+    std::string err;
+};
+
+extern "C" {
+
+khost_snap *khost_snap_new() { return new khost_snap(); }
+void khost_snap_free(khost_snap *s) { delete s; }
+const char *khost_snap_error(khost_snap *s) { return s->err.c_str(); }
+
+static int snap_result(khost_snap *s, bool ok, const ParseError &e) {
+    s->err = ok ? "" : (e.msg + " (line " + std::to_string(e.line) + ")");
+    return ok ? 0 : -1;
+}
+int khost_snap_add_pools_yaml(khost_snap *s, const char *text) {
+    ParseError e;
+    return snap_result(s, s->b.AddPoolsYaml(text, &e), e);
+}
+int khost_snap_add_vms_json(khost_snap *s, const char *text) {
+    ParseError e;
+    return snap_result(s, s->b.AddVmsJson(text, &e), e);
+}
+int khost_snap_add_jobs_yaml(khost_snap *s, const char *text) {
+    ParseError e;
+    return snap_result(s, s->b.AddJobsYaml(text, &e), e);
+}
+void khost_snap_register_sku(khost_snap *s, const char *vm_size, uint32_t gpu, uint32_t mcpu, uint32_t mib) {
+    s->b.RegisterSku(vm_size, gpu, mcpu, mib);
+}
+void khost_snap_build(khost_snap *s) {
+    s->rec = s->b.BuildReconcileTables();
+    s->nodes = s->b.BuildNodeTable();  // interns the zones the pod table then refers to
+    s->pods = s->b.BuildPodTable();
+}
+// table: 0 pools, 1 vms, 2 nodes, 3 pods
+uint32_t khost_snap_rows(khost_snap *s, int table) {
+    switch (table) {
+        case 0: return static_cast<uint32_t>(s->rec.desired.size());
+        case 1: return static_cast<uint32_t>(s->rec.vm_owner.size());
+        case 2: return static_cast<uint32_t>(s->nodes.flags.size());
+        default: return static_cast<uint32_t>(s->pods.req_gpu.size());
+    }
+}
+uint32_t khost_snap_n_owner_ids(khost_snap *s) { return s->rec.n_owner_ids; }
+// columns in the order of include/k8sgpu.h; pools: desired (as i32 bits), owner_id
+const uint32_t *khost_snap_col(khost_snap *s, int table, int col) {
+    const std::vector<uint32_t> *v = nullptr;
+    if (table == 0) {
+        if (col == 0) return reinterpret_cast<const uint32_t *>(s->rec.desired.data());
+        v = &s->rec.pool_owner;
+    } else if (table == 1) {
+        v = col == 0 ? &s->rec.vm_owner : col == 1 ? &s->rec.vm_flags : &s->rec.vm_ordinal;
+    } else if (table == 2) {
+        const std::vector<uint32_t> *c[8] = {&s->nodes.free_gpu, &s->nodes.free_mcpu, &s->nodes.free_mib, &s->nodes.cap_gpu,
+                                             &s->nodes.sku_id,   &s->nodes.zone_id,   &s->nodes.taint_mask, &s->nodes.flags};
+        v = c[col & 7];
+    } else {
+        const std::vector<uint32_t> *c[8] = {&s->pods.req_gpu,  &s->pods.req_mcpu, &s->pods.req_mib,   &s->pods.sku_mask,
+                                             &s->pods.zone_mask, &s->pods.tol_mask, &s->pods.pref_zone, &s->pods.priority};
+        v = c[col & 7];
+    }
+    return v->data();
+}
+const char *khost_snap_name(khost_snap *s, int table, uint32_t row) {
+    const std::vector<std::string> *v = table == 0 ? &s->rec.pool_key : table == 1 ? &s->rec.vm_name
+                                        : table == 2 ? &s->nodes.name : &s->pods.name;
+    return row < v->size() ? (*v)[row].c_str() : nullptr;
+}
+const char *khost_snap_pool_field(khost_snap *s, uint32_t i, const char *field) {
+    const auto &pools = s->b.Pools();
+    if (i >= pools.size()) return nullptr;
+    const auto &p = pools[i];
+    std::string f = field;
+    const std::string *v = f == "name" ? &p.Metadata.Name : f == "namespace" ? &p.Metadata.Namespace
+                           : f == "resourceGroupName" ? &p.Spec.ResourceGroupName : f == "location" ? &p.Spec.Location
+                           : f == "vmSize" ? &p.Spec.VMSize : f == "vnetName" ? &p.Spec.VnetName
+                           : f == "subnetName" ? &p.Spec.SubnetName : f == "azureCredentialSecret" ? &p.Spec.AzureCredentialSecret
+                           : f == "imageReference.publisher" ? &p.Spec.ImageReference.Publisher
+                           : f == "imageReference.offer" ? &p.Spec.ImageReference.Offer
+                           : f == "imageReference.sku" ? &p.Spec.ImageReference.SKU
+                           : f == "imageReference.version" ? &p.Spec.ImageReference.Version : nullptr;
+    return v ? v->c_str() : nullptr;
+}
+
+}  // extern "C"

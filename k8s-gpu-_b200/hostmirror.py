@@ -112,3 +112,84 @@ class World:
     @property
     def last_gpu_launches(self):
         return int(self._L.khost_last_gpu_launches(self._h))
+
+
+NODE_COLS = ("free_gpu", "free_mcpu", "free_mib", "cap_gpu", "sku_id", "zone_id", "taint_mask", "flags")
+POD_COLS = ("req_gpu", "req_mcpu", "req_mib", "sku_mask", "zone_mask", "tol_mask", "pref_zone", "priority")
+
+
+class Snapshot:
+    """host/snapshot.hpp: AzureVmPool manifests (YAML) + ARM VM list (JSON) + Volcano jobs (YAML)
+    -> the u32 tables of include/k8sgpu.h, as numpy columns."""
+
+    def __init__(self):
+        import numpy as np
+
+        self.np = np
+        L = self._L = load()
+        vp, cp = C.c_void_p, C.c_char_p
+        L.khost_snap_new.restype = vp
+        L.khost_snap_free.argtypes = [vp]
+        L.khost_snap_error.argtypes = [vp]
+        L.khost_snap_error.restype = cp
+        for f in ("khost_snap_add_pools_yaml", "khost_snap_add_vms_json", "khost_snap_add_jobs_yaml"):
+            getattr(L, f).argtypes = [vp, cp]
+        L.khost_snap_register_sku.argtypes = [vp, cp, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.khost_snap_register_sku.restype = None
+        L.khost_snap_build.argtypes = [vp]
+        L.khost_snap_build.restype = None
+        L.khost_snap_rows.argtypes = [vp, C.c_int]
+        L.khost_snap_rows.restype = C.c_uint32
+        L.khost_snap_n_owner_ids.argtypes = [vp]
+        L.khost_snap_n_owner_ids.restype = C.c_uint32
+        L.khost_snap_col.argtypes = [vp, C.c_int, C.c_int]
+        L.khost_snap_col.restype = C.POINTER(C.c_uint32)
+        L.khost_snap_name.argtypes = [vp, C.c_int, C.c_uint32]
+        L.khost_snap_name.restype = cp
+        L.khost_snap_pool_field.argtypes = [vp, C.c_uint32, cp]
+        L.khost_snap_pool_field.restype = cp
+        self._h = L.khost_snap_new()
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._L.khost_snap_free(self._h)
+            self._h = None
+
+    def _add(self, fn, text):
+        if getattr(self._L, fn)(self._h, text.encode()) != 0:
+            raise ValueError(self._L.khost_snap_error(self._h).decode())
+
+    def add_pools_yaml(self, text): self._add("khost_snap_add_pools_yaml", text)
+    def add_vms_json(self, text): self._add("khost_snap_add_vms_json", text)
+    def add_jobs_yaml(self, text): self._add("khost_snap_add_jobs_yaml", text)
+
+    def register_sku(self, vm_size, gpu, mcpu, mib):
+        self._L.khost_snap_register_sku(self._h, vm_size.encode(), gpu, mcpu, mib)
+
+    def pool_field(self, i, field):
+        v = self._L.khost_snap_pool_field(self._h, i, field.encode())
+        return None if v is None else v.decode()
+
+    def _col(self, table, col, n, dtype=None):
+        np = self.np
+        if n == 0:
+            return np.zeros(0, dtype or np.uint32)
+        p = self._L.khost_snap_col(self._h, table, col)
+        a = np.ctypeslib.as_array(p, shape=(n,)).copy()
+        return a.view(dtype) if dtype is not None else a
+
+    def _names(self, table, n):
+        return [self._L.khost_snap_name(self._h, table, i).decode() for i in range(n)]
+
+    def build(self) -> dict:
+        """-> {"reconcile": kwargs of Context.reconcile_batch, "nodes": {...}, "pods": {...}, names}"""
+        np, L = self.np, self._L
+        L.khost_snap_build(self._h)
+        P, V, N, M = (L.khost_snap_rows(self._h, t) for t in range(4))
+        rec = dict(desired=self._col(0, 0, P, np.int32), pool_owner_id=self._col(0, 1, P),
+                   vm_owner_id=self._col(1, 0, V), vm_flags=self._col(1, 1, V), vm_ordinal=self._col(1, 2, V),
+                   n_owner_ids=int(L.khost_snap_n_owner_ids(self._h)))
+        nodes = {c: self._col(2, i, N) for i, c in enumerate(NODE_COLS)}
+        pods = {c: self._col(3, i, M) for i, c in enumerate(POD_COLS)}
+        return dict(reconcile=rec, nodes=nodes, pods=pods, pool_keys=self._names(0, P), vm_names=self._names(1, V),
+                    node_names=self._names(2, N), pod_names=self._names(3, M))
