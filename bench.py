@@ -176,6 +176,7 @@ def main():
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-reconcile", action="store_true")
+    ap.add_argument("--no-scaling-base", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -321,6 +322,22 @@ def main():
     }
     if launches_e2e is not None:
         line["config"]["launches_per_e2e_step"] = launches_e2e
+    if world == 1 and wl == "c3" and not args.no_scaling_base:
+        # N>1 runs config 4 (BASELINE.json), so the like-for-like 1-GPU base of the scaling
+        # series is config 4 on one GPU: measure it here too (2 steps, ~0.5 s each).
+        n4, p4 = gen_workload("c4")
+        placer.upload(n4, p4)
+        placer.run()
+        b_ms = b_ev = 0.0
+        for _ in range(2):
+            flush.zero_()
+            torch.cuda.synchronize()
+            st4 = placer.run()
+            b_ms += st4["step_ms"]
+            b_ev += st4["evals"]
+        line["scaling_base"] = {"workload": WORKLOADS["c4"]["desc"], "n_gpus": 1, "value": b_ev / (b_ms * 1e-3),
+                                "unit": "evals/s", "ms_per_step": b_ms / 2, "rounds": st4["rounds"],
+                                "note": "divide the --gpus N>1 values by N times this for same-workload scaling efficiency"}
 
     if not args.no_reconcile and world == 1:
         from k8sgpu_b200 import synth
@@ -335,17 +352,40 @@ def main():
             flush.zero_()
             torch.cuda.synchronize()
             rms += ctx.reconcile_run()["device_ms"]
+        # end to end: pinned host tables in, host results out, one k8sgpu_reconcile_batch call per step
+        pin1 = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+        pargs = tuple(pin1(a) if isinstance(a, np.ndarray) else a for a in rargs)
+        ctx.reconcile_batch(*pargs)
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            ctx.reconcile_batch(*rargs)
+            rr = ctx.reconcile_batch(*pargs)
         rdt = time.perf_counter() - t0
         alg = 12 * C2["v"] + 16 * C2["p"]
         line["reconcile"] = {
             "workload": f"config2: {C2['p']} pools x {C2['v']} VMs", "decisions_per_s": C2["p"] * args.steps / (rms * 1e-3),
             "vm_rows_per_s": C2["v"] * args.steps / (rms * 1e-3), "ms_per_step": rms / args.steps,
-            "e2e_decisions_per_s": C2["p"] * args.steps / rdt, "algorithmic_bytes": alg,
+            "e2e_decisions_per_s": C2["p"] * args.steps / rdt, "e2e_ms_per_step": 1e3 * rdt / args.steps,
+            "h2d_bytes_per_step": int(rr["h2d_bytes"]), "d2h_bytes_per_step": int(rr["d2h_bytes"]),
+            "launches_per_step": int(rr["kernel_launches"]), "algorithmic_bytes": alg,
             "achieved_gbs": alg * args.steps / (rms * 1e-3) / 1e9,
+            "note": "1.2 MB of work: launch-latency bound at this size; see profiles/ for the scaled sweep",
         }
+        if not args.no_cpu_baseline:
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import oracle as orc
+
+            threads = os.cpu_count() or 1
+            best = 1e9
+            for nt in (1, threads):
+                orc.reconcile_batch(*rargs, nthreads=nt)
+                t0 = time.perf_counter()
+                for _ in range(5):
+                    orc.reconcile_batch(*rargs, nthreads=nt)
+                dt = (time.perf_counter() - t0) / 5
+                if dt < best:
+                    best, best_nt = dt, nt
+            line["reconcile"]["cpu_baseline"] = {"value": C2["p"] / best, "unit": "decisions/s", "cores": best_nt,
+                                                 "kind": "port", "sample": "whole config 2, best of 1 and all threads"}
 
     if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
