@@ -117,7 +117,7 @@ typedef struct {
     float score_ms;           /* CUDA-event time spent in the scoring kernel (sum over rounds)   */
     uint64_t score_evals;     /* evals covered by score_ms                                       */
     uint32_t score_launches;  /* scoring-kernel launches covered by score_ms                     */
-    uint32_t reserved;
+    uint32_t gang_iterations; /* place/retry iterations of the last k8sgpu_place_gang call       */
 } k8sgpu_stats;
 
 /* ------------------------------------------------------------------ context */
@@ -160,6 +160,25 @@ int k8sgpu_place(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_p
 int k8sgpu_place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods);
 int k8sgpu_place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy);
 int k8sgpu_place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out);
+
+/* Gang placement: all-or-nothing groups, the reference's `minAvailable` (GPU调度平台搭建.md:648,
+ * value 1 in its only example) generalised.  Layered on the round loop of k8sgpu_place:
+ *   1. every candidate pod is placed by the normal rounds (tentatively);
+ *   2. a gang with fewer placed members than min_available[g] is rejected for good: its pods
+ *      get K8SGPU_ASSIGN_GANG and what they had reserved is released;
+ *   3. pods still unplaced (-1) whose gang is not rejected are retried against the released
+ *      capacity; back to 2 until an iteration rejects no new gang.
+ * gang_id[p] == K8SGPU_NONE_U32: the pod is on its own.  gang_ok[g] (may be NULL) = 1 if kept.
+ * Queues (`queue: default`, :650) are not modelled.  Single GPU. */
+#define K8SGPU_ASSIGN_GANG (-3)
+typedef struct {
+    uint32_t n_gangs;
+    const uint32_t *gang_id;        /* [m]        */
+    const uint32_t *min_available;  /* [n_gangs]  */
+} k8sgpu_gang_table;
+int k8sgpu_place_gang(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods,
+                      const k8sgpu_gang_table *gangs, const k8sgpu_policy *policy, k8sgpu_place_out *out,
+                      int32_t *gang_ok);
 
 /* One scoring pass of all pods against the uploaded node table (no admission):
  * best_node[m] = argmax node per pod, -1 if none.  Host buffer out. */

@@ -25,7 +25,9 @@ EXPORTS = (
     "k8sgpu_place", "k8sgpu_place_upload", "k8sgpu_place_run", "k8sgpu_place_download", "k8sgpu_score_once",
     "k8sgpu_place_round_begin", "k8sgpu_place_round_score", "k8sgpu_place_round_admit", "k8sgpu_place_round_end",
     "k8sgpu_debug_sort_pairs", "k8sgpu_debug_exclusive_scan", "k8sgpu_exclusive_scan_noalloc",
+    "k8sgpu_place_gang",
 )
+ASSIGN_GANG = -3
 SCAN_NOALLOC_MAX_N = 1 << 24
 
 u32p = C.POINTER(C.c_uint32)
@@ -66,10 +68,14 @@ class Stats(C.Structure):
     _fields_ = [("rounds", C.c_uint32), ("placed", C.c_uint32), ("evals", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("device_ms", C.c_float), ("score_ms", C.c_float), ("score_evals", C.c_uint64),
-                ("score_launches", C.c_uint32), ("reserved", C.c_uint32)]
+                ("score_launches", C.c_uint32), ("gang_iterations", C.c_uint32)]
 
     def as_dict(self):
-        return {f: getattr(self, f) for f, _ in self._fields_ if f != "reserved"}
+        return {f: getattr(self, f) for f, _ in self._fields_}
+
+
+class GangTable(C.Structure):
+    _fields_ = [("n_gangs", C.c_uint32), ("gang_id", u32p), ("min_available", u32p)]
 
 
 class K8sGpuError(RuntimeError):
@@ -103,6 +109,8 @@ def load() -> C.CDLL:
         L.k8sgpu_reconcile_download.argtypes = [vp, C.POINTER(ReconcileOut)]
         L.k8sgpu_place.argtypes = [vp, C.POINTER(NodeTable), C.POINTER(PodTable), C.POINTER(Policy),
                                    C.POINTER(PlaceOut)]
+        L.k8sgpu_place_gang.argtypes = [vp, C.POINTER(NodeTable), C.POINTER(PodTable), C.POINTER(GangTable),
+                                        C.POINTER(Policy), C.POINTER(PlaceOut), i32p]
         L.k8sgpu_place_upload.argtypes = [vp, C.POINTER(NodeTable), C.POINTER(PodTable)]
         L.k8sgpu_place_run.argtypes = [vp, C.POINTER(Policy)]
         L.k8sgpu_place_download.argtypes = [vp, C.POINTER(PlaceOut)]
@@ -193,6 +201,22 @@ class Context:
         out, res = self._place_out(nt.n, pt.m)
         pol = Policy(flags, max_rounds)
         self._check(self._L.k8sgpu_place(self._h, C.byref(nt), C.byref(pt), C.byref(pol), C.byref(out)))
+        res.update(self.stats())
+        return res
+
+    def place_gang(self, nodes: dict, pods: dict, gang_id, min_available, flags: int = 0, max_rounds: int = 0) -> dict:
+        """All-or-nothing gangs on top of the placement rounds (k8sgpu_place_gang)."""
+        nt, k1 = node_table(nodes)
+        pt, k2 = pod_table(pods)
+        gid, gidp = _u32(gang_id)
+        mn, mnp = _u32(min_available)
+        gt = GangTable(len(mn), gidp, mnp)
+        out, res = self._place_out(nt.n, pt.m)
+        ok = np.zeros(len(mn), np.int32)
+        pol = Policy(flags, max_rounds)
+        self._check(self._L.k8sgpu_place_gang(self._h, C.byref(nt), C.byref(pt), C.byref(gt), C.byref(pol),
+                                              C.byref(out), ok.ctypes.data_as(i32p)))
+        res["gang_ok"] = ok
         res.update(self.stats())
         return res
 

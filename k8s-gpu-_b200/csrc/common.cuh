@@ -70,6 +70,8 @@ struct PlaceState {
     uint32_t rounds = 0;
     uint64_t evals = 0;
     uint32_t policy_flags = 0, max_rounds = 0;
+    bool nodeq_stale = true;  // packed node records do not reflect free_cols yet
+    DevBuf gang_id, gang_min, gang_count, gang_state;  // gang placement: [m], [g], [g], [2g] (rejected, newly)
     int timed = 0;        // scoring launches timed so far in this run
     uint64_t timed_evals = 0;
 };

@@ -25,7 +25,7 @@ struct __align__(16) NodeQ {  // what the inner loop reads; rebuilt from the fre
     uint32_t free_gpu_s;  // free_gpu, or 0xFFFFFFFF (= -1 signed) when the node is not schedulable
     uint32_t free_mcpu, free_mib;
     uint32_t sku_bit;     // 1 << sku_id
-    uint32_t zone_bit;    // 1 << zone_id
+    uint32_t zone_bit;    // 1 << (31 - zone_id): bit-reversed one-hot (see eval_pair RES = 3)
     uint32_t taint;
     uint32_t khi;         // 1<<31 | (0x7FFF - free_gpu) << 16 | (255 - cap_gpu) << 8 | (63 - n % 64) << 1
     uint32_t zrot;        // (zone_id - 7) mod 32: rotates the pod's one-hot preferred zone onto bit 7
@@ -34,7 +34,7 @@ static_assert(sizeof(NodeQ) == 32, "node record is 32 B: the algorithmic bytes p
 
 struct __align__(16) PodQ {
     uint32_t req_gpu, req_mcpu, req_mib;
-    uint32_t nsku, nzone, ntol;  // complements of sku_mask / zone_mask / tol_mask
+    uint32_t nsku, nzone, ntol;  // complements of sku_mask / zone_mask (bit-reversed) / tol_mask
     uint32_t pzb;                // 1 << pref_zone, or 0
     uint32_t rot;                // rot(p), DESIGN.md a12
 };
@@ -60,7 +60,7 @@ __global__ void pod_prep_kernel(const uint32_t *__restrict__ cols, uint32_t m, u
     q.req_mcpu = cols[1 * (size_t)m + p];
     q.req_mib = cols[2 * (size_t)m + p];
     q.nsku = ~cols[3 * (size_t)m + p];
-    q.nzone = ~cols[4 * (size_t)m + p];
+    q.nzone = __brev(~cols[4 * (size_t)m + p]);  // bit-reversed, like NodeQ::zone_bit
     q.ntol = ~cols[5 * (size_t)m + p];
     uint32_t pz = cols[6 * (size_t)m + p];
     q.pzb = pz < 32u ? (1u << pz) : 0u;
@@ -87,7 +87,7 @@ __device__ __forceinline__ NodeQ make_nodeq(const uint32_t *__restrict__ cols, c
         q.free_mcpu = fc;
         q.free_mib = fm;
         q.sku_bit = 1u << (sku & 31u);
-        q.zone_bit = 1u << (zone & 31u);
+        q.zone_bit = 0x80000000u >> (zone & 31u);
         q.taint = taint;
         q.khi = 0x80000000u | ((0x7FFFu - (fg & 0x7FFFu)) << 16) | ((255u - (cap & 255u)) << 8) |
                 ((63u - (i & 63u)) << 1);
@@ -153,6 +153,9 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
 //          OR says "some resource is short".  One ALU instruction fewer per eval.
 // RES = 2: as 1, and the running best is updated by a predicated mad (key * runtime 1 + 0), which
 //          ptxas keeps on the FMA pipe instead of turning it into an ALU select: 8 ALU ops/eval.
+// RES = 3: as 2, and the zone-preference bit comes from two multiplies instead of a funnel shift:
+//          pzb * zone_bit = 2^(31 + pref - zone) has bit 31 set exactly when pref == zone, and
+//          mul.hi by 2^8 brings that bit to position 7.  7 ALU + 6 FMA-pipe ops per eval.
 template <int RES>
 __device__ __forceinline__ void eval_pair(const uint4 &a, const uint4 &b, uint32_t rg, uint32_t rc, uint32_t rm,
                                           uint32_t nsku, uint32_t nzone, uint32_t ntol, uint32_t pzb,
@@ -197,7 +200,7 @@ __device__ __forceinline__ void eval_pair(const uint4 &a, const uint4 &b, uint32
             : "+r"(best)
             : "r"(a.w), "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.x), "r"(b.y), "r"(b.w), "r"(nsku), "r"(nzone),
               "r"(ntol), "r"(pzb), "r"(rg), "r"(rc), "r"(rm), "r"(b.z), "r"(negone));
-    } else {
+    } else if (RES == 2) {
         asm("{\n\t"
             ".reg .pred pf;\n\t"
             ".reg .b32 m, z, key, d1, d2, d3;\n\t"
@@ -218,6 +221,28 @@ __device__ __forceinline__ void eval_pair(const uint4 &a, const uint4 &b, uint32
             : "+r"(best)
             : "r"(a.w), "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.x), "r"(b.y), "r"(b.w), "r"(nsku), "r"(nzone),
               "r"(ntol), "r"(pzb), "r"(rg), "r"(rc), "r"(rm), "r"(b.z), "r"(negone), "r"(0u - negone));
+    } else {
+        asm("{\n\t"
+            ".reg .pred pf;\n\t"
+            ".reg .b32 m, z, key, d1, d2, d3;\n\t"
+            "and.b32 m, %1, %8;\n\t"
+            "lop3.b32 m, %5, %9, m, 0xEA;\n\t"
+            "lop3.b32 m, %6, %10, m, 0xEA;\n\t"
+            "mad.lo.s32 d1, %12, %16, %2;\n\t"
+            "mad.lo.s32 d2, %13, %16, %3;\n\t"
+            "mad.lo.s32 d3, %14, %16, %4;\n\t"
+            "setp.eq.u32 pf, m, 0;\n\t"
+            "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t"
+            "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
+            "mul.lo.u32 z, %11, %5;\n\t"
+            "mul.hi.u32 z, z, %18;\n\t"
+            "lop3.b32 key, z, 0x80, %15, 0xEA;\n\t"
+            "setp.gt.and.u32 pf, key, %0, pf;\n\t"
+            "@pf mad.lo.u32 %0, key, %17, 0;\n\t"
+            "}"
+            : "+r"(best)
+            : "r"(a.w), "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.x), "r"(b.y), "r"(b.w), "r"(nsku), "r"(nzone),
+              "r"(ntol), "r"(pzb), "r"(rg), "r"(rc), "r"(rm), "r"(b.z), "r"(negone), "r"(0u - negone), "r"((0u - negone) << 8));
     }
 }
 
@@ -798,6 +823,7 @@ static int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_
     st.evals = 0;
     st.timed = 0;
     st.timed_evals = 0;
+    st.nodeq_stale = true;
     K8S_CUDA(ctx, cudaMemsetAsync(st.counters.p, 0, 64 * 4, s));
     if (st.n)
         K8S_CUDA(ctx, cudaMemcpyAsync(st.free_cols.p, st.node_cols.p, 3 * (size_t)st.n * 4, cudaMemcpyDeviceToDevice, s));
@@ -857,10 +883,12 @@ static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_bes
 #define K8S_SCORE(P, R)                                                                                         \
     K8S_LAUNCH(ctx, (score_kernel<P, R>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
                st.active[st.cur].as<uint32_t>(), lo, hi, bk, st.n, use_atomic, 0xFFFFFFFFu)
-    if (ppt == 2 && res >= 2) K8S_SCORE(2, 2);
+    if (ppt == 2 && res >= 3) K8S_SCORE(2, 3);
+    else if (ppt == 2 && res == 2) K8S_SCORE(2, 2);
     else if (ppt == 2 && res == 1) K8S_SCORE(2, 1);
     else if (ppt == 2) K8S_SCORE(2, 0);
-    else if (res >= 2) K8S_SCORE(1, 2);
+    else if (res >= 3) K8S_SCORE(1, 3);
+    else if (res == 2) K8S_SCORE(1, 2);
     else if (res == 1) K8S_SCORE(1, 1);
     else K8S_SCORE(1, 0);
 #undef K8S_SCORE
@@ -1018,22 +1046,21 @@ static int round_end(k8sgpu_ctx *ctx, cudaStream_t s) {
     return K8SGPU_OK;
 }
 
-static int place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy) {
+// Rounds of score + admit until no pod is active (or max_rounds is reached).
+static int run_rounds(k8sgpu_ctx *ctx, cudaStream_t s) {
     PlaceState &st = ctx->place;
-    cudaStream_t s = ctx->stream;
-    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
-    int rc = round_begin(ctx, policy, s);
-    if (rc) return rc;
     // Admission as ONE cooperative launch per round (two launches per round in all): measured
     // ~3 % faster per config-3 step than the chain of ~20 small kernels.  K8SGPU_COOP=0 selects
     // the chain (the round-at-a-time API always uses it); both give identical results.
     bool coop = true;
     if (const char *e = getenv("K8SGPU_COOP")) coop = atoi(e) != 0;
+    int rc = K8SGPU_OK;
     while (st.n_active > 0 && (st.max_rounds == 0 || st.rounds < st.max_rounds)) {
         if (coop) {
-            rc = round_score(ctx, 0, st.n_active, nullptr, s, /*prep=*/st.rounds == 0, /*finalize=*/false);
+            rc = round_score(ctx, 0, st.n_active, nullptr, s, /*prep=*/st.nodeq_stale, /*finalize=*/false);
             if (rc) return rc;
-            rc = round_admit_coop(ctx, s);
+            rc = round_admit_coop(ctx, s);  // leaves the next round's node records ready
+            st.nodeq_stale = false;
         } else {
             rc = round_score(ctx, 0, st.n_active, st.best.as<int32_t>(), s);
             if (rc) return rc;
@@ -1041,9 +1068,154 @@ static int place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy) {
         }
         if (rc) return rc;
     }
+    return K8SGPU_OK;
+}
+
+static int place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy) {
+    cudaStream_t s = ctx->stream;
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
+    int rc = round_begin(ctx, policy, s);
+    if (rc) return rc;
+    rc = run_rounds(ctx, s);
+    if (rc) return rc;
     K8S_CUDA(ctx, cudaEventRecord(ctx->ev_end, s));
     rc = round_end(ctx, s);
     if (rc) return rc;
+    float ms = 0.f;
+    K8S_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
+    ctx->stats.device_ms = ms;
+    return K8SGPU_OK;
+}
+
+// ------------------------------------------------------------------ gang placement (f4)
+
+__global__ void gang_count_kernel(const int32_t *__restrict__ assign, const uint32_t *__restrict__ gang_id, uint32_t m,
+                                  uint32_t n_gangs, uint32_t *__restrict__ count, uint32_t *__restrict__ err) {
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= m) return;
+    uint32_t g = gang_id[p];
+    if (g == K8SGPU_NONE_U32) return;
+    if (g >= n_gangs) {
+        atomicOr(err, kErrPod);
+        return;
+    }
+    if (assign[p] >= 0) atomicAdd(&count[g], 1u);  // counts only: order-free
+}
+
+// state[g] = rejected so far, state[n_gangs + g] = rejected in this iteration; counters[3] += new rejections
+__global__ void gang_decide_kernel(const uint32_t *__restrict__ count, const uint32_t *__restrict__ min_available,
+                                   uint32_t n_gangs, uint32_t *__restrict__ state, uint32_t *__restrict__ counters) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_gangs) return;
+    uint32_t newly = (!state[g] && count[g] < min_available[g]) ? 1u : 0u;
+    state[n_gangs + g] = newly;
+    if (newly) {
+        state[g] = 1u;
+        atomicAdd(&counters[3], 1u);
+    }
+}
+
+// Pods of a gang rejected in this iteration give back what they reserved and are marked; pods
+// still unplaced whose gang survives are flagged for the retry list.
+__global__ void gang_release_kernel(int32_t *__restrict__ assign, const uint32_t *__restrict__ gang_id,
+                                    const PodQ *__restrict__ podq, uint32_t m, uint32_t n_gangs, uint32_t n_nodes,
+                                    const uint32_t *__restrict__ state, uint32_t *__restrict__ freec,
+                                    uint32_t *__restrict__ retry_flags) {
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= m) return;
+    const uint32_t g = gang_id[p];
+    int32_t a = assign[p];
+    if (g != K8SGPU_NONE_U32 && g < n_gangs && state[n_gangs + g]) {
+        if (a >= 0) {  // commutative integer atomics: the result does not depend on order
+            const PodQ *q = podq + p;
+            if (q->req_gpu) atomicAdd(&freec[a], q->req_gpu);
+            if (q->req_mcpu) atomicAdd(&freec[(size_t)n_nodes + a], q->req_mcpu);
+            if (q->req_mib) atomicAdd(&freec[2 * (size_t)n_nodes + a], q->req_mib);
+        }
+        assign[p] = a = K8SGPU_ASSIGN_GANG;
+    }
+    const bool survives = g == K8SGPU_NONE_U32 || (g < n_gangs && !state[g]);
+    const uint32_t retry = (a == K8SGPU_ASSIGN_NONE && survives) ? 1u : 0u;
+    retry_flags[p] = retry;
+    if (retry) assign[p] = K8SGPU_ASSIGN_PENDING;
+}
+
+__global__ void gang_retry_compact_kernel(const uint32_t *__restrict__ flags, const uint32_t *__restrict__ offs,
+                                          uint32_t m, uint32_t *__restrict__ active) {
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < m && flags[p]) active[offs[p]] = p;
+}
+
+__global__ void gang_unretry_kernel(int32_t *__restrict__ assign, const uint32_t *__restrict__ flags, uint32_t m) {
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < m && flags[p]) assign[p] = K8SGPU_ASSIGN_NONE;
+}
+
+__global__ void gang_ok_kernel(const uint32_t *__restrict__ state, uint32_t n_gangs, int32_t *__restrict__ ok) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g < n_gangs) ok[g] = state[g] ? 0 : 1;
+}
+
+static int place_gang_run(k8sgpu_ctx *ctx, const k8sgpu_gang_table *gangs, const k8sgpu_policy *policy) {
+    PlaceState &st = ctx->place;
+    cudaStream_t s = ctx->stream;
+    const uint32_t G = gangs->n_gangs, M = st.m;
+    if (M && !gangs->gang_id) return fail(ctx, K8SGPU_E_ARG, "place_gang: gang_id is NULL");
+    if (G && !gangs->min_available) return fail(ctx, K8SGPU_E_ARG, "place_gang: min_available is NULL");
+    K8S_CUDA(ctx, st.gang_id.reserve((size_t)M * 4 + 16));
+    K8S_CUDA(ctx, st.gang_min.reserve((size_t)G * 4 + 16));
+    K8S_CUDA(ctx, st.gang_count.reserve((size_t)G * 4 + 16));
+    K8S_CUDA(ctx, st.gang_state.reserve((size_t)G * 8 + 16));
+    if (M) K8S_CUDA(ctx, cudaMemcpyAsync(st.gang_id.p, gangs->gang_id, (size_t)M * 4, cudaMemcpyHostToDevice, s));
+    if (G) K8S_CUDA(ctx, cudaMemcpyAsync(st.gang_min.p, gangs->min_available, (size_t)G * 4, cudaMemcpyHostToDevice, s));
+    ctx->stats.h2d_bytes += ((uint64_t)M + G) * 4;
+    K8S_CUDA(ctx, cudaMemsetAsync(st.gang_state.p, 0, (size_t)G * 8 + 16, s));
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
+    int rc = round_begin(ctx, policy, s);
+    if (rc) return rc;
+    uint32_t *cnts = st.counters.as<uint32_t>();
+    uint32_t iters = 0;
+    for (;;) {
+        rc = run_rounds(ctx, s);  // step 1: policy v0 rounds over the current candidates
+        if (rc) return rc;
+        ++iters;
+        if (st.n_active > 0 || M == 0) break;  // max_rounds reached: no verdicts on half a placement
+        // step 2: count placed members, reject gangs below min_available, release their reservations
+        K8S_CUDA(ctx, cudaMemsetAsync(st.gang_count.p, 0, (size_t)G * 4 + 16, s));
+        K8S_CUDA(ctx, cudaMemsetAsync(cnts + 3, 0, 4, s));
+        K8S_LAUNCH(ctx, gang_count_kernel, ceil_div(M, 256), 256, 0, s, st.assign.as<int32_t>(),
+                   st.gang_id.as<uint32_t>(), M, G, st.gang_count.as<uint32_t>(), cnts);
+        if (G)
+            K8S_LAUNCH(ctx, gang_decide_kernel, ceil_div(G, 256), 256, 0, s, st.gang_count.as<uint32_t>(),
+                       st.gang_min.as<uint32_t>(), G, st.gang_state.as<uint32_t>(), cnts);
+        uint32_t *flags = st.flags.as<uint32_t>(), *offs = flags + st.m;
+        K8S_LAUNCH(ctx, gang_release_kernel, ceil_div(M, 256), 256, 0, s, st.assign.as<int32_t>(),
+                   st.gang_id.as<uint32_t>(), st.podq.as<PodQ>(), M, G, st.n, st.gang_state.as<uint32_t>(),
+                   st.free_cols.as<uint32_t>(), flags);
+        // step 3: the retry list, ascending in pod index (stable compaction)
+        rc = exclusive_scan_u32(ctx, s, flags, offs, M, st.scan_tmp, cnts + 1);
+        if (rc) return rc;
+        K8S_LAUNCH(ctx, gang_retry_compact_kernel, ceil_div(M, 256), 256, 0, s, flags, offs, M,
+                   st.active[st.cur].as<uint32_t>());
+        K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, cnts, 16, cudaMemcpyDeviceToHost, s));
+        K8S_CUDA(ctx, cudaStreamSynchronize(s));
+        if (ctx->h_pinned[0] != 0u) return fail(ctx, K8SGPU_E_ARG, "place_gang: a gang id is >= n_gangs, or a table is outside the input domain");
+        const uint32_t n_new = ctx->h_pinned[3], n_retry = ctx->h_pinned[1];
+        if (n_new == 0) {  // nothing was rejected: the flagged pods keep their verdict (-1)
+            if (n_retry) {
+                // they were marked PENDING for a retry that will not happen: restore -1
+                K8S_LAUNCH(ctx, gang_unretry_kernel, ceil_div(M, 256), 256, 0, s, st.assign.as<int32_t>(), flags, M);
+            }
+            break;
+        }
+        st.n_active = n_retry;
+        st.nodeq_stale = true;  // free columns changed under the packed records
+        if (n_retry == 0) break;
+    }
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_end, s));
+    rc = round_end(ctx, s);
+    if (rc) return rc;
+    ctx->stats.gang_iterations = iters;
     float ms = 0.f;
     K8S_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
     ctx->stats.device_ms = ms;
@@ -1103,6 +1275,27 @@ extern "C" int k8sgpu_place(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, con
     if (rc) return rc;
     rc = place_run(ctx, policy);
     if (rc) return rc;
+    return place_download(ctx, out);
+}
+
+extern "C" int k8sgpu_place_gang(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods,
+                                 const k8sgpu_gang_table *gangs, const k8sgpu_policy *policy, k8sgpu_place_out *out,
+                                 int32_t *gang_ok) {
+    K8S_ENTER(ctx);
+    reset_call_stats(ctx);
+    if (!gangs) return fail(ctx, K8SGPU_E_ARG, "place_gang: NULL gang table");
+    int rc = place_upload(ctx, nodes, pods);
+    if (rc) return rc;
+    rc = place_gang_run(ctx, gangs, policy);
+    if (rc) return rc;
+    if (gang_ok && gangs->n_gangs) {
+        PlaceState &st = ctx->place;
+        int32_t *d_ok = reinterpret_cast<int32_t *>(st.gang_count.p);  // reuse: counts are no longer needed
+        K8S_LAUNCH(ctx, gang_ok_kernel, ceil_div(gangs->n_gangs, 256), 256, 0, ctx->stream,
+                   st.gang_state.as<uint32_t>(), gangs->n_gangs, d_ok);
+        K8S_CUDA(ctx, cudaMemcpyAsync(gang_ok, d_ok, (size_t)gangs->n_gangs * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        ctx->stats.d2h_bytes += (uint64_t)gangs->n_gangs * 4;
+    }
     return place_download(ctx, out);
 }
 

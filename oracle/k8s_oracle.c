@@ -196,6 +196,79 @@ int orc_place(const orc_node_table *nodes, const orc_pod_table *pods, uint32_t p
     return 0;
 }
 
+/* all-or-nothing gangs on top of the round loop (see k8s_oracle.h). */
+int orc_place_gang(const orc_node_table *nodes, const orc_pod_table *pods, const uint32_t *gang_id,
+                   const uint32_t *min_available, uint32_t n_gangs, uint32_t policy_flags, uint32_t max_rounds,
+                   int nthreads, int32_t *assign, uint32_t *fg, uint32_t *fc, uint32_t *fm, int32_t *gang_ok,
+                   orc_place_stats *stats, uint32_t *iterations) {
+    if (orc_validate_tables(nodes, pods) != 0) return -1;
+    const uint32_t N = nodes->n, M = pods->m;
+    for (uint32_t p = 0; p < M; ++p)
+        if (gang_id[p] != ORC_NONE_U32 && gang_id[p] >= n_gangs) return -1;
+    memcpy(fg, nodes->free_gpu, (size_t)N * 4);
+    memcpy(fc, nodes->free_mcpu, (size_t)N * 4);
+    memcpy(fm, nodes->free_mib, (size_t)N * 4);
+    uint32_t *act = (uint32_t *)malloc(((size_t)M + 1) * 4);
+    uint32_t *nxt = (uint32_t *)malloc(((size_t)M + 1) * 4);
+    int32_t *best = (int32_t *)malloc(((size_t)M + 1) * 4);
+    uint32_t *count = (uint32_t *)calloc((size_t)n_gangs + 1, 4);
+    uint8_t *rejected = (uint8_t *)calloc((size_t)n_gangs + 1, 1);
+    uint8_t *newly = (uint8_t *)calloc((size_t)n_gangs + 1, 1);
+    uint32_t na = M, rounds = 0, iters = 0;
+    uint64_t evals = 0;
+    for (uint32_t p = 0; p < M; ++p) {
+        act[p] = p;
+        assign[p] = ORC_ASSIGN_PENDING;
+    }
+    for (;;) {
+        while (na > 0 && (max_rounds == 0 || rounds < max_rounds)) {  /* step 1: policy v0 rounds */
+            orc_score_round(nodes, fg, fc, fm, pods, act, na, policy_flags, nthreads, best);
+            evals += (uint64_t)na * N;
+            uint32_t nn = orc_admit_round(N, fg, fc, fm, pods, act, na, best, assign, nxt);
+            uint32_t *t = act; act = nxt; nxt = t;
+            na = nn;
+            ++rounds;
+        }
+        ++iters;
+        if (na > 0) break; /* max_rounds reached: leave the rest pending, no verdicts on half a placement */
+        for (uint32_t g = 0; g < n_gangs; ++g) count[g] = 0;
+        for (uint32_t p = 0; p < M; ++p)
+            if (gang_id[p] != ORC_NONE_U32 && assign[p] >= 0) count[gang_id[p]]++;
+        uint32_t n_new = 0;
+        for (uint32_t g = 0; g < n_gangs; ++g) { /* step 2 */
+            newly[g] = (!rejected[g] && count[g] < min_available[g]) ? 1 : 0;
+            if (newly[g]) { rejected[g] = 1; ++n_new; }
+        }
+        if (n_new == 0) break;
+        for (uint32_t p = 0; p < M; ++p) {
+            uint32_t g = gang_id[p];
+            if (g == ORC_NONE_U32 || !newly[g]) continue;
+            if (assign[p] >= 0) { /* release the reservation */
+                fg[assign[p]] += pods->req_gpu[p];
+                fc[assign[p]] += pods->req_mcpu[p];
+                fm[assign[p]] += pods->req_mib[p];
+            }
+            assign[p] = ORC_ASSIGN_GANG;
+        }
+        na = 0; /* step 3: retry what is still unplaced and not rejected */
+        for (uint32_t p = 0; p < M; ++p) {
+            uint32_t g = gang_id[p];
+            if (assign[p] == ORC_ASSIGN_NONE && (g == ORC_NONE_U32 || !rejected[g])) {
+                act[na++] = p;
+                assign[p] = ORC_ASSIGN_PENDING;
+            }
+        }
+        if (na == 0) break;
+    }
+    uint32_t placed = 0;
+    for (uint32_t p = 0; p < M; ++p) placed += assign[p] >= 0;
+    for (uint32_t g = 0; g < n_gangs; ++g) gang_ok[g] = rejected[g] ? 0 : 1;
+    if (stats) { stats->rounds = rounds; stats->placed = placed; stats->evals = evals; }
+    if (iterations) *iterations = iters;
+    free(act); free(nxt); free(best); free(count); free(rejected); free(newly);
+    return 0;
+}
+
 /* ------------------------------------------------------------------ batch reconcile */
 typedef struct {
     const orc_vm_table *vms;

@@ -84,6 +84,21 @@ int orc_place(const orc_node_table *nodes, const orc_pod_table *pods, uint32_t p
               uint32_t max_rounds, int nthreads, int32_t *assign, uint32_t *out_free_gpu,
               uint32_t *out_free_mcpu, uint32_t *out_free_mib, orc_place_stats *stats);
 
+/* Gang placement (the reference only shows minAvailable: 1,
+ * GPU调度平台搭建.md:648).  Build-defined, layered on orc_place's rounds:
+ *   1. place every candidate pod (policy v0 rounds) -- tentative;
+ *   2. a gang with fewer placed members than min_available[g] is REJECTED for good: its pods get
+ *      ORC_ASSIGN_GANG and what they had reserved is released;
+ *   3. pods left unplaced (-1) whose gang is not rejected are retried against the released
+ *      capacity; repeat from 2 until an iteration rejects no new gang.
+ * gang_id[p] == ORC_NONE_U32: pod belongs to no gang.  gang_ok[g] = 1 if gang g was kept.
+ * Returns 0, -1 on invalid tables or a gang id >= n_gangs. */
+#define ORC_ASSIGN_GANG (-3)
+int orc_place_gang(const orc_node_table *nodes, const orc_pod_table *pods, const uint32_t *gang_id,
+                   const uint32_t *min_available, uint32_t n_gangs, uint32_t policy_flags, uint32_t max_rounds,
+                   int nthreads, int32_t *assign, uint32_t *out_free_gpu, uint32_t *out_free_mcpu,
+                   uint32_t *out_free_mib, int32_t *gang_ok, orc_place_stats *stats, uint32_t *iterations);
+
 /* ---- batch reconcile */
 typedef struct {
     uint32_t p;

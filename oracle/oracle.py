@@ -20,6 +20,7 @@ POD_COLS = ("req_gpu", "req_mcpu", "req_mib", "sku_mask", "zone_mask", "tol_mask
 NONE_U32 = 0xFFFFFFFF
 ASSIGN_NONE = -1
 ASSIGN_PENDING = -2
+ASSIGN_GANG = -3
 POLICY_ROT_ZERO = 1
 
 u32p = C.POINTER(C.c_uint32)
@@ -89,6 +90,8 @@ def lib() -> C.CDLL:
                                       i32p, i32p, u32p]
         L.orc_place.argtypes = [C.POINTER(NodeTable), C.POINTER(PodTable), C.c_uint32, C.c_uint32, C.c_int,
                                 i32p, u32p, u32p, u32p, C.POINTER(PlaceStats)]
+        L.orc_place_gang.argtypes = [C.POINTER(NodeTable), C.POINTER(PodTable), u32p, u32p, C.c_uint32, C.c_uint32,
+                                     C.c_uint32, C.c_int, i32p, u32p, u32p, u32p, i32p, C.POINTER(PlaceStats), u32p]
         L.orc_reconcile_batch.argtypes = [C.POINTER(PoolTable), C.POINTER(VmTable), C.c_uint32, C.c_int,
                                           C.POINTER(ReconcileOut)]
         for f in ("orc_arm_new", "orc_cluster_new"):
@@ -210,6 +213,24 @@ def place(nodes, pods, flags: int = 0, max_rounds: int = 0, nthreads: int = 1):
         raise ValueError("oracle: tables outside the input domain")
     return {"assign": assign, "free_gpu": fg, "free_mcpu": fc, "free_mib": fm,
             "rounds": int(st.rounds), "placed": int(st.placed), "evals": int(st.evals)}
+
+
+def place_gang(nodes, pods, gang_id, min_available, flags: int = 0, max_rounds: int = 0, nthreads: int = 1):
+    nt, k1 = _node_table(nodes)
+    pt, k2 = _pod_table(pods)
+    gid, gidp = _u32(gang_id)
+    mn, mnp = _u32(min_available)
+    assign = np.empty(pt.m, dtype=np.int32)
+    fg = np.empty(nt.n, dtype=np.uint32); fc = np.empty(nt.n, dtype=np.uint32); fm = np.empty(nt.n, dtype=np.uint32)
+    ok = np.empty(len(mn), dtype=np.int32)
+    st, it = PlaceStats(), C.c_uint32()
+    rc = lib().orc_place_gang(C.byref(nt), C.byref(pt), gidp, mnp, len(mn), flags, max_rounds, nthreads,
+                              assign.ctypes.data_as(i32p), fg.ctypes.data_as(u32p), fc.ctypes.data_as(u32p),
+                              fm.ctypes.data_as(u32p), ok.ctypes.data_as(i32p), C.byref(st), C.byref(it))
+    if rc != 0:
+        raise ValueError("oracle: tables outside the input domain or bad gang id")
+    return {"assign": assign, "free_gpu": fg, "free_mcpu": fc, "free_mib": fm, "gang_ok": ok,
+            "rounds": int(st.rounds), "placed": int(st.placed), "evals": int(st.evals), "iterations": int(it.value)}
 
 
 def reconcile_batch(desired, pool_owner_id, vm_owner_id, vm_flags, n_owner_ids, vm_ordinal=None,
