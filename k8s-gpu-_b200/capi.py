@@ -91,10 +91,11 @@ def load() -> C.CDLL:
     """dlopen libk8sgpu.so (built in-tree by __graft_entry__.build / csrc/Makefile)."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
-            raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+        path = os.environ.get("K8SGPU_LIB", LIB_PATH)  # developer override: a differently tuned build
+        if not os.path.exists(path):
+            raise ImportError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                               "(there is no fallback path)")
-        L = C.CDLL(LIB_PATH)
+        L = C.CDLL(path)
         vp = C.c_void_p
         L.k8sgpu_abi_version.restype = C.c_int
         L.k8sgpu_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]

@@ -13,7 +13,10 @@
 namespace k8sgpu {
 
 constexpr int kMaxTimedRounds = 512;   // scoring-kernel event pairs kept per run
-constexpr uint32_t kNodeTile = 256;    // nodes per shared-memory tile (32 B each)
+#ifndef K8S_NODE_TILE
+#define K8S_NODE_TILE 256
+#endif
+constexpr uint32_t kNodeTile = K8S_NODE_TILE;  // nodes per shared-memory tile (32 B each)
 constexpr uint32_t kSortTile = 2048;   // pairs per radix-sort block
 constexpr int kSortThreads = 256;
 constexpr int kScanThreads = 256;
