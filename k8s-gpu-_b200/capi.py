@@ -284,16 +284,18 @@ class Context:
         return PoolTable(len(d), dp, pop), VmTable(len(vo), vop, vfp, vrp), (d, po, vo, vf, vr)
 
     @staticmethod
-    def _rec_out(P, V, create_cap, members=True, ordinals=True):
-        o = {"pool_of": np.empty(V, np.int32), "current": np.empty(P, np.int32), "delta": np.empty(P, np.int32),
-             "ready": np.empty(P, np.int32), "create_count": np.empty(P, np.int32),
-             "victim_off": np.zeros(P + 1, np.int32), "victim_vm": np.zeros(V + 1, np.uint32)}
+    def _rec_out(P, V, create_cap, members=True, ordinals=True, alloc=None):
+        """alloc(n, dtype) -> array: lets a caller hand in pinned or reused host buffers."""
+        mk = alloc or (lambda n, dt: np.zeros(n, dt))
+        o = {"pool_of": mk(V, np.int32), "current": mk(P, np.int32), "delta": mk(P, np.int32),
+             "ready": mk(P, np.int32), "create_count": mk(P, np.int32),
+             "victim_off": mk(P + 1, np.int32), "victim_vm": mk(V + 1, np.uint32)}
         if members:
-            o["member_off"] = np.zeros(P + 1, np.int32)
-            o["member_vm"] = np.zeros(V + 1, np.uint32)
+            o["member_off"] = mk(P + 1, np.int32)
+            o["member_vm"] = mk(V + 1, np.uint32)
         if ordinals:
-            o["create_off"] = np.zeros(P + 1, np.int32)
-            o["create_ordinal"] = np.zeros(create_cap + 1, np.uint32)
+            o["create_off"] = mk(P + 1, np.int32)
+            o["create_ordinal"] = mk(create_cap + 1, np.uint32)
         out = ReconcileOut()
         for k, v in o.items():
             setattr(out, k, v.ctypes.data_as(i32p if v.dtype == np.int32 else u32p))
@@ -310,12 +312,13 @@ class Context:
         return o
 
     def reconcile_batch(self, desired, pool_owner_id, vm_owner_id, vm_flags, n_owner_ids, vm_ordinal=None,
-                        members=True, ordinals=True, create_capacity=None) -> dict:
+                        members=True, ordinals=True, create_capacity=None, alloc=None, trim=True) -> dict:
         pools, vms, keep = self._rec_tables(desired, pool_owner_id, vm_owner_id, vm_flags, vm_ordinal)
         cap = int(np.maximum(keep[0].astype(np.int64), 0).sum()) if create_capacity is None else create_capacity
-        out, o = self._rec_out(pools.p, vms.v, cap, members, ordinals)
+        out, o = self._rec_out(pools.p, vms.v, cap, members, ordinals, alloc)
         self._check(self._L.k8sgpu_reconcile_batch(self._h, C.byref(pools), C.byref(vms), n_owner_ids, C.byref(out)))
-        o = self._rec_trim(o, pools.p)
+        if trim:
+            o = self._rec_trim(o, pools.p)
         o.update(self.stats())
         return o
 

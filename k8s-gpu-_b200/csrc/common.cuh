@@ -89,6 +89,8 @@ struct ReconcileState {
     SortScratch sort;
     DevBuf scan_tmp;
     uint32_t n_victims = 0, n_members = 0, n_creates = 0;
+    const uint32_t *sorted_vals = nullptr;  // rows grouped by pool (member_vm) after the last run
+    int coop_blocks_per_sm = 0;             // occupancy of reconcile_coop_kernel (0 = not queried)
 };
 
 }  // namespace k8sgpu

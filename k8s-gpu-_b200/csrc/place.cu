@@ -11,15 +11,11 @@
 //   admit       : stable sort of proposals by node, segmented prefix sums in pod order,
 //                 S <= free test (a13), free -= admitted, stable compaction of the active list.
 // Integer only; no atomics decide any result except commutative max / add.
-#include <cooperative_groups.h>
-
 #include <cstdlib>
 
 #include "prims.cuh"
 
 namespace k8sgpu {
-
-namespace cg = cooperative_groups;
 
 struct __align__(16) NodeQ {  // what the inner loop reads; rebuilt from the free columns each round
     uint32_t free_gpu_s;  // free_gpu, or 0xFFFFFFFF (= -1 signed) when the node is not schedulable
@@ -609,34 +605,6 @@ struct AdmitArgs {
     int bits;
     unsigned long long *prof;  // optional: %globaltimer at each phase boundary (CTA 0), else null
 };
-
-// Exclusive scan of n u32 by the whole grid; every CTA must call it.  Ends with a grid barrier.
-__device__ __forceinline__ void coop_exclusive_scan(cg::grid_group &grid, const uint32_t *in, uint32_t *out, uint32_t n,
-                                                    uint32_t *sums, uint32_t *total) {
-    const uint32_t nt = (n + kScanTile - 1) / kScanTile;
-    if (nt <= 16) {  // small: CTA 0 walks it
-        if (blockIdx.x == 0) {
-            uint32_t carry = 0;
-            for (uint32_t t = 0; t < nt; ++t) carry = block_scan_tile(in, out, t * kScanTile, n, carry, true);
-            if (threadIdx.x == 0 && total) *total = carry;
-        }
-        grid.sync();
-        return;
-    }
-    for (uint32_t t = blockIdx.x; t < nt; t += gridDim.x) {
-        uint32_t tot = block_scan_tile(in, nullptr, t * kScanTile, n, 0u, false);
-        if (threadIdx.x == 0) sums[t] = tot;
-    }
-    grid.sync();
-    if (blockIdx.x == 0) {  // nt <= 2^31 / 2048: one CTA scans the tile sums in place
-        uint32_t carry = 0;
-        for (uint32_t t = 0; t * kScanTile < nt; ++t) carry = block_scan_tile(sums, sums, t * kScanTile, nt, carry, true);
-        if (threadIdx.x == 0 && total) *total = carry;
-    }
-    grid.sync();
-    for (uint32_t t = blockIdx.x; t < nt; t += gridDim.x) block_scan_tile(in, out, t * kScanTile, n, sums[t], true);
-    grid.sync();
-}
 
 __device__ __forceinline__ void prof_mark(const AdmitArgs &a, int slot) {
     if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) {

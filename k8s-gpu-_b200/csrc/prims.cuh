@@ -2,9 +2,13 @@
 // against a *virtual* tile index so that the same code serves the one-tile-per-CTA kernels in
 // primitives.cu and the persistent cooperative admission kernel in place.cu.
 #pragma once
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace k8sgpu {
+
+namespace cg = cooperative_groups;
 
 __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t x, int lane) {
 #pragma unroll
@@ -173,6 +177,34 @@ __device__ __forceinline__ void sort_scatter_tile(
         }
     }
     __syncthreads();  // shared staging is reused by the caller's next tile
+}
+
+// Exclusive scan of n u32 by the whole grid; every CTA must call it.  Ends with a grid barrier.
+__device__ __forceinline__ void coop_exclusive_scan(cg::grid_group &grid, const uint32_t *in, uint32_t *out, uint32_t n,
+                                                    uint32_t *sums, uint32_t *total) {
+    const uint32_t nt = (n + kScanTile - 1) / kScanTile;
+    if (nt <= 16) {  // small: CTA 0 walks it
+        if (blockIdx.x == 0) {
+            uint32_t carry = 0;
+            for (uint32_t t = 0; t < nt; ++t) carry = block_scan_tile(in, out, t * kScanTile, n, carry, true);
+            if (threadIdx.x == 0 && total) *total = carry;
+        }
+        grid.sync();
+        return;
+    }
+    for (uint32_t t = blockIdx.x; t < nt; t += gridDim.x) {
+        uint32_t tot = block_scan_tile(in, nullptr, t * kScanTile, n, 0u, false);
+        if (threadIdx.x == 0) sums[t] = tot;
+    }
+    grid.sync();
+    if (blockIdx.x == 0) {  // nt <= 2^31 / 2048: one CTA scans the tile sums in place
+        uint32_t carry = 0;
+        for (uint32_t t = 0; t * kScanTile < nt; ++t) carry = block_scan_tile(sums, sums, t * kScanTile, nt, carry, true);
+        if (threadIdx.x == 0 && total) *total = carry;
+    }
+    grid.sync();
+    for (uint32_t t = blockIdx.x; t < nt; t += gridDim.x) block_scan_tile(in, out, t * kScanTile, n, sums[t], true);
+    grid.sync();
 }
 
 }  // namespace k8sgpu

@@ -9,7 +9,9 @@
 //   names of new VMs (README.md:204)         -> ordinal bitmap kernels
 //   Status.ReadyReplicas = currentCount (README.md:225)    -> ready == current
 // createVM / deleteVM themselves are ARM calls (network) and stay on the host.
-#include "common.cuh"
+#include <cstdlib>
+
+#include "prims.cuh"
 
 namespace k8sgpu {
 
@@ -128,13 +130,13 @@ __global__ void ordinal_mark_kernel(const uint32_t *__restrict__ keys, const uin
 }
 
 // One warp per pool: emit the create_count lowest clear bits of the pool's ordinal bitmap.
-__global__ void ordinal_emit_kernel(uint32_t P, const int32_t *__restrict__ current,
-                                    const int32_t *__restrict__ create_count, const uint32_t *__restrict__ word_off,
-                                    const uint32_t *__restrict__ bitmap, const int32_t *__restrict__ create_off,
-                                    uint32_t *__restrict__ create_ordinal) {
-    const uint32_t p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+__device__ __forceinline__ void ordinal_emit_pool(uint32_t p, const int32_t *__restrict__ current,
+                                                  const int32_t *__restrict__ create_count,
+                                                  const uint32_t *__restrict__ word_off,
+                                                  const uint32_t *__restrict__ bitmap,
+                                                  const int32_t *__restrict__ create_off,
+                                                  uint32_t *__restrict__ create_ordinal) {
     const int lane = threadIdx.x & 31;
-    if (p >= P) return;
     const uint32_t cc = (uint32_t)create_count[p];
     if (!cc) return;
     const uint32_t span = (uint32_t)current[p] + cc, words = (span + 31u) / 32u;
@@ -163,6 +165,119 @@ __global__ void ordinal_emit_kernel(uint32_t P, const int32_t *__restrict__ curr
         }
         emitted += __shfl_sync(0xFFFFFFFFu, inc, 31);
     }
+}
+
+__global__ void ordinal_emit_kernel(uint32_t P, const int32_t *__restrict__ current,
+                                    const int32_t *__restrict__ create_count, const uint32_t *__restrict__ word_off,
+                                    const uint32_t *__restrict__ bitmap, const int32_t *__restrict__ create_off,
+                                    uint32_t *__restrict__ create_ordinal) {
+    const uint32_t p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (p < P) ordinal_emit_pool(p, current, create_count, word_off, bitmap, create_off, create_ordinal);
+}
+
+// ------------------------------------------------------------------ one launch for the whole pass
+//
+// Config 2 (1k pools x 100k VMs) is 1.2 MB of work: as ~16 dependent kernels it is pure launch
+// latency.  reconcile_coop_kernel runs the same phases inside ONE cooperative launch with grid
+// barriers between them (same tile functions as the chain, so the results are identical).
+
+struct RecArgs {
+    const int32_t *desired;
+    const uint32_t *pool_owner, *vm_owner, *vm_flags, *vm_ordinal;  // vm_ordinal may be null
+    int32_t *lut;  // pre-set to -1 by the host
+    int32_t *pool_of, *current, *delta, *create_count, *member_off, *victim_off, *create_off;
+    uint32_t *keys, *vals, *keys_alt, *vals_alt, *hist, *hist_scan, *scan_sums;
+    uint32_t *kvict, *span_words, *word_off, *victim_vm, *bitmap /* pre-zeroed */, *create_ordinal, *counters;
+    uint32_t P, V, n_owner_ids;
+    int bits, want_ordinals;
+};
+
+__global__ void __launch_bounds__(256) reconcile_coop_kernel(RecArgs a) {
+    cg::grid_group grid = cg::this_grid();
+    const uint32_t tid = threadIdx.x, cta = blockIdx.x, G = gridDim.x, gtid = cta * 256 + tid, gsz = G * 256;
+    const uint32_t P = a.P, V = a.V;
+    const uint32_t nb = (V + kSortTile - 1) / kSortTile;
+
+    for (uint32_t p = gtid; p < P; p += gsz) {  // owner id -> pool row
+        if (a.desired[p] < 0) atomicOr(a.counters, kErrNegDesired);
+        uint32_t o = a.pool_owner[p];
+        if (o < a.n_owner_ids && atomicCAS(&a.lut[o], -1, (int32_t)p) != -1) atomicOr(a.counters, kErrDupOwner);
+    }
+    grid.sync();
+    for (uint32_t vt = cta; vt < nb; vt += G) {  // tag filter + sort keys + digit-0 histogram
+#pragma unroll
+        for (uint32_t r = 0; r < kSortTile / 256; ++r) {
+            uint32_t v = vt * kSortTile + r * 256 + tid;
+            if (v < V) {
+                int32_t p = match_one(a.vm_owner[v], a.vm_flags[v], a.n_owner_ids, a.lut);
+                a.pool_of[v] = p;
+                a.keys[v] = p < 0 ? P : (uint32_t)p;
+                a.vals[v] = v;
+            }
+        }
+        __syncthreads();
+        sort_hist_tile(a.keys, V, 0, 0xFFu, a.hist, nb, vt);
+    }
+    grid.sync();
+    uint32_t *sk = a.keys, *sv = a.vals, *dk = a.keys_alt, *dv = a.vals_alt;
+    if (V > 0) {
+        for (int shift = 0; shift < a.bits; shift += 8) {
+            const int w = a.bits - shift < 8 ? a.bits - shift : 8;
+            const uint32_t mask = (1u << w) - 1u;
+            if (shift > 0) {
+                for (uint32_t vt = cta; vt < nb; vt += G) sort_hist_tile(sk, V, shift, mask, a.hist, nb, vt);
+                grid.sync();
+            }
+            coop_exclusive_scan(grid, a.hist, a.hist_scan, nb * 256u, a.scan_sums, nullptr);
+            for (uint32_t vt = cta; vt < nb; vt += G) sort_scatter_tile(sk, sv, dk, dv, V, shift, mask, a.hist_scan, nb, vt);
+            grid.sync();
+            uint32_t *t;
+            t = sk; sk = dk; dk = t;
+            t = sv; sv = dv; dv = t;
+        }
+    }
+    // (the host knows where the sorted pairs ended up: in keys/vals after an even number of passes)
+    for (uint32_t p = gtid; p <= P; p += gsz) {  // existingVMs of pool p = sorted rows [member_off[p], member_off[p+1])
+        uint32_t lo = 0, hi = V;
+        while (lo < hi) {
+            uint32_t mid = lo + ((hi - lo) >> 1);
+            if (sk[mid] < p) lo = mid + 1;
+            else hi = mid;
+        }
+        a.member_off[p] = (int32_t)lo;
+    }
+    grid.sync();
+    for (uint32_t p = gtid; p < P; p += gsz) {  // README.md:195-212
+        int32_t cur = a.member_off[p + 1] - a.member_off[p], d = a.desired[p] - cur;
+        a.current[p] = cur;
+        a.delta[p] = d;
+        int32_t cc = d > 0 ? d : 0;
+        a.create_count[p] = cc;
+        a.kvict[p] = d < 0 ? (uint32_t)(-d) : 0u;
+        a.span_words[p] = cc ? ((uint32_t)cur + (uint32_t)cc + 31u) / 32u : 0u;
+    }
+    grid.sync();
+    coop_exclusive_scan(grid, a.kvict, (uint32_t *)a.victim_off, P, a.scan_sums, (uint32_t *)a.victim_off + P);
+    coop_exclusive_scan(grid, (const uint32_t *)a.create_count, (uint32_t *)a.create_off, P, a.scan_sums,
+                        (uint32_t *)a.create_off + P);
+    if (a.want_ordinals) coop_exclusive_scan(grid, a.span_words, a.word_off, P, a.scan_sums, a.counters + 4);
+    for (uint32_t i = gtid; i < V; i += gsz) {  // victims (README.md:214) and used-ordinal bits
+        uint32_t p = sk[i];
+        if (p >= P) continue;
+        uint32_t r = i - (uint32_t)a.member_off[p];
+        if (r < a.kvict[p]) a.victim_vm[(uint32_t)a.victim_off[p] + r] = sv[i];
+        if (a.want_ordinals && a.vm_ordinal) {
+            uint32_t cc = (uint32_t)a.create_count[p];
+            if (cc) {
+                uint32_t o = a.vm_ordinal[sv[i]];
+                if (o < (uint32_t)a.current[p] + cc) atomicOr(&a.bitmap[a.word_off[p] + (o >> 5)], 1u << (o & 31u));
+            }
+        }
+    }
+    if (!a.want_ordinals) return;
+    grid.sync();
+    for (uint32_t p = gtid >> 5; p < P; p += gsz >> 5)  // one warp per pool
+        ordinal_emit_pool(p, a.current, a.create_count, a.word_off, a.bitmap, a.create_off, a.create_ordinal);
 }
 
 static int rec_upload(k8sgpu_ctx *ctx, const k8sgpu_pool_table *pools, const k8sgpu_vm_table *vms,
@@ -223,6 +338,72 @@ static int rec_upload(k8sgpu_ctx *ctx, const k8sgpu_pool_table *pools, const k8s
     return K8SGPU_OK;
 }
 
+static int rec_finish(k8sgpu_ctx *ctx, cudaStream_t s);
+
+static int rec_run_coop(k8sgpu_ctx *ctx, cudaStream_t s) {
+    ReconcileState &st = ctx->rec;
+    const uint32_t P = st.p, V = st.v;
+    uint32_t *cnts = st.counters.as<uint32_t>();
+    if (st.coop_blocks_per_sm == 0) {
+        int per_sm = 0;
+        K8S_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, reconcile_coop_kernel, 256, 0));
+        st.coop_blocks_per_sm = per_sm > 0 ? per_sm : -1;
+    }
+    if (st.coop_blocks_per_sm < 0) return fail(ctx, K8SGPU_E_CUDA, "cooperative reconcile kernel cannot be resident");
+    const uint32_t nb = ceil_div(V ? V : 1u, kSortTile);
+    K8S_CUDA(ctx, st.sort.keys_alt.reserve((size_t)V * 4 + 16));
+    K8S_CUDA(ctx, st.sort.vals_alt.reserve((size_t)V * 4 + 16));
+    K8S_CUDA(ctx, st.sort.hist.reserve(((size_t)nb * 256 * 2 + 256) * 4));
+    K8S_CUDA(ctx, st.sort.scan_tmp.reserve(((size_t)nb * 256 / kScanTile + (size_t)P / kScanTile + 128) * 4));
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
+    K8S_CUDA(ctx, cudaMemsetAsync(cnts, 0, 64 * 4, s));
+    K8S_CUDA(ctx, cudaMemsetAsync(st.lut.p, 0xFF, ((size_t)st.n_owner_ids + 1) * 4, s));
+    if (st.want_ordinals) K8S_CUDA(ctx, cudaMemsetAsync(st.bitmap.p, 0, st.bitmap.cap, s));
+    RecArgs a;
+    a.desired = st.desired.as<int32_t>();
+    a.pool_owner = st.pool_owner.as<uint32_t>();
+    a.vm_owner = st.vm_owner.as<uint32_t>();
+    a.vm_flags = st.vm_flags.as<uint32_t>();
+    a.vm_ordinal = st.has_ordinal ? st.vm_ordinal.as<uint32_t>() : nullptr;
+    a.lut = st.lut.as<int32_t>();
+    a.pool_of = st.pool_of.as<int32_t>();
+    a.current = st.current.as<int32_t>();
+    a.delta = st.delta.as<int32_t>();
+    a.create_count = st.create_count.as<int32_t>();
+    a.member_off = st.member_off.as<int32_t>();
+    a.victim_off = st.victim_off.as<int32_t>();
+    a.create_off = st.create_off.as<int32_t>();
+    a.keys = st.sort_keys.as<uint32_t>();
+    a.vals = st.sort_vals.as<uint32_t>();
+    a.keys_alt = st.sort.keys_alt.as<uint32_t>();
+    a.vals_alt = st.sort.vals_alt.as<uint32_t>();
+    a.hist = st.sort.hist.as<uint32_t>();
+    a.hist_scan = a.hist + (size_t)nb * 256;
+    a.scan_sums = st.sort.scan_tmp.as<uint32_t>();
+    a.kvict = st.kvict.as<uint32_t>();
+    a.span_words = st.span_off.as<uint32_t>();
+    a.word_off = a.span_words + P + 1;
+    a.victim_vm = st.victim_vm.as<uint32_t>();
+    a.bitmap = st.bitmap.as<uint32_t>();
+    a.create_ordinal = st.create_ordinal.as<uint32_t>();
+    a.counters = cnts;
+    a.P = P;
+    a.V = V;
+    a.n_owner_ids = st.n_owner_ids;
+    a.bits = key_bits(P);
+    a.want_ordinals = st.want_ordinals ? 1 : 0;
+    const int passes = V ? (a.bits + 7) / 8 : 0;
+    st.sorted_vals = (passes & 1) ? a.vals_alt : a.vals;
+    uint32_t want = ceil_div(V ? V : 1u, 512u), pw = ceil_div(P + 1, 256u);
+    if (pw > want) want = pw;
+    uint32_t cap = (uint32_t)ctx->sm_count * (uint32_t)(st.coop_blocks_per_sm < 2 ? st.coop_blocks_per_sm : 2);
+    uint32_t grid = want < 1 ? 1 : (want > cap ? cap : want);
+    void *args[] = {&a};
+    K8S_CUDA(ctx, cudaLaunchCooperativeKernel((void *)reconcile_coop_kernel, dim3(grid), dim3(256), args, 0, s));
+    ctx->stats.kernel_launches++;
+    return rec_finish(ctx, s);
+}
+
 static int rec_run(k8sgpu_ctx *ctx, int want_members, int want_ordinals) {
     ReconcileState &st = ctx->rec;
     cudaStream_t s = ctx->stream;
@@ -231,6 +412,13 @@ static int rec_run(k8sgpu_ctx *ctx, int want_members, int want_ordinals) {
     st.want_members = want_members != 0;
     st.want_ordinals = want_ordinals != 0;
     uint32_t *cnts = st.counters.as<uint32_t>();
+    st.sorted_vals = st.sort_vals.as<uint32_t>();
+    // One cooperative launch for the whole pass while it is latency bound (config 2 is); the chain
+    // of kernels below once the tables are big enough to be bandwidth bound.  K8SGPU_REC_COOP=0/1
+    // forces either.
+    bool coop = V <= (4u << 20);
+    if (const char *e = getenv("K8SGPU_REC_COOP")) coop = atoi(e) != 0;
+    if (coop) return rec_run_coop(ctx, s);
     K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
     K8S_CUDA(ctx, cudaMemsetAsync(cnts, 0, 64 * 4, s));
     K8S_CUDA(ctx, cudaMemsetAsync(st.lut.p, 0xFF, ((size_t)st.n_owner_ids + 1) * 4, s));
@@ -277,6 +465,15 @@ static int rec_run(k8sgpu_ctx *ctx, int want_members, int want_ordinals) {
                    st.create_count.as<int32_t>(), word_off, st.bitmap.as<uint32_t>(), create_off,
                    st.create_ordinal.as<uint32_t>());
     }
+    return rec_finish(ctx, s);
+}
+
+static int rec_finish(k8sgpu_ctx *ctx, cudaStream_t s) {
+    ReconcileState &st = ctx->rec;
+    const uint32_t P = st.p;
+    uint32_t *cnts = st.counters.as<uint32_t>();
+    int32_t *victim_off = st.victim_off.as<int32_t>(), *create_off = st.create_off.as<int32_t>();
+    int32_t *member_off = st.member_off.as<int32_t>();
     K8S_CUDA(ctx, cudaEventRecord(ctx->ev_end, s));
     // totals + error flag
     K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, cnts, 4, cudaMemcpyDeviceToHost, s));
@@ -323,7 +520,7 @@ static int rec_download(k8sgpu_ctx *ctx, k8sgpu_reconcile_out *out) {
     D2H(out->victim_vm, st.victim_vm.p, st.n_victims);
     if (out->member_off && out->member_vm && st.want_members) {
         D2H(out->member_off, st.member_off.p, P + 1);
-        D2H(out->member_vm, st.sort_vals.p, st.n_members);
+        D2H(out->member_vm, st.sorted_vals, st.n_members);
     }
     if (out->create_off && out->create_ordinal && st.want_ordinals) {
         D2H(out->create_off, st.create_off.p, P + 1);
