@@ -965,6 +965,10 @@ static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s) {
     if (prep > want) want = prep;
     uint32_t cap = (uint32_t)ctx->sm_count * (uint32_t)(ctx->coop_blocks_per_sm < 2 ? ctx->coop_blocks_per_sm : 2);
     uint32_t grid = want < 1 ? 1 : (want > cap ? cap : want);
+    if (const char *e = getenv("K8SGPU_COOP_GRID")) {  // developer knob: CTAs in the cooperative grid
+        uint32_t g = (uint32_t)atoi(e);
+        if (g >= 1 && g <= cap) grid = g;
+    }
     void *args[] = {&a};
     K8S_CUDA(ctx, cudaLaunchCooperativeKernel((void *)admit_coop_kernel, dim3(grid), dim3(256), args, 0, s));
     ctx->stats.kernel_launches++;
