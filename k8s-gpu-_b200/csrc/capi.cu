@@ -53,7 +53,9 @@ extern "C" int k8sgpu_create(const int *devices, int ndev, k8sgpu_ctx **out) {
     CREATE_TRY(cudaEventCreate(&ctx->ev_begin));
     CREATE_TRY(cudaEventCreate(&ctx->ev_end));
     for (int i = 0; i < 2 * kMaxTimedRounds; ++i) CREATE_TRY(cudaEventCreate(&ctx->ev_score[i]));
-    CREATE_TRY(cudaMallocHost((void **)&ctx->h_pinned, 64 * sizeof(uint32_t)));
+    CREATE_TRY(cudaHostAlloc((void **)&ctx->h_pinned, 64 * sizeof(uint32_t), cudaHostAllocMapped));
+    memset(ctx->h_pinned, 0, 64 * sizeof(uint32_t));
+    CREATE_TRY(cudaHostGetDevicePointer((void **)&ctx->d_mailbox, ctx->h_pinned + 32, 0));
 #undef CREATE_TRY
     *out = ctx;
     return K8SGPU_OK;

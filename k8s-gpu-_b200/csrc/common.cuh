@@ -100,7 +100,9 @@ struct k8sgpu_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     cudaEvent_t ev_score[2 * k8sgpu::kMaxTimedRounds] = {};
-    uint32_t *h_pinned = nullptr;  // 64 u32 of pinned host memory for small read-backs
+    uint32_t *h_pinned = nullptr;  // 64 u32 of pinned, device-mapped host memory for small read-backs
+    uint32_t *d_mailbox = nullptr; // device view of h_pinned[32..]: {seq, next active count, error flags}
+    uint32_t mail_seq = 0;         // last sequence number handed to a kernel
     int sm_count = 148;
     int coop_blocks_per_sm = 0;  // occupancy of admit_coop_kernel (0 = not queried yet, <0 = unusable)
     char err[512] = {0};

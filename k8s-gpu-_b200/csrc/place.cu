@@ -10,7 +10,10 @@
 //   finalize    : packed best key -> node row
 //   admit       : stable sort of proposals by node, segmented prefix sums in pod order,
 //                 S <= free test (a13), free -= admitted, stable compaction of the active list.
-// Integer only; no atomics decide any result except commutative max / add.
+// In the in-library loop (k8sgpu_place / _run) finalize, admit and the next round's node_prep are
+// ONE cooperative launch (admit_coop_kernel); the round-at-a-time API used across GPUs runs them
+// as separate kernels.  k8sgpu_place_gang wraps the same loop in reject / release / retry
+// iterations.  Integer only; no atomics decide any result except commutative max / add.
 #include <cstdlib>
 
 #include "prims.cuh"
@@ -604,6 +607,8 @@ struct AdmitArgs {
     uint32_t na, n_nodes, n_pad;
     int bits;
     unsigned long long *prof;  // optional: %globaltimer at each phase boundary (CTA 0), else null
+    uint32_t *mailbox;         // mapped host memory: {seq, next active count, error flags}
+    uint32_t seq;
 };
 
 __device__ __forceinline__ void prof_mark(const AdmitArgs &a, int slot) {
@@ -709,6 +714,13 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
     prof_mark(a, 6);
     coop_exclusive_scan(grid, a.flags, a.offs, na, a.scan_sums, a.counters + 1);
     prof_mark(a, 7);
+    if (cta == 0 && tid == 0) {  // tell the host now: it can queue the next round while we finish
+        volatile uint32_t *mb = a.mailbox;
+        mb[1] = a.counters[1];
+        mb[2] = a.counters[0];
+        __threadfence_system();
+        mb[0] = a.seq;
+    }
     // stable compaction of the active list, and the next round's packed node records
     for (uint32_t i = cta * 256 + tid; i < na; i += G * 256)
         if (a.flags[i]) a.next_active[a.offs[i]] = a.active[i];
@@ -969,16 +981,32 @@ static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s) {
         uint32_t g = (uint32_t)atoi(e);
         if (g >= 1 && g <= cap) grid = g;
     }
+    a.mailbox = ctx->d_mailbox;
+    a.seq = ++ctx->mail_seq;
     void *args[] = {&a};
     K8S_CUDA(ctx, cudaLaunchCooperativeKernel((void *)admit_coop_kernel, dim3(grid), dim3(256), args, 0, s));
     ctx->stats.kernel_launches++;
-    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, cnts, 8, cudaMemcpyDeviceToHost, s));
-    K8S_CUDA(ctx, cudaStreamSynchronize(s));
-    if (ctx->h_pinned[0] != 0u)
+    // The kernel posts {seq, count, flags} to mapped host memory as soon as the count is known;
+    // poll that instead of a copy + stream synchronise (saves a stream op and the wake-up).
+    volatile uint32_t *mb = ctx->h_pinned + 32;
+    for (uint32_t spins = 0; mb[0] != a.seq; ++spins) {
+        if ((spins & 0x3FFu) == 0x3FFu) {
+            cudaError_t q = cudaStreamQuery(s);
+            if (q == cudaSuccess) {
+                if (mb[0] == a.seq) break;
+                return fail(ctx, K8SGPU_E_CUDA, "place: admission kernel finished without posting its result");
+            }
+            if (q != cudaErrorNotReady)
+                return fail(ctx, K8SGPU_E_CUDA, "place: admission kernel failed: %s", cudaGetErrorString(q));
+        }
+    }
+    const uint32_t next_count = mb[1], err_flags = mb[2];
+    if (err_flags != 0u)
         return fail(ctx, K8SGPU_E_ARG, "place: %s table outside the input domain (see k8sgpu.h)",
-                    (ctx->h_pinned[0] & kErrNode) ? "node" : "pod");
-    if (ctx->h_pinned[1] >= na)
+                    (err_flags & kErrNode) ? "node" : "pod");
+    if (next_count >= na)
         return fail(ctx, K8SGPU_E_CUDA, "place: round %u made no progress (%u pods still active)", st.rounds, na);
+    ctx->h_pinned[1] = next_count;
     if (want_prof) {  // developer aid: phase boundaries of this round's admission, microseconds
         unsigned long long t[9];
         K8S_CUDA(ctx, cudaMemcpy(t, cnts + 16, sizeof t, cudaMemcpyDeviceToHost));
