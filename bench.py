@@ -305,7 +305,7 @@ def main():
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None,  # total work per workload is fixed
         "dtype": "u32", "data": "synthetic",
         "config": {"workload": WORKLOADS[wl]["desc"], "nodes": N, "pods": M, "rounds": rounds, "placed": placed,
-                   "evals_per_step": tot_evals // args.steps, "parallelism": f"pods sharded x{world}, nodes replicated",
+                   "evals_per_step": tot_evals // args.steps, "parallelism": f"pods sharded x{world}, nodes replicated", "exchange": placer.exchange,
                    "l2": "flushed between timed steps (256 MB write)", "wall_s_timed_region": wall},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic["dram_bytes_per_launch"] if traffic else None, "peak_source": peak_src,

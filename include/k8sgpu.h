@@ -200,6 +200,21 @@ int k8sgpu_place_round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t 
 int k8sgpu_place_round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, void *stream, uint32_t *n_active);
 int k8sgpu_place_round_end(k8sgpu_ctx *ctx, void *stream);
 
+/* Peer exchange for the round-at-a-time form: instead of an NCCL all-gather of the proposal
+ * slices, the kernel that decodes the scores stores every proposal directly into EVERY rank's
+ * exchange buffer over NVLink peer memory (CUDA IPC; one process per GPU on one node).
+ *   export : allocates this rank's exchange buffer (two halves of m proposals, used alternately
+ *            by even and odd rounds), returns its 64-byte IPC handle and its local device pointer
+ *            (round r's proposals are at d_local + (r & 1) * m for k8sgpu_place_round_admit);
+ *   import : handles = world x 64 bytes, rank r's handle at offset 64 r (gathered by the host);
+ *   score_p2p : like k8sgpu_place_round_score, but the results land at positions [lo,hi) of all
+ *            ranks' buffers.  The caller then needs only a barrier across ranks (e.g. a
+ *            1-element all-reduce on the same stream) before k8sgpu_place_round_admit.
+ * No reference counterpart. */
+int k8sgpu_peer_export(k8sgpu_ctx *ctx, uint32_t m, void *handle64, void **d_local);
+int k8sgpu_peer_import(k8sgpu_ctx *ctx, int rank, int world, const void *handles);
+int k8sgpu_place_round_score_p2p(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, void *stream);
+
 /* ------------------------------------------------------------------ primitives (tests) */
 
 /* Stable LSD radix sort of (key,val) pairs on `bits` low key bits, and an exclusive u32

@@ -25,7 +25,7 @@ EXPORTS = (
     "k8sgpu_place", "k8sgpu_place_upload", "k8sgpu_place_run", "k8sgpu_place_download", "k8sgpu_score_once",
     "k8sgpu_place_round_begin", "k8sgpu_place_round_score", "k8sgpu_place_round_admit", "k8sgpu_place_round_end",
     "k8sgpu_debug_sort_pairs", "k8sgpu_debug_exclusive_scan", "k8sgpu_exclusive_scan_noalloc",
-    "k8sgpu_place_gang",
+    "k8sgpu_place_gang", "k8sgpu_peer_export", "k8sgpu_peer_import", "k8sgpu_place_round_score_p2p",
 )
 ASSIGN_GANG = -3
 SCAN_NOALLOC_MAX_N = 1 << 24
@@ -120,6 +120,9 @@ def load() -> C.CDLL:
         L.k8sgpu_place_round_score.argtypes = [vp, C.c_uint32, C.c_uint32, vp, vp]
         L.k8sgpu_place_round_admit.argtypes = [vp, vp, vp, u32p]
         L.k8sgpu_place_round_end.argtypes = [vp, vp]
+        L.k8sgpu_peer_export.argtypes = [vp, C.c_uint32, vp, C.POINTER(vp)]
+        L.k8sgpu_peer_import.argtypes = [vp, C.c_int, C.c_int, vp]
+        L.k8sgpu_place_round_score_p2p.argtypes = [vp, C.c_uint32, C.c_uint32, vp]
         L.k8sgpu_debug_sort_pairs.argtypes = [vp, u32p, u32p, C.c_uint32, C.c_int, u32p, u32p]
         L.k8sgpu_debug_exclusive_scan.argtypes = [vp, u32p, C.c_uint32, u32p, u32p]
         L.k8sgpu_exclusive_scan_noalloc.argtypes = [vp, vp, C.c_uint32, vp, vp, vp]
@@ -265,6 +268,20 @@ class Context:
         self._check(self._L.k8sgpu_place_round_admit(self._h, C.c_void_p(d_best_all_ptr), C.c_void_p(stream),
                                                      C.byref(na)))
         return na.value
+
+    def peer_export(self, m: int):
+        """-> (64-byte IPC handle of this rank's exchange buffer, its device pointer)."""
+        h = (C.c_ubyte * 64)()
+        p = C.c_void_p()
+        self._check(self._L.k8sgpu_peer_export(self._h, m, C.cast(h, C.c_void_p), C.byref(p)))
+        return bytes(h), p.value
+
+    def peer_import(self, rank: int, world: int, handles: bytes):
+        buf = (C.c_ubyte * len(handles)).from_buffer_copy(handles)
+        self._check(self._L.k8sgpu_peer_import(self._h, rank, world, C.cast(buf, C.c_void_p)))
+
+    def round_score_p2p(self, lo: int, hi: int, stream: int = 0):
+        self._check(self._L.k8sgpu_place_round_score_p2p(self._h, lo, hi, C.c_void_p(stream)))
 
     def round_end(self, stream: int = 0) -> dict:
         self._check(self._L.k8sgpu_place_round_end(self._h, C.c_void_p(stream)))

@@ -76,6 +76,9 @@ extern "C" int k8sgpu_destroy(k8sgpu_ctx *ctx) {
     DevBuf *pb[] = {&p.node_cols, &p.pod_cols, &p.free_cols, &p.nodeq,     &p.podq,      &p.assign, &p.active[0],
                     &p.active[1], &p.best_key, &p.best,      &p.sort_keys, &p.sort_vals, &p.seg,    &p.flags,
                     &p.counters,  &p.scan_tmp,  &p.gang_id,  &p.gang_min,  &p.gang_count, &p.gang_state};
+    for (int r = 0; r < p.peer_world; ++r)
+        if (r != p.peer_rank && p.peer_ptr[r]) cudaIpcCloseMemHandle(p.peer_ptr[r]);
+    p.peer_local.release();
     for (DevBuf *b : pb) b->release();
     release_sort(p.sort);
     ReconcileState &r = ctx->rec;

@@ -74,6 +74,10 @@ struct PlaceState {
     uint64_t evals = 0;
     uint32_t policy_flags = 0, max_rounds = 0;
     bool nodeq_stale = true;  // packed node records do not reflect free_cols yet
+    DevBuf peer_local;        // exchange buffer other ranks store their proposals into (IPC-exported)
+    int32_t *peer_ptr[16] = {};  // every rank's exchange buffer as seen from this GPU (own included)
+    int peer_world = 0, peer_rank = -1;
+    uint32_t peer_m = 0;         // proposals per half of the exchange buffer
     DevBuf gang_id, gang_min, gang_count, gang_state;  // gang placement: [m], [g], [g], [2g] (rejected, newly)
     int timed = 0;        // scoring launches timed so far in this run
     uint64_t timed_evals = 0;

@@ -412,6 +412,28 @@ __global__ void score_finalize_kernel(const unsigned long long *__restrict__ bes
     out[i] = node;
 }
 
+// Decode the packed best key of active positions [lo, lo+cnt) and store the proposal straight
+// into EVERY rank's exchange buffer (peer stores over NVLink; the own buffer is just another
+// pointer): the all-gather of the round is done by the kernel that produces the values.
+struct PeerPtrs {
+    int32_t *p[16];
+    int world;
+};
+__global__ void score_finalize_p2p_kernel(const unsigned long long *__restrict__ best_key,
+                                          const PodQ *__restrict__ podq, const uint32_t *__restrict__ active,
+                                          uint32_t lo, uint32_t cnt, uint32_t n_nodes, PeerPtrs peers) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cnt) return;
+    unsigned long long key = best_key[lo + i];
+    int32_t node = -1;
+    if (key != 0ull) {
+        uint32_t n = (0xFFFFFFFFu - (uint32_t)key) + podq[active[lo + i]].rot;
+        node = (int32_t)(n >= n_nodes ? n - n_nodes : n);
+    }
+#pragma unroll 1
+    for (int r = 0; r < peers.world; ++r) peers.p[r][lo + i] = node;
+}
+
 // ------------------------------------------------------------------ admission (a13)
 
 __global__ void admit_keys_kernel(const int32_t *__restrict__ best, const uint32_t *__restrict__ active,
@@ -1350,4 +1372,69 @@ extern "C" int k8sgpu_place_round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_a
 extern "C" int k8sgpu_place_round_end(k8sgpu_ctx *ctx, void *stream) {
     K8S_ENTER(ctx);
     return round_end(ctx, ::k8sgpu::pick_stream(ctx, stream));
+}
+
+// ------------------------------------------------------------------ peer exchange (one process per GPU)
+
+extern "C" int k8sgpu_peer_export(k8sgpu_ctx *ctx, uint32_t m, void *handle64, void **d_local) {
+    K8S_ENTER(ctx);
+    if (!handle64) return fail(ctx, K8SGPU_E_ARG, "peer_export: NULL handle buffer");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+    PlaceState &st = ctx->place;
+    for (int r = 0; r < st.peer_world; ++r)  // drop mappings of an earlier exchange buffer
+        if (r != st.peer_rank && st.peer_ptr[r]) cudaIpcCloseMemHandle(st.peer_ptr[r]);
+    st.peer_world = 0;
+    st.peer_rank = -1;
+    st.peer_local.release();  // a fresh allocation: its handle must match what peers will open
+    K8S_CUDA(ctx, st.peer_local.reserve((size_t)(m ? m : 1u) * 2 * 4));  // two halves, used by round parity
+    st.peer_m = m ? m : 1u;
+    cudaIpcMemHandle_t h;
+    K8S_CUDA(ctx, cudaIpcGetMemHandle(&h, st.peer_local.p));
+    memcpy(handle64, &h, 64);
+    if (d_local) *d_local = st.peer_local.p;
+    return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_peer_import(k8sgpu_ctx *ctx, int rank, int world, const void *handles) {
+    K8S_ENTER(ctx);
+    PlaceState &st = ctx->place;
+    if (world < 1 || world > 16 || rank < 0 || rank >= world || !handles)
+        return fail(ctx, K8SGPU_E_ARG, "peer_import: bad rank/world (%d/%d; at most 16 ranks)", rank, world);
+    if (!st.peer_local.p) return fail(ctx, K8SGPU_E_ARG, "peer_import: call k8sgpu_peer_export first");
+    for (int r = 0; r < world; ++r) {
+        if (r == rank) {
+            st.peer_ptr[r] = st.peer_local.as<int32_t>();
+            continue;
+        }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, static_cast<const char *>(handles) + 64 * (size_t)r, 64);
+        void *p = nullptr;
+        K8S_CUDA(ctx, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        st.peer_ptr[r] = static_cast<int32_t *>(p);
+    }
+    st.peer_world = world;
+    st.peer_rank = rank;
+    return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_place_round_score_p2p(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, void *stream) {
+    K8S_ENTER(ctx);
+    PlaceState &st = ctx->place;
+    if (st.peer_world < 1) return fail(ctx, K8SGPU_E_ARG, "round_score_p2p: no peers imported");
+    if (st.m > st.peer_m) return fail(ctx, K8SGPU_E_CAPACITY, "round_score_p2p: exchange buffer holds %u proposals, tables have %u pods", st.peer_m, st.m);
+    cudaStream_t s = pick_stream(ctx, stream);
+    int rc = round_score(ctx, lo, hi, nullptr, s, /*prep=*/true, /*finalize=*/false);
+    if (rc) return rc;
+    if (hi > lo) {
+        // Rounds alternate between the two halves of every exchange buffer: a fast rank's stores of
+        // round r+1 must not land in the half a slower rank is still reading for round r.
+        const size_t half = (size_t)(st.rounds & 1u) * st.peer_m;
+        PeerPtrs pp;
+        for (int r = 0; r < 16; ++r) pp.p[r] = r < st.peer_world ? st.peer_ptr[r] + half : nullptr;
+        pp.world = st.peer_world;
+        K8S_LAUNCH(ctx, score_finalize_p2p_kernel, ceil_div(hi - lo, 256), 256, 0, s,
+                   st.best_key.as<unsigned long long>(), st.podq.as<PodQ>(), st.active[st.cur].as<uint32_t>(), lo,
+                   hi - lo, st.n, pp);
+    }
+    return K8SGPU_OK;
 }

@@ -43,9 +43,11 @@ def main():
              ("c4-slice", synth.gen_nodes(100_000, 4), synth.gen_pods(60_000, 4), 0, False)]
     ok_all = True
     with capi.Context(local) as ctx:
-        pl = placement.ShardedPlacer(ctx, dist, rank, world)
+      for p2p in (True, False):  # peer-store exchange, then the NCCL all-gather exchange
+        pl = placement.ShardedPlacer(ctx, dist, rank, world, p2p=p2p)
         for name, nodes, pods, flags, check_oracle in cases:
             pl.upload(nodes, pods)
+            name = f"{name} [{pl.exchange}]"
             st = pl.run(flags=flags)
             got = pl.download()
             single = ctx.place(nodes, pods, flags=flags)
