@@ -295,7 +295,10 @@ def main():
     if traffic and traffic.get("workload", "c3") != wl:
         traffic = None  # the committed ncu capture is of another workload's launch
     # second roofline, the one that actually binds: INT ALU pipe, 16 lanes/clk/SMSP on 592 SMSPs
-    alu_ops_per_eval = 8  # SASS of score_kernel<1,2>: 4 LOP3 + SHF + LOP3 + 2 ISETP per eval (the rest is FMA pipe / LDS)
+    # SASS of score_kernel<2,4> (the default): 4 LOP3 + SHF + 2 ISETP per eval on the ALU pipe; 6 IMAD on
+    # the FMA pipe and one LDS.128 (two pods share each node record) -- 14 issue slots per eval, so the
+    # issue rate (32 lanes/clk/SMSP / 14) gives the same ceiling as the ALU pipe (16 lanes/clk/SMSP / 7).
+    alu_ops_per_eval = 7
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965
     alu_peak = 148 * 4 * 16 * sm_mhz * 1e6 / alu_ops_per_eval  # evals/s if the ALU pipe never idled
     alu_achieved = tot_score_evals / (tot_score_ms * 1e-3) if tot_score_ms > 0 else 0.0
@@ -317,7 +320,9 @@ def main():
                              "(DESIGN.md 'roofline')"},
         "roofline_alu": {"bound": "int32 ALU pipe", "achieved": alu_achieved, "peak": alu_peak, "unit": "evals/s",
                          "frac": alu_achieved / alu_peak, "alu_ops_per_eval": alu_ops_per_eval,
-                         "note": "peak = 592 SMSPs x 16 lanes/clk x sm clock / ALU instructions per eval"},
+                         "issue_slots_per_eval": 14,
+                         "note": "peak = 592 SMSPs x 16 lanes/clk x sm clock / ALU instructions per eval "
+                                 "(= the issue-slot ceiling, 32 lanes/clk / 14 instructions)"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
     if launches_e2e is not None:

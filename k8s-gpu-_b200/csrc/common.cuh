@@ -16,6 +16,9 @@ constexpr int kMaxTimedRounds = 512;   // scoring-kernel event pairs kept per ru
 #ifndef K8S_NODE_TILE
 #define K8S_NODE_TILE 256
 #endif
+#ifndef K8S_STAGES
+#define K8S_STAGES 3
+#endif
 constexpr uint32_t kNodeTile = K8S_NODE_TILE;  // nodes per shared-memory tile (32 B each)
 constexpr uint32_t kSortTile = 2048;   // pairs per radix-sort block
 constexpr int kSortThreads = 256;
@@ -73,6 +76,7 @@ struct PlaceState {
     uint32_t rounds = 0;
     uint64_t evals = 0;
     uint32_t policy_flags = 0, max_rounds = 0;
+    int score_res = 2;  // eval_pair variant the pod records are laid out for
     bool nodeq_stale = true;  // packed node records do not reflect free_cols yet
     DevBuf peer_local;        // exchange buffer other ranks store their proposals into (IPC-exported)
     int32_t *peer_ptr[16] = {};  // every rank's exchange buffer as seen from this GPU (own included)

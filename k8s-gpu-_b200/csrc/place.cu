@@ -50,7 +50,7 @@ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
 // ------------------------------------------------------------------ table preparation
 
 __global__ void pod_prep_kernel(const uint32_t *__restrict__ cols, uint32_t m, uint32_t n_nodes, uint32_t policy,
-                                PodQ *__restrict__ podq, int32_t *__restrict__ assign,
+                                int mul_masks, PodQ *__restrict__ podq, int32_t *__restrict__ assign,
                                 uint32_t *__restrict__ active, uint32_t *__restrict__ err) {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= m) return;
@@ -60,6 +60,10 @@ __global__ void pod_prep_kernel(const uint32_t *__restrict__ cols, uint32_t m, u
     q.req_mib = cols[2 * (size_t)m + p];
     q.nsku = ~cols[3 * (size_t)m + p];
     q.nzone = __brev(~cols[4 * (size_t)m + p]);  // bit-reversed, like NodeQ::zone_bit
+    if (mul_masks) {  // eval_pair RES = 4: each mask is mirrored against its node-side one-hot word
+        q.nsku = __brev(q.nsku);
+        q.nzone = __brev(q.nzone);
+    }
     q.ntol = ~cols[5 * (size_t)m + p];
     uint32_t pz = cols[6 * (size_t)m + p];
     q.pzb = pz < 32u ? (1u << pz) : 0u;
@@ -114,6 +118,9 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)_
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                  : "memory");
@@ -152,6 +159,10 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
 //          OR says "some resource is short".  One ALU instruction fewer per eval.
 // RES = 2: as 1, and the running best is updated by a predicated mad (key * runtime 1 + 0), which
 //          ptxas keeps on the FMA pipe instead of turning it into an ALU select: 8 ALU ops/eval.
+// RES = 4: as 2, and the SKU and zone allow-masks are tested on the FMA pipe too: the pod's mask,
+//          mirrored against the node's one-hot word, times that word is the mask shifted so that
+//          the node's own bit lands on bit 31 -- a sign bit that joins the resource differences'
+//          OR.  7 ALU + 6 FMA-pipe ops per eval.  (PodQ::nsku / nzone are stored mirrored for it.)
 // RES = 3: as 2, and the zone-preference bit comes from two multiplies instead of a funnel shift:
 //          pzb * zone_bit = 2^(31 + pref - zone) has bit 31 set exactly when pref == zone, and
 //          mul.hi by 2^8 brings that bit to position 7.  7 ALU + 6 FMA-pipe ops per eval.
@@ -220,6 +231,28 @@ __device__ __forceinline__ void eval_pair(const uint4 &a, const uint4 &b, uint32
             : "+r"(best)
             : "r"(a.w), "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.x), "r"(b.y), "r"(b.w), "r"(nsku), "r"(nzone),
               "r"(ntol), "r"(pzb), "r"(rg), "r"(rc), "r"(rm), "r"(b.z), "r"(negone), "r"(0u - negone));
+    } else if (RES == 4) {
+        asm("{\n\t"
+            ".reg .pred pf;\n\t"
+            ".reg .b32 m, z, key, d1, d2, d3, d4, d5;\n\t"
+            "mad.lo.s32 d1, %12, %16, %2;\n\t"
+            "mad.lo.s32 d2, %13, %16, %3;\n\t"
+            "mad.lo.s32 d3, %14, %16, %4;\n\t"
+            "mul.lo.u32 d4, %8, %1;\n\t"
+            "mul.lo.u32 d5, %9, %5;\n\t"
+            "and.b32 m, %6, %10;\n\t"
+            "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t"
+            "setp.eq.u32 pf, m, 0;\n\t"
+            "lop3.b32 d1, d1, d4, d5, 0xFE;\n\t"
+            "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
+            "shf.r.wrap.b32 z, %11, %11, %7;\n\t"
+            "lop3.b32 key, z, 0x80, %15, 0xEA;\n\t"
+            "setp.gt.and.u32 pf, key, %0, pf;\n\t"
+            "@pf mad.lo.u32 %0, key, %17, 0;\n\t"
+            "}"
+            : "+r"(best)
+            : "r"(a.w), "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.x), "r"(b.y), "r"(b.w), "r"(nsku), "r"(nzone),
+              "r"(ntol), "r"(pzb), "r"(rg), "r"(rc), "r"(rm), "r"(b.z), "r"(negone), "r"(0u - negone));
     } else {
         asm("{\n\t"
             ".reg .pred pf;\n\t"
@@ -245,6 +278,8 @@ __device__ __forceinline__ void eval_pair(const uint4 &a, const uint4 &b, uint32
     }
 }
 
+constexpr int kDefaultRes = 4;
+constexpr uint32_t kStages = K8S_STAGES;  // node tiles in flight per CTA
 constexpr uint32_t kGroup = 64;        // nodes per index group (index bits 1..6 of the key)
 constexpr uint32_t kIdxMask = 0x7Eu;   // those bits
 
@@ -258,28 +293,36 @@ constexpr uint32_t kIdxMask = 0x7Eu;   // those bits
 // the running best is lowered to just below its own key, which lets a later node with an EQUAL
 // key take over -- exactly "nodes at or after rot come first".  Only the 8-node chunk that
 // contains rot takes the slow path.
-template <int PPT, int RES>
-__global__ void __launch_bounds__(256) score_kernel(const NodeQ *__restrict__ nodeq, uint32_t n_tiles,
+template <int PPT, int RES, int MB>
+__global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict__ nodeq, uint32_t n_tiles,
                                                     uint32_t tiles_per_split, const PodQ *__restrict__ podq,
                                                     const uint32_t *__restrict__ active, uint32_t lo, uint32_t hi,
                                                     unsigned long long *__restrict__ best_key, uint32_t n_nodes,
                                                     int use_atomic, uint32_t negone) {
-    __shared__ __align__(128) uint4 tile[2][kNodeTile * 2];
-    __shared__ __align__(8) uint64_t bar[2];
+    // kStages-deep ring of node tiles.  full[b]: the TMA copy into buffer b has landed (one
+    // arrival + its byte count); empty[b]: all 8 warps are done reading buffer b (one arrival per
+    // warp).  No __syncthreads in the tile loop: a warp may run a tile ahead of its slowest sibling.
+    __shared__ __align__(128) uint4 tile[kStages][kNodeTile * 2];
+    __shared__ __align__(8) uint64_t full[kStages], empty[kStages];
     const int tid = threadIdx.x;
     const uint32_t t0 = blockIdx.y * tiles_per_split;
     const uint32_t t1 = min(t0 + tiles_per_split, n_tiles);
     constexpr uint32_t kTileBytes = kNodeTile * sizeof(NodeQ);
 
     if (tid == 0) {
-        mbar_init(&bar[0], 1);
-        mbar_init(&bar[1], 1);
+#pragma unroll
+        for (uint32_t b = 0; b < kStages; ++b) {
+            mbar_init(&full[b], 1);
+            mbar_init(&empty[b], 256 / 32);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    if (tid == 0 && t0 < t1) {
-        mbar_expect_tx(&bar[0], kTileBytes);
-        bulk_g2s(&tile[0][0], nodeq + (size_t)t0 * kNodeTile, kTileBytes, &bar[0]);
+    if (tid == 0) {
+        for (uint32_t b = 0; b + 1 < kStages && t0 + b < t1; ++b) {
+            mbar_expect_tx(&full[b], kTileBytes);
+            bulk_g2s(&tile[b][0], nodeq + (size_t)(t0 + b) * kNodeTile, kTileBytes, &full[b]);
+        }
     }
 
     uint32_t pos[PPT], rg[PPT], rc[PPT], rm[PPT], nsku[PPT], nzone[PPT], ntol[PPT], pzb[PPT], rot[PPT];
@@ -300,12 +343,8 @@ __global__ void __launch_bounds__(256) score_kernel(const NodeQ *__restrict__ no
     }
 
     for (uint32_t t = t0; t < t1; ++t) {
-        const uint32_t it = t - t0, buf = it & 1u;
-        if (tid == 0 && t + 1 < t1) {  // prefetch the next tile into the other buffer
-            mbar_expect_tx(&bar[buf ^ 1u], kTileBytes);
-            bulk_g2s(&tile[buf ^ 1u][0], nodeq + (size_t)(t + 1) * kNodeTile, kTileBytes, &bar[buf ^ 1u]);
-        }
-        for (uint32_t spins = 0; !mbar_try_wait(&bar[buf], (it >> 1) & 1u);)
+        const uint32_t it = t - t0, buf = it % kStages;
+        for (uint32_t spins = 0; !mbar_try_wait(&full[buf], (it / kStages) & 1u);)
             if (++spins > (1u << 26)) __trap();  // a lost TMA completion must fail loudly, not hang the GPU
         const uint32_t nbase = t * kNodeTile;
         uint32_t rrel[PPT];  // rot - nbase: the scan crosses rot inside this tile iff rrel < 256
@@ -375,7 +414,22 @@ __global__ void __launch_bounds__(256) score_kernel(const NodeQ *__restrict__ no
                     best[j] |= kIdxMask;
                 }
         }
-        __syncthreads();  // everyone is done with tile[buf] before it is refilled
+        __syncwarp();
+        if ((tid & 31) == 0) mbar_arrive(&empty[buf]);  // this warp is done with tile[buf]
+        const uint32_t nxt = it + kStages - 1u;          // refill the buffer that was read one tile ago
+        if (t0 + nxt < t1) {
+            const uint32_t b2 = nxt % kStages;
+            // Every thread waits (block-uniform control flow keeps the loop counters and tile
+            // addresses in uniform registers); the buffer was read a whole tile ago, so this
+            // almost never spins -- the warps may drift apart by one tile.
+            if (nxt >= kStages)
+                for (uint32_t spins = 0; !mbar_try_wait(&empty[b2], (nxt / kStages - 1u) & 1u);)
+                    if (++spins > (1u << 26)) __trap();
+            if (tid == 0) {
+                mbar_expect_tx(&full[b2], kTileBytes);
+                bulk_g2s(&tile[b2][0], nodeq + (size_t)(t0 + nxt) * kNodeTile, kTileBytes, &full[b2]);
+            }
+        }
     }
 
 #pragma unroll
@@ -826,13 +880,15 @@ static int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_
     st.timed = 0;
     st.timed_evals = 0;
     st.nodeq_stale = true;
+    st.score_res = kDefaultRes;  // which eval_pair variant (see its comment); all are bit-identical
+    if (const char *e = getenv("K8SGPU_RES")) st.score_res = atoi(e);
     K8S_CUDA(ctx, cudaMemsetAsync(st.counters.p, 0, 64 * 4, s));
     if (st.n)
         K8S_CUDA(ctx, cudaMemcpyAsync(st.free_cols.p, st.node_cols.p, 3 * (size_t)st.n * 4, cudaMemcpyDeviceToDevice, s));
     if (st.m)
         K8S_LAUNCH(ctx, pod_prep_kernel, ceil_div(st.m, 256), 256, 0, s, st.pod_cols.as<uint32_t>(), st.m, st.n,
-                   st.policy_flags, st.podq.as<PodQ>(), st.assign.as<int32_t>(), st.active[0].as<uint32_t>(),
-                   st.counters.as<uint32_t>());
+                   st.policy_flags, st.score_res == 4 ? 1 : 0, st.podq.as<PodQ>(), st.assign.as<int32_t>(),
+                   st.active[0].as<uint32_t>(), st.counters.as<uint32_t>());
     return K8SGPU_OK;
 }
 
@@ -851,19 +907,20 @@ static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_bes
     const uint32_t cnt = hi - lo;
     if (cnt == 0) return K8SGPU_OK;
     const uint32_t n_tiles = st.n_pad / kNodeTile;
-    // Grid shape.  The kernel is ALU bound, so what matters is an even spread over the 148 SMs:
-    // aim for ~20 CTAs per SM (the hardware scheduler then balances to a few percent) while each
-    // CTA still scans at least two node tiles.
+    // Grid shape.  The kernel is bound by the ALU pipe and the issue slots, so what matters is an
+    // even spread over the 148 SMs and a short tail: aim for ~64 CTAs per SM (one node tile per
+    // CTA at config 3), which measured 3-4 % faster than ~20 (profiles/r01_sweep_res4_ppt.txt).
     const uint32_t sms = (uint32_t)ctx->sm_count;
-    // One pod per thread: measured fastest on config 3 with the FMA-pipe resource test (two pods
-    // per thread halve the shared-memory reads but cost registers; profiles/r01_sweep_*.txt).
-    int ppt = 1;
-    if (const char *e = getenv("K8SGPU_PPT")) ppt = atoi(e) >= 2 ? 2 : 1;
+    // Pods per thread: two share every shared-memory read of a node record, which is what makes
+    // the 7-ALU variant (RES = 4) pay -- with one pod per thread it is issue bound at 15 slots per
+    // eval.  Four pay only on wide node tables, where few 64-node groups contain some pod's rot(p)
+    // (profiles/r01_sweep_res4_ppt.txt).
+    int ppt = st.score_res == 4 ? ((st.n >= 65536u && cnt >= 4u * 256u * 2u * sms) ? 4 : 2) : 1;
+    if (const char *e = getenv("K8SGPU_PPT")) ppt = atoi(e) >= 4 ? 4 : atoi(e) >= 2 ? 2 : 1;
+    if (ppt == 4 && st.score_res != 4) ppt = 2;
     const uint32_t xb = ceil_div(cnt, 256u * ppt);
-    uint32_t splits = ceil_div(20u * sms, xb);
+    uint32_t splits = ceil_div(64u * sms, xb);
     if (splits > n_tiles) splits = n_tiles;
-    if (splits > 1 && n_tiles / splits < 2 && (uint64_t)xb * ceil_div(n_tiles, 2u) >= 8ull * sms)
-        splits = ceil_div(n_tiles, 2u);
     if (const char *e = getenv("K8SGPU_SPLITS")) splits = (uint32_t)atoi(e);
     if (splits < 1) splits = 1;
     if (splits > n_tiles) splits = n_tiles;
@@ -880,19 +937,25 @@ static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_bes
     const bool timed = st.timed < kMaxTimedRounds;
     if (timed) K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed], s));
     dim3 grid(xb, splits);
-    int res = 2;  // which eval_pair variant (see its comment); all are bit-identical
-    if (const char *e = getenv("K8SGPU_RES")) res = atoi(e);
-#define K8S_SCORE(P, R)                                                                                         \
-    K8S_LAUNCH(ctx, (score_kernel<P, R>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
+    const int res = st.score_res;  // fixed at round_begin: the pod records are laid out for it
+#define K8S_SCORE(P, R, B)                                                                                         \
+    K8S_LAUNCH(ctx, (score_kernel<P, R, B>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
                st.active[st.cur].as<uint32_t>(), lo, hi, bk, st.n, use_atomic, 0xFFFFFFFFu)
-    if (ppt == 2 && res >= 3) K8S_SCORE(2, 3);
-    else if (ppt == 2 && res == 2) K8S_SCORE(2, 2);
-    else if (ppt == 2 && res == 1) K8S_SCORE(2, 1);
-    else if (ppt == 2) K8S_SCORE(2, 0);
-    else if (res >= 3) K8S_SCORE(1, 3);
-    else if (res == 2) K8S_SCORE(1, 2);
-    else if (res == 1) K8S_SCORE(1, 1);
-    else K8S_SCORE(1, 0);
+    int mb = 0;
+    if (const char *e = getenv("K8SGPU_MB")) mb = atoi(e);
+    if (ppt == 4 && mb == 2) K8S_SCORE(4, 4, 2);
+    else if (ppt == 4) K8S_SCORE(4, 4, 3);
+    else if (ppt == 2 && res >= 4 && mb == 5) K8S_SCORE(2, 4, 5);
+    else if (ppt == 2 && res >= 4) K8S_SCORE(2, 4, 4);
+    else if (ppt == 2 && res == 3) K8S_SCORE(2, 3, 5);
+    else if (ppt == 2 && res == 2) K8S_SCORE(2, 2, 5);
+    else if (ppt == 2 && res == 1) K8S_SCORE(2, 1, 5);
+    else if (ppt == 2) K8S_SCORE(2, 0, 5);
+    else if (res >= 4) K8S_SCORE(1, 4, 6);
+    else if (res == 3) K8S_SCORE(1, 3, 6);
+    else if (res == 2) K8S_SCORE(1, 2, 6);
+    else if (res == 1) K8S_SCORE(1, 1, 6);
+    else K8S_SCORE(1, 0, 6);
 #undef K8S_SCORE
     if (timed) {
         K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed + 1], s));

@@ -62,7 +62,7 @@ def case_place(rng, ctx):
     n, m = pick_size(rng, 3000), pick_size(rng, 12000)
     nodes, pods = random_nodes(rng, n), random_pods(rng, m)
     flags = int(rng.random() < 0.2)
-    env = dict(K8SGPU_RES=str(rng.integers(0, 4)), K8SGPU_PPT=str(rng.integers(1, 3)),
+    env = dict(K8SGPU_RES=str(rng.integers(0, 5)), K8SGPU_PPT=str(rng.choice([1, 2, 4])),
                K8SGPU_COOP=str(rng.integers(0, 2)))
     if rng.random() < 0.5:
         env["K8SGPU_SPLITS"] = str(rng.integers(1, 9))

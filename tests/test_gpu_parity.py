@@ -234,6 +234,37 @@ def test_round_api_with_two_emulated_shards(ctx, orc, synth):
     same_placement(got, orc.place(nodes, pods, nthreads=NCPU))
 
 
+def test_round_api_peer_store_world_of_one(ctx, orc, synth):
+    """The peer-store scoring entry with a world of one rank (its own exchange buffer is the
+    only destination): two slices per round, admission from the half the round's parity selects.
+    The multi-process form is checked by tests/run_sharded_gpu.py on 2+ GPUs."""
+    import torch
+
+    nodes, pods = synth.gen_nodes(700, 5), synth.gen_pods(3000, 5)
+    ctx.place_upload(nodes, pods)
+    handle, local = ctx.peer_export(3000)
+    assert len(handle) == 64 and local
+    ctx.peer_import(0, 1, handle)
+    stream = torch.cuda.current_stream().cuda_stream
+    na, r = ctx.round_begin(stream=stream), 0
+    while na:
+        half = (na + 1) // 2
+        ctx.round_score_p2p(0, half, stream)
+        ctx.round_score_p2p(half, na, stream)
+        na = ctx.round_admit(local + 4 * 3000 * (r & 1), stream)
+        r += 1
+    st = ctx.round_end(stream)
+    got = ctx.place_download()
+    got.update(st)
+    same_placement(got, orc.place(nodes, pods, nthreads=NCPU))
+    # a table larger than the exported buffer is refused, not overrun
+    ctx.place_upload(nodes, synth.gen_pods(3001, 5))
+    ctx.round_begin(stream=stream)
+    with pytest.raises(Exception, match="exchange buffer"):
+        ctx.round_score_p2p(0, 10, stream)
+    ctx.round_end(stream)
+
+
 def test_config3_full_size(ctx, orc, synth):
     """BASELINE.json config 3 at full size: 10k nodes x 100k pods, bit-exact vs the oracle
     (the oracle needs roughly 100 core-seconds; it is threaded over pods)."""
