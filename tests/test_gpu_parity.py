@@ -67,12 +67,16 @@ def test_sort_pairs_is_stable(ctx, n, bits):
 
 
 # ------------------------------------------------------------------ scoring kernel alone
-@pytest.mark.parametrize("ppt,splits", [(None, None), ("1", "1"), ("2", "1"), ("1", "3"), ("2", "7")])
+@pytest.mark.parametrize("ppt,splits,res", [(None, None, None), ("1", "1", "4"), ("2", "1", "4"), ("1", "3", "2"),
+                                            ("2", "7", "2"), ("4", "2", "4"), ("4", "1", "4"), ("1", "2", "0"),
+                                            ("2", "3", "1"), ("1", "5", "3")])
 @pytest.mark.parametrize("flags", [0, 1])
-def test_score_once_matches_oracle(ctx, orc, synth, ppt, splits, flags, monkeypatch):
+def test_score_once_matches_oracle(ctx, orc, synth, ppt, splits, res, flags, monkeypatch):
+    """Every kernel variant (pods per thread, node splits, eval_pair RES 0-4) is bit-identical."""
     if ppt:
         monkeypatch.setenv("K8SGPU_PPT", ppt)
         monkeypatch.setenv("K8SGPU_SPLITS", splits)
+        monkeypatch.setenv("K8SGPU_RES", res)
     nodes, pods = synth.gen_nodes(1500, config_id=5), synth.gen_pods(3333, config_id=5)
     ctx.place_upload(nodes, pods)
     got = ctx.score_once(flags)
