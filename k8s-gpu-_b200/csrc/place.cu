@@ -704,17 +704,28 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
 
     // phase 0: packed best key -> proposal; sort key = node (N for "no feasible node"); digit-0 histogram
     for (uint32_t vt = cta; vt < nb; vt += G) {
+        // all loads of the tile first: the stores below would otherwise order each row's loads
+        // behind the previous row's stores (8 dependent round trips instead of 2)
+        unsigned long long k64[kSortTile / 256];
+        uint32_t pod[kSortTile / 256], rot[kSortTile / 256];
+#pragma unroll
+        for (uint32_t r = 0; r < kSortTile / 256; ++r) {
+            uint32_t i = vt * kSortTile + r * 256 + tid;
+            k64[r] = i < na ? a.best_key[i] : 0ull;
+            pod[r] = i < na ? a.active[i] : 0u;
+        }
+#pragma unroll
+        for (uint32_t r = 0; r < kSortTile / 256; ++r) rot[r] = k64[r] != 0ull ? a.podq[pod[r]].rot : 0u;
 #pragma unroll
         for (uint32_t r = 0; r < kSortTile / 256; ++r) {
             uint32_t i = vt * kSortTile + r * 256 + tid;
             if (i < na) {
-                unsigned long long k64 = a.best_key[i];
-                uint32_t pod = a.active[i], key = N;
-                if (k64 != 0ull) {
-                    uint32_t n = (0xFFFFFFFFu - (uint32_t)k64) + a.podq[pod].rot;
+                uint32_t key = N;
+                if (k64[r] != 0ull) {
+                    uint32_t n = (0xFFFFFFFFu - (uint32_t)k64[r]) + rot[r];
                     key = n >= N ? n - N : n;
                 } else {
-                    a.assign[pod] = K8SGPU_ASSIGN_NONE;
+                    a.assign[pod[r]] = K8SGPU_ASSIGN_NONE;
                 }
                 a.keys[i] = key;
                 a.vals[i] = i;
@@ -735,9 +746,14 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
             for (uint32_t vt = cta; vt < nb; vt += G) sort_hist_tile(sk, na, shift, mask, a.hist, nb, vt);
             grid.sync();
         }
-        coop_exclusive_scan(grid, a.hist, a.hist_scan, nb * 256u, a.scan_sums, nullptr);
-        for (uint32_t vt = cta; vt < nb; vt += G)
-            sort_scatter_tile(sk, sv, dk, dv, na, shift, mask, a.hist_scan, nb, vt);
+        if (nb <= kLocalScanMaxTiles) {  // every CTA scans the small histogram itself: no scan phase, no barrier
+            for (uint32_t vt = cta; vt < nb; vt += G)
+                sort_scatter_tile(sk, sv, dk, dv, na, shift, mask, a.hist, nb, vt, true);
+        } else {
+            coop_exclusive_scan(grid, a.hist, a.hist_scan, nb * 256u, a.scan_sums, nullptr);
+            for (uint32_t vt = cta; vt < nb; vt += G)
+                sort_scatter_tile(sk, sv, dk, dv, na, shift, mask, a.hist_scan, nb, vt);
+        }
         grid.sync();
         uint32_t *t;
         t = sk; sk = dk; dk = t;

@@ -92,13 +92,20 @@ __device__ __forceinline__ void sort_hist_tile(const uint32_t *__restrict__ keys
 // from __match_any_sync; per-warp digit counters carry the rank across sub-rows.  The tile is
 // then laid out digit-major in shared memory and written out by consecutive threads, so each
 // (block, digit) run leaves as one contiguous store instead of 4-byte scattered writes.
+//
+// hist_scan is the exclusive scan of the digit-major histogram -- or, with local_scan, the raw
+// histogram itself: thread d then sums row d (all tiles of digit d) and the row's prefix up to this
+// tile, and a block scan over the 256 row totals gives the same number.  Every CTA re-reads the
+// whole histogram (256 * nblocks words, L2 resident), which is cheaper than a separate grid-wide
+// scan phase plus its barrier while nblocks is small (kLocalScanMaxTiles).
+constexpr uint32_t kLocalScanMaxTiles = 64;
 __device__ __forceinline__ void sort_scatter_tile(
     const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals, uint32_t *__restrict__ out_keys,
     uint32_t *__restrict__ out_vals, uint32_t n, int shift, uint32_t mask, const uint32_t *__restrict__ hist_scan,
-    uint32_t nblocks, uint32_t vt) {
+    uint32_t nblocks, uint32_t vt, bool local_scan = false) {
     __shared__ uint32_t cnt[8][256];
     __shared__ uint32_t gdelta[256];  // global base of digit d minus its start inside the tile
-    __shared__ uint32_t wtot[8];
+    __shared__ uint32_t wtot[8], wtot2[8];
     __shared__ uint32_t sk[kSortTile], sv[kSortTile];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 #pragma unroll
@@ -114,6 +121,18 @@ __device__ __forceinline__ void sort_scatter_tile(
         bool in = i < n;
         k[s] = in ? keys[i] : 0u;
         v[s] = in ? vals[i] : 0u;
+    }
+    uint32_t gbase = 0, row_tot = 0;
+    if (local_scan) {  // issued before the ranking so the loads overlap it
+        const uint32_t *row = hist_scan + (size_t)tid * nblocks;
+#pragma unroll 8
+        for (uint32_t b = 0; b < nblocks; ++b) {
+            const uint32_t h = row[b];
+            gbase += b < vt ? h : 0u;
+            row_tot += h;
+        }
+    } else {
+        gbase = hist_scan[(size_t)tid * nblocks + vt];
     }
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
@@ -142,16 +161,24 @@ __device__ __forceinline__ void sort_scatter_tile(
             run += t;
         }
         uint32_t inc = warp_incl_scan(run, lane);  // exclusive start of digit `tid` inside the tile
-        if (lane == 31) wtot[warp] = inc;
+        uint32_t inc2 = local_scan ? warp_incl_scan(row_tot, lane) : 0u;  // ... and in the whole array
+        if (lane == 31) {
+            wtot[warp] = inc;
+            wtot2[warp] = inc2;
+        }
         __syncthreads();
-        uint32_t woff = 0;
+        uint32_t woff = 0, woff2 = 0;
 #pragma unroll
         for (int w = 0; w < 8; ++w)
-            if (w < warp) woff += wtot[w];
+            if (w < warp) {
+                woff += wtot[w];
+                woff2 += wtot2[w];
+            }
         const uint32_t dstart = woff + inc - run;
 #pragma unroll
         for (int w = 0; w < 8; ++w) cnt[w][tid] += dstart;
-        gdelta[tid] = hist_scan[tid * nblocks + vt] - dstart;
+        if (local_scan) gbase += woff2 + inc2 - row_tot;
+        gdelta[tid] = gbase - dstart;
     }
     __syncthreads();
 #pragma unroll

@@ -190,35 +190,138 @@ struct RecArgs {
     uint32_t *kvict, *span_words, *word_off, *victim_vm, *bitmap /* pre-zeroed */, *create_ordinal, *counters;
     uint32_t P, V, n_owner_ids;
     int bits, want_ordinals;
+    unsigned long long *prof;  // optional (K8SGPU_REC_PROF): %globaltimer at each phase boundary, else null
 };
 
+__device__ __forceinline__ void rec_mark(const RecArgs &a, int slot) {
+    if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.prof[slot] = t;
+    }
+}
+
+// README.md:195-212 for pool p, from its member count.
+__device__ __forceinline__ void pool_math(const RecArgs &a, uint32_t p) {
+    int32_t cur = a.current[p], d = a.desired[p] - cur;
+    a.delta[p] = d;
+    int32_t cc = d > 0 ? d : 0;
+    a.create_count[p] = cc;
+    a.kvict[p] = d < 0 ? (uint32_t)(-d) : 0u;
+    a.span_words[p] = cc ? ((uint32_t)cur + (uint32_t)cc + 31u) / 32u : 0u;
+}
+
+// Exclusive scan of n <= 16 tiles by the calling CTA alone; out[n] = total.
+__device__ __forceinline__ void cta_exclusive_scan(const uint32_t *in, uint32_t *out, uint32_t n) {
+    uint32_t carry = 0;
+    for (uint32_t t = 0; t * kScanTile < n; ++t) carry = block_scan_tile(in, out, t * kScanTile, n, carry, true);
+    if (threadIdx.x == 0) out[n] = carry;
+}
+
+// Phases (each line ends in a grid barrier):
+//   1. owner id -> pool row table; member counters zeroed
+//   2. tag filter, sort keys, digit-0 histogram, per-pool member count (warp-aggregated atomics:
+//      counts only, order-free)
+//   3. per 8-bit digit: histogram (after digit 0), its scan, the stable scatter.  While CTA 0
+//      scans the first histogram, the LAST CTA does everything that needs only the counts --
+//      currentCount, the diff, and the offsets of every output list -- so none of that costs a
+//      barrier of its own (when P is too large for one CTA, the whole grid does it instead).
+//   4. victims = first -delta rows of each pool's run of the sorted list; used-ordinal bits
+//   5. names of the VMs to create (lowest free ordinals)
 __global__ void __launch_bounds__(256) reconcile_coop_kernel(RecArgs a) {
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = threadIdx.x, cta = blockIdx.x, G = gridDim.x, gtid = cta * 256 + tid, gsz = G * 256;
     const uint32_t P = a.P, V = a.V;
     const uint32_t nb = (V + kSortTile - 1) / kSortTile;
+    const bool one_cta_pools = (P + kScanTile - 1) / kScanTile <= 16;
+    constexpr uint32_t kSmallP = 4096;  // pools whose member counters fit in shared memory
+    __shared__ uint32_t pcount[kSmallP];
+    const bool small_p = P <= kSmallP;
+    if (small_p)
+        for (uint32_t p = tid; p < P; p += 256) pcount[p] = 0;
+    rec_mark(a, 0);
 
     for (uint32_t p = gtid; p < P; p += gsz) {  // owner id -> pool row
         if (a.desired[p] < 0) atomicOr(a.counters, kErrNegDesired);
         uint32_t o = a.pool_owner[p];
         if (o < a.n_owner_ids && atomicCAS(&a.lut[o], -1, (int32_t)p) != -1) atomicOr(a.counters, kErrDupOwner);
+        a.current[p] = 0;
     }
     grid.sync();
-    for (uint32_t vt = cta; vt < nb; vt += G) {  // tag filter + sort keys + digit-0 histogram
+    rec_mark(a, 1);
+    for (uint32_t vt = cta; vt < nb; vt += G) {  // tag filter + sort keys + digit-0 histogram + member counts
+        // all loads of the tile first (the stores below would otherwise fence each row's loads
+        // behind the previous row's stores: 8 dependent round trips instead of 2)
+        uint32_t ow[kSortTile / 256], fl[kSortTile / 256];
+        int32_t pp[kSortTile / 256];
 #pragma unroll
         for (uint32_t r = 0; r < kSortTile / 256; ++r) {
             uint32_t v = vt * kSortTile + r * 256 + tid;
+            ow[r] = v < V ? a.vm_owner[v] : K8SGPU_NONE_U32;
+            fl[r] = v < V ? a.vm_flags[v] : 0u;
+        }
+#pragma unroll
+        for (uint32_t r = 0; r < kSortTile / 256; ++r)  // README.md:238; the table was written in phase 1: L2 load
+            pp[r] = ((fl[r] & 1u) && ow[r] < a.n_owner_ids) ? __ldcg(&a.lut[ow[r]]) : -1;
+#pragma unroll
+        for (uint32_t r = 0; r < kSortTile / 256; ++r) {
+            uint32_t v = vt * kSortTile + r * 256 + tid;
+            uint32_t key = 0xFFFFFFFFu;  // rows past the end: no pool, nothing stored
             if (v < V) {
-                int32_t p = match_one(a.vm_owner[v], a.vm_flags[v], a.n_owner_ids, a.lut);
+                int32_t p = pp[r];
                 a.pool_of[v] = p;
-                a.keys[v] = p < 0 ? P : (uint32_t)p;
+                key = p < 0 ? P : (uint32_t)p;
+                a.keys[v] = key;
                 a.vals[v] = v;
+            }
+            // currentCount := len(existingVMs), README.md:195 (counts only: order-free)
+            if (small_p) {
+                if (key < P) atomicAdd(&pcount[key], 1u);
+            } else {  // one global atomic per distinct pool per warp
+                const uint32_t peers = __match_any_sync(0xFFFFFFFFu, key);
+                if (key < P && (tid & 31u) == (uint32_t)__ffs(peers) - 1u)
+                    atomicAdd(&a.current[key], (int32_t)__popc(peers));
+            }
+        }
+        if (small_p) {  // flush this tile's per-pool counts
+            __syncthreads();
+            for (uint32_t p = tid; p < P; p += 256) {
+                const uint32_t c = pcount[p];
+                if (c) {
+                    atomicAdd(&a.current[p], (int32_t)c);
+                    pcount[p] = 0;
+                }
             }
         }
         __syncthreads();
+        if (vt == 0) rec_mark(a, 6);
         sort_hist_tile(a.keys, V, 0, 0xFFu, a.hist, nb, vt);
+        if (vt == 0) rec_mark(a, 7);
     }
     grid.sync();
+    rec_mark(a, 2);
+    if (one_cta_pools) {
+        if (cta == G - 1) {  // overlaps the first histogram scan (CTA 0) unless the grid is one CTA
+            for (uint32_t p = tid; p < P; p += 256) pool_math(a, p);
+            __syncthreads();
+            cta_exclusive_scan((const uint32_t *)a.current, (uint32_t *)a.member_off, P);
+            cta_exclusive_scan(a.kvict, (uint32_t *)a.victim_off, P);
+            cta_exclusive_scan((const uint32_t *)a.create_count, (uint32_t *)a.create_off, P);
+            if (a.want_ordinals) {
+                cta_exclusive_scan(a.span_words, a.word_off, P);
+                if (tid == 0) a.counters[4] = a.word_off[P];
+            }
+        }
+    } else {
+        for (uint32_t p = gtid; p < P; p += gsz) pool_math(a, p);
+        grid.sync();
+        coop_exclusive_scan(grid, (const uint32_t *)a.current, (uint32_t *)a.member_off, P, a.scan_sums,
+                            (uint32_t *)a.member_off + P);
+        coop_exclusive_scan(grid, a.kvict, (uint32_t *)a.victim_off, P, a.scan_sums, (uint32_t *)a.victim_off + P);
+        coop_exclusive_scan(grid, (const uint32_t *)a.create_count, (uint32_t *)a.create_off, P, a.scan_sums,
+                            (uint32_t *)a.create_off + P);
+        if (a.want_ordinals) coop_exclusive_scan(grid, a.span_words, a.word_off, P, a.scan_sums, a.counters + 4);
+    }
     uint32_t *sk = a.keys, *sv = a.vals, *dk = a.keys_alt, *dv = a.vals_alt;
     if (V > 0) {
         for (int shift = 0; shift < a.bits; shift += 8) {
@@ -228,39 +331,22 @@ __global__ void __launch_bounds__(256) reconcile_coop_kernel(RecArgs a) {
                 for (uint32_t vt = cta; vt < nb; vt += G) sort_hist_tile(sk, V, shift, mask, a.hist, nb, vt);
                 grid.sync();
             }
-            coop_exclusive_scan(grid, a.hist, a.hist_scan, nb * 256u, a.scan_sums, nullptr);
-            for (uint32_t vt = cta; vt < nb; vt += G) sort_scatter_tile(sk, sv, dk, dv, V, shift, mask, a.hist_scan, nb, vt);
+            if (nb <= kLocalScanMaxTiles) {  // every CTA scans the small histogram itself: no scan phase, no barrier
+                for (uint32_t vt = cta; vt < nb; vt += G) sort_scatter_tile(sk, sv, dk, dv, V, shift, mask, a.hist, nb, vt, true);
+            } else {
+                coop_exclusive_scan(grid, a.hist, a.hist_scan, nb * 256u, a.scan_sums, nullptr);
+                for (uint32_t vt = cta; vt < nb; vt += G) sort_scatter_tile(sk, sv, dk, dv, V, shift, mask, a.hist_scan, nb, vt);
+            }
             grid.sync();
             uint32_t *t;
             t = sk; sk = dk; dk = t;
             t = sv; sv = dv; dv = t;
         }
+    } else {
+        grid.sync();  // the offsets written by the last CTA become visible to everyone
     }
     // (the host knows where the sorted pairs ended up: in keys/vals after an even number of passes)
-    for (uint32_t p = gtid; p <= P; p += gsz) {  // existingVMs of pool p = sorted rows [member_off[p], member_off[p+1])
-        uint32_t lo = 0, hi = V;
-        while (lo < hi) {
-            uint32_t mid = lo + ((hi - lo) >> 1);
-            if (sk[mid] < p) lo = mid + 1;
-            else hi = mid;
-        }
-        a.member_off[p] = (int32_t)lo;
-    }
-    grid.sync();
-    for (uint32_t p = gtid; p < P; p += gsz) {  // README.md:195-212
-        int32_t cur = a.member_off[p + 1] - a.member_off[p], d = a.desired[p] - cur;
-        a.current[p] = cur;
-        a.delta[p] = d;
-        int32_t cc = d > 0 ? d : 0;
-        a.create_count[p] = cc;
-        a.kvict[p] = d < 0 ? (uint32_t)(-d) : 0u;
-        a.span_words[p] = cc ? ((uint32_t)cur + (uint32_t)cc + 31u) / 32u : 0u;
-    }
-    grid.sync();
-    coop_exclusive_scan(grid, a.kvict, (uint32_t *)a.victim_off, P, a.scan_sums, (uint32_t *)a.victim_off + P);
-    coop_exclusive_scan(grid, (const uint32_t *)a.create_count, (uint32_t *)a.create_off, P, a.scan_sums,
-                        (uint32_t *)a.create_off + P);
-    if (a.want_ordinals) coop_exclusive_scan(grid, a.span_words, a.word_off, P, a.scan_sums, a.counters + 4);
+    rec_mark(a, 3);
     for (uint32_t i = gtid; i < V; i += gsz) {  // victims (README.md:214) and used-ordinal bits
         uint32_t p = sk[i];
         if (p >= P) continue;
@@ -276,8 +362,10 @@ __global__ void __launch_bounds__(256) reconcile_coop_kernel(RecArgs a) {
     }
     if (!a.want_ordinals) return;
     grid.sync();
+    rec_mark(a, 4);
     for (uint32_t p = gtid >> 5; p < P; p += gsz >> 5)  // one warp per pool
         ordinal_emit_pool(p, a.current, a.create_count, a.word_off, a.bitmap, a.create_off, a.create_ordinal);
+    rec_mark(a, 5);
 }
 
 static int rec_upload(k8sgpu_ctx *ctx, const k8sgpu_pool_table *pools, const k8sgpu_vm_table *vms,
@@ -394,14 +482,35 @@ static int rec_run_coop(k8sgpu_ctx *ctx, cudaStream_t s) {
     a.want_ordinals = st.want_ordinals ? 1 : 0;
     const int passes = V ? (a.bits + 7) / 8 : 0;
     st.sorted_vals = (passes & 1) ? a.vals_alt : a.vals;
-    uint32_t want = ceil_div(V ? V : 1u, 512u), pw = ceil_div(P + 1, 256u);
+    // CTAs: enough to spread the tiles (+1 for the pool offsets), few enough that the grid barriers
+    // stay cheap -- at most one per SM while the pass is latency bound (measured at config 2:
+    // 98-148 CTAs 57-58 us, 196 CTAs 62 us), two per SM beyond that.
+    uint32_t want = ceil_div(V ? V : 1u, 1024u) + 1u, pw = ceil_div(P + 1, 256u);
     if (pw > want) want = pw;
-    uint32_t cap = (uint32_t)ctx->sm_count * (uint32_t)(st.coop_blocks_per_sm < 2 ? st.coop_blocks_per_sm : 2);
-    uint32_t grid = want < 1 ? 1 : (want > cap ? cap : want);
+    const uint32_t per_sm = (V <= (256u << 10) || st.coop_blocks_per_sm < 2) ? 1u : 2u;
+    uint32_t cap = (uint32_t)ctx->sm_count * per_sm;
+    uint32_t grid = want > cap ? cap : want;
+    if (const char *e = getenv("K8SGPU_REC_GRID")) {  // developer knob: CTAs in the cooperative grid
+        uint32_t g = (uint32_t)atoi(e);
+        if (g >= 1 && g <= (uint32_t)ctx->sm_count * (uint32_t)st.coop_blocks_per_sm) grid = g;
+    }
+    static const bool want_prof = getenv("K8SGPU_REC_PROF") != nullptr;
+    a.prof = want_prof ? reinterpret_cast<unsigned long long *>(cnts + 16) : nullptr;  // counters[16..28)
     void *args[] = {&a};
     K8S_CUDA(ctx, cudaLaunchCooperativeKernel((void *)reconcile_coop_kernel, dim3(grid), dim3(256), args, 0, s));
     ctx->stats.kernel_launches++;
-    return rec_finish(ctx, s);
+    int rc = rec_finish(ctx, s);
+    if (want_prof && rc == K8SGPU_OK) {  // developer aid: phase boundaries (CTA 0's clock), microseconds
+        unsigned long long t[8];
+        K8S_CUDA(ctx, cudaMemcpy(t, cnts + 16, sizeof t, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "[reconcile coop CTA 0, tile 0] match %.1f hist %.1f barrier %.1f us\n", (t[6] - t[1]) / 1e3,
+                (t[7] - t[6]) / 1e3, (t[2] - t[7]) / 1e3);
+        fprintf(stderr, "[reconcile coop P=%u V=%u grid=%u] lut %.1f match+hist %.1f pools+sort %.1f gather %.1f "
+                        "ordinals %.1f kernel %.1f us, events %.1f us\n",
+                P, V, grid, (t[1] - t[0]) / 1e3, (t[2] - t[1]) / 1e3, (t[3] - t[2]) / 1e3, (t[4] - t[3]) / 1e3,
+                (t[5] - t[4]) / 1e3, (t[5] - t[0]) / 1e3, ctx->stats.device_ms * 1e3);
+    }
+    return rc;
 }
 
 static int rec_run(k8sgpu_ctx *ctx, int want_members, int want_ordinals) {
