@@ -557,6 +557,26 @@ __device__ __forceinline__ Seg seg_block_scan(Seg x, Seg *block_total) {
     return out;
 }
 
+// Exclusive carry of block vb (everything in blocks [0, vb)), computed by the calling CTA alone
+// from the per-block totals: thread t folds its contiguous share, one block scan orders the
+// shares.  All threads return the same value.  Replaces the one-CTA carry phase and its grid
+// barrier while the list is short (kLocalCarryMaxBlocks).
+constexpr uint32_t kLocalCarryMaxBlocks = 1024;
+__device__ __forceinline__ Seg seg_carry_local(const Seg *__restrict__ block_tot, uint32_t vb) {
+    __shared__ Seg total;
+    const uint32_t per = (vb + kSegThreads - 1) / kSegThreads;
+    Seg run;
+    run.g = run.c = run.m = run.head = 0;
+    for (uint32_t j = 0; j < per; ++j) {
+        const uint32_t b = threadIdx.x * per + j;
+        if (b < vb) run = seg_combine(run, block_tot[b]);
+    }
+    Seg inc = seg_block_scan(run, nullptr);
+    if (threadIdx.x == kSegThreads - 1) total = inc;
+    __syncthreads();  // also: seg_block_scan's shared scratch is free again
+    return total;
+}
+
 __device__ __forceinline__ Seg load_seg(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals,
                                         const uint32_t *__restrict__ active, const PodQ *__restrict__ podq,
                                         uint32_t i, uint32_t na, uint32_t *key_out) {
@@ -771,14 +791,18 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
     }
     grid.sync();
     prof_mark(a, 3);
-    if (cta == 0) seg_carry_block(a.seg, nb2);
-    grid.sync();
+    const bool local_carry = nb2 <= kLocalCarryMaxBlocks;
+    if (!local_carry) {
+        if (cta == 0) seg_carry_block(a.seg, nb2);
+        grid.sync();
+    }
     prof_mark(a, 4);
     for (uint32_t vb = cta; vb < nb2; vb += G) {  // S <= free (a13); admitted flags go to offs[] for now
         const uint32_t i = vb * kSegThreads + tid;
+        const Seg carry = local_carry ? seg_carry_local(a.seg, vb) : a.seg[vb];
         uint32_t key;
         Seg x = load_seg(sk, sv, a.active, a.podq, i, na, &key);
-        Seg s = seg_combine(a.seg[vb], seg_block_scan(x, nullptr));
+        Seg s = seg_combine(carry, seg_block_scan(x, nullptr));
         if (i < na) {
             uint32_t ok = 0;
             if (key < N) {
@@ -791,31 +815,102 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
     }
     grid.sync();
     prof_mark(a, 5);
-    // free -= admitted (commutative integer atomics), pending flags in ORIGINAL active order
-    for (uint32_t i = cta * 256 + tid; i < na; i += G * 256) {
-        if (a.offs[i]) {
-            uint32_t key = sk[i];
-            const PodQ *q = a.podq + a.active[sv[i]];
-            if (q->req_gpu) atomicSub(&a.freec[key], q->req_gpu);
-            if (q->req_mcpu) atomicSub(&a.freec[(size_t)N + key], q->req_mcpu);
-            if (q->req_mib) atomicSub(&a.freec[2 * (size_t)N + key], q->req_mib);
+    // free -= admitted (commutative integer atomics), pending flags in ORIGINAL active order, and
+    // the number of still-pending pods per 256-element chunk (in hist_scan: the sort is done with it)
+    const uint32_t nt = (na + kScanTile - 1) / kScanTile, nchunks = (na + 255u) / 256u;
+    const bool local_scan = nt <= kLocalScanMaxTiles;
+    uint32_t *chunk_tot = a.hist_scan;
+    __shared__ uint32_t red[8];
+    for (uint32_t c = cta; c < nchunks; c += G) {
+        const uint32_t i = c * 256 + tid;
+        uint32_t f = 0;
+        if (i < na) {
+            if (a.offs[i]) {
+                uint32_t key = sk[i];
+                const PodQ *q = a.podq + a.active[sv[i]];
+                if (q->req_gpu) atomicSub(&a.freec[key], q->req_gpu);
+                if (q->req_mcpu) atomicSub(&a.freec[(size_t)N + key], q->req_mcpu);
+                if (q->req_mib) atomicSub(&a.freec[2 * (size_t)N + key], q->req_mib);
+            }
+            f = a.assign[a.active[i]] == K8SGPU_ASSIGN_PENDING ? 1u : 0u;
+            a.flags[i] = f;
         }
-        a.flags[i] = a.assign[a.active[i]] == K8SGPU_ASSIGN_PENDING ? 1u : 0u;
+        const uint32_t cnt = (uint32_t)__syncthreads_count((int)f);
+        if (tid == 0) chunk_tot[c] = cnt;
     }
     grid.sync();
     prof_mark(a, 6);
-    coop_exclusive_scan(grid, a.flags, a.offs, na, a.scan_sums, a.counters + 1);
-    prof_mark(a, 7);
-    if (cta == 0 && tid == 0) {  // tell the host now: it can queue the next round while we finish
-        volatile uint32_t *mb = a.mailbox;
-        mb[1] = a.counters[1];
-        mb[2] = a.counters[0];
-        __threadfence_system();
-        mb[0] = a.seq;
+    if (local_scan) {
+        // Stable compaction without a scan phase: each CTA adds up the pending counts of the tiles
+        // before its own, scans its tile in registers and writes the survivors.  The CTA that owns
+        // the last tile knows the next round's length and tells the host before it scatters.
+        for (uint32_t vt = cta; vt < nt; vt += G) {
+            uint32_t before = 0;
+            if (tid < 32) {
+                for (uint32_t t = tid; t < vt * (kScanTile / 256u); t += 32) before += chunk_tot[t];
+                before = __reduce_add_sync(0xFFFFFFFFu, before);
+                if (tid == 0) red[0] = before;
+            }
+            const uint32_t i0 = vt * kScanTile + tid * 8u;
+            uint32_t f[8], act[8], mine = 0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const bool in = i0 + k < na;
+                f[k] = in ? a.flags[i0 + k] : 0u;
+                act[k] = in ? a.active[i0 + k] : 0u;
+                mine += f[k];
+            }
+            const uint32_t inc = warp_incl_scan(mine, tid & 31);
+            __syncthreads();  // red[0] written; red[] of the previous phase / tile no longer read
+            before = red[0];
+            __syncthreads();
+            if ((tid & 31u) == 31u) red[tid >> 5] = inc;
+            __syncthreads();
+            uint32_t woff = 0, all = 0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) {
+                const uint32_t t = red[w];
+                if (w < (int)(tid >> 5)) woff += t;
+                all += t;
+            }
+            if (vt == nt - 1 && tid == 0) {  // tell the host now: it can queue the next round while we finish
+                a.counters[1] = before + all;
+                volatile uint32_t *mb = a.mailbox;
+                mb[1] = before + all;
+                mb[2] = a.counters[0];
+                __threadfence_system();
+                mb[0] = a.seq;
+            }
+            uint32_t pos = before + woff + inc - mine;
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                if (f[k]) a.next_active[pos++] = act[k];
+            __syncthreads();
+        }
+        if (nt == 0 && cta == 0 && tid == 0) {  // (not reached: the host never launches with na == 0)
+            a.counters[1] = 0;
+            volatile uint32_t *mb = a.mailbox;
+            mb[1] = 0;
+            mb[2] = a.counters[0];
+            __threadfence_system();
+            mb[0] = a.seq;
+        }
+        prof_mark(a, 7);
+    } else {
+        coop_exclusive_scan(grid, a.flags, a.offs, na, a.scan_sums, a.counters + 1);
+        prof_mark(a, 7);
+        if (cta == 0 && tid == 0) {  // tell the host now: it can queue the next round while we finish
+            volatile uint32_t *mb = a.mailbox;
+            mb[1] = a.counters[1];
+            mb[2] = a.counters[0];
+            __threadfence_system();
+            mb[0] = a.seq;
+        }
+        // stable compaction of the active list
+        for (uint32_t i = cta * 256 + tid; i < na; i += G * 256)
+            if (a.flags[i]) a.next_active[a.offs[i]] = a.active[i];
     }
-    // stable compaction of the active list, and the next round's packed node records
-    for (uint32_t i = cta * 256 + tid; i < na; i += G * 256)
-        if (a.flags[i]) a.next_active[a.offs[i]] = a.active[i];
+    // the next round's packed node records
     for (uint32_t i = cta * 256 + tid; i < a.n_pad; i += G * 256)
         a.nodeq[i] = make_nodeq(a.node_cols, a.freec, N, i, nullptr, 0);
     prof_mark(a, 8);
