@@ -688,6 +688,7 @@ __global__ void count_placed_kernel(const int32_t *__restrict__ assign, uint32_t
 
 struct AdmitArgs {
     const unsigned long long *best_key;  // by active position (score_kernel output)
+    const int32_t *proposals;            // or: node row per active position (exchanged between GPUs); else null
     const PodQ *podq;
     const uint32_t *active;
     uint32_t *next_active;
@@ -731,11 +732,21 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
 #pragma unroll
         for (uint32_t r = 0; r < kSortTile / 256; ++r) {
             uint32_t i = vt * kSortTile + r * 256 + tid;
-            k64[r] = i < na ? a.best_key[i] : 0ull;
             pod[r] = i < na ? a.active[i] : 0u;
+            if (a.proposals) {  // already decoded: re-encode as "distance 0 from rot = node" below
+                int32_t b = i < na ? a.proposals[i] : -1;
+                if (b < -1 || b >= (int32_t)N) {  // not something score_kernel can produce: a stale or
+                    atomicOr(&a.counters[0], kErrProposal);  // unsynchronised buffer was handed in
+                    b = -1;
+                }
+                k64[r] = b < 0 ? 0ull : (0x100000000ull | (unsigned long long)(0xFFFFFFFFu - (uint32_t)b));
+            } else {
+                k64[r] = i < na ? a.best_key[i] : 0ull;
+            }
         }
 #pragma unroll
-        for (uint32_t r = 0; r < kSortTile / 256; ++r) rot[r] = k64[r] != 0ull ? a.podq[pod[r]].rot : 0u;
+        for (uint32_t r = 0; r < kSortTile / 256; ++r)
+            rot[r] = (k64[r] != 0ull && !a.proposals) ? a.podq[pod[r]].rot : 0u;
 #pragma unroll
         for (uint32_t r = 0; r < kSortTile / 256; ++r) {
             uint32_t i = vt * kSortTile + r * 256 + tid;
@@ -1011,10 +1022,12 @@ static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_bes
     PlaceState &st = ctx->place;
     if (hi > st.n_active || lo > hi) return fail(ctx, K8SGPU_E_ARG, "score: bad slice [%u,%u) of %u", lo, hi, st.n_active);
     // node records from the current free columns (validated on the first round)
-    if (prep)
+    if (prep) {
         K8S_LAUNCH(ctx, node_prep_kernel, ceil_div(st.n_pad, 256), 256, 0, s, st.node_cols.as<uint32_t>(),
                    st.free_cols.as<uint32_t>(), st.n, st.n_pad, st.nodeq.as<NodeQ>(), st.counters.as<uint32_t>(),
                    st.rounds == 0 ? 1 : 0);
+        st.nodeq_stale = false;
+    }
     const uint32_t cnt = hi - lo;
     if (cnt == 0) return K8SGPU_OK;
     const uint32_t n_tiles = st.n_pad / kNodeTile;
@@ -1124,13 +1137,14 @@ static int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t 
     st.rounds++;
     st.cur ^= 1;
     st.n_active = ctx->h_pinned[1];
+    st.nodeq_stale = true;  // the free columns changed under the packed node records
     if (n_active_out) *n_active_out = st.n_active;
     return K8SGPU_OK;
 }
 
 // Single-launch admission (admit_coop_kernel) for the in-library single-GPU loop: consumes
 // best_key[0..n_active) as score_kernel left it, and leaves the next round's node records ready.
-static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s) {
+static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals = nullptr) {
     PlaceState &st = ctx->place;
     const uint32_t na = st.n_active;
     uint32_t *cnts = st.counters.as<uint32_t>();
@@ -1143,6 +1157,7 @@ static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s) {
     const uint32_t nb = ceil_div(na, kSortTile);
     AdmitArgs a;
     a.best_key = st.best_key.as<unsigned long long>();
+    a.proposals = proposals;
     a.podq = st.podq.as<PodQ>();
     a.active = st.active[st.cur].as<uint32_t>();
     a.next_active = st.active[st.cur ^ 1].as<uint32_t>();
@@ -1197,6 +1212,9 @@ static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s) {
         }
     }
     const uint32_t next_count = mb[1], err_flags = mb[2];
+    if (err_flags & kErrProposal)
+        return fail(ctx, K8SGPU_E_ARG, "place: proposal buffer holds values outside [-1, n): was it written on "
+                                       "another stream than the one passed here?");
     if (err_flags != 0u)
         return fail(ctx, K8SGPU_E_ARG, "place: %s table outside the input domain (see k8sgpu.h)",
                     (err_flags & kErrNode) ? "node" : "pod");
@@ -1215,6 +1233,7 @@ static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s) {
     st.rounds++;
     st.cur ^= 1;
     st.n_active = ctx->h_pinned[1];
+    st.nodeq_stale = false;  // the kernel rebuilt the packed node records from the new free columns
     return K8SGPU_OK;
 }
 
@@ -1242,21 +1261,24 @@ static int round_end(k8sgpu_ctx *ctx, cudaStream_t s) {
     return K8SGPU_OK;
 }
 
+static bool coop_admission() {
+    if (const char *e = getenv("K8SGPU_COOP")) return atoi(e) != 0;
+    return true;
+}
+
 // Rounds of score + admit until no pod is active (or max_rounds is reached).
 static int run_rounds(k8sgpu_ctx *ctx, cudaStream_t s) {
     PlaceState &st = ctx->place;
     // Admission as ONE cooperative launch per round (two launches per round in all): measured
     // ~3 % faster per config-3 step than the chain of ~20 small kernels.  K8SGPU_COOP=0 selects
     // the chain (the round-at-a-time API always uses it); both give identical results.
-    bool coop = true;
-    if (const char *e = getenv("K8SGPU_COOP")) coop = atoi(e) != 0;
+    const bool coop = coop_admission();
     int rc = K8SGPU_OK;
     while (st.n_active > 0 && (st.max_rounds == 0 || st.rounds < st.max_rounds)) {
         if (coop) {
             rc = round_score(ctx, 0, st.n_active, nullptr, s, /*prep=*/st.nodeq_stale, /*finalize=*/false);
             if (rc) return rc;
             rc = round_admit_coop(ctx, s);  // leaves the next round's node records ready
-            st.nodeq_stale = false;
         } else {
             rc = round_score(ctx, 0, st.n_active, st.best.as<int32_t>(), s);
             if (rc) return rc;
@@ -1533,14 +1555,18 @@ extern "C" int k8sgpu_place_round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *po
 extern "C" int k8sgpu_place_round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, void *stream) {
     K8S_ENTER(ctx);
     if (!d_best && hi > lo) return fail(ctx, K8SGPU_E_ARG, "round_score: NULL device buffer");
-    return round_score(ctx, lo, hi, d_best, ::k8sgpu::pick_stream(ctx, stream));
+    return round_score(ctx, lo, hi, d_best, ::k8sgpu::pick_stream(ctx, stream), /*prep=*/ctx->place.nodeq_stale);
 }
 
 extern "C" int k8sgpu_place_round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, void *stream,
                                         uint32_t *n_active) {
     K8S_ENTER(ctx);
     if (!d_best_all && ctx->place.n_active) return fail(ctx, K8SGPU_E_ARG, "round_admit: NULL device buffer");
-    return round_admit(ctx, d_best_all, ::k8sgpu::pick_stream(ctx, stream), n_active);
+    cudaStream_t s = ::k8sgpu::pick_stream(ctx, stream);
+    if (!coop_admission() || ctx->place.n_active == 0) return round_admit(ctx, d_best_all, s, n_active);
+    int rc = round_admit_coop(ctx, s, d_best_all);  // one launch; also rebuilds the packed node records
+    if (rc == K8SGPU_OK && n_active) *n_active = ctx->place.n_active;
+    return rc;
 }
 
 extern "C" int k8sgpu_place_round_end(k8sgpu_ctx *ctx, void *stream) {
@@ -1597,7 +1623,7 @@ extern "C" int k8sgpu_place_round_score_p2p(k8sgpu_ctx *ctx, uint32_t lo, uint32
     if (st.peer_world < 1) return fail(ctx, K8SGPU_E_ARG, "round_score_p2p: no peers imported");
     if (st.m > st.peer_m) return fail(ctx, K8SGPU_E_CAPACITY, "round_score_p2p: exchange buffer holds %u proposals, tables have %u pods", st.peer_m, st.m);
     cudaStream_t s = pick_stream(ctx, stream);
-    int rc = round_score(ctx, lo, hi, nullptr, s, /*prep=*/true, /*finalize=*/false);
+    int rc = round_score(ctx, lo, hi, nullptr, s, /*prep=*/st.nodeq_stale, /*finalize=*/false);
     if (rc) return rc;
     if (hi > lo) {
         // Rounds alternate between the two halves of every exchange buffer: a fast rank's stores of

@@ -3,7 +3,8 @@
 //
 //   tag filter (listManagedVMs, README.md:188-189,238)     -> match_kernel (128-bit SoA loads)
 //   existingVMs of each pool, in list order                -> stable sort of rows by pool
-//   currentCount := len(existingVMs)  (README.md:195)      -> segment bounds (binary search)
+//   currentCount := len(existingVMs)  (README.md:195)      -> per-pool counters filled by the tag filter
+//                                                             (chain of kernels: segment bounds of the sort)
 //   scaleUp / scaleDown counts (README.md:199-201,210-212) -> pool_kernel
 //   vmsToDelete := existingVMs[:scaleDownCount] (:214)     -> victim_gather_kernel
 //   names of new VMs (README.md:204)         -> ordinal bitmap kernels
