@@ -11,8 +11,8 @@
 //   admit       : stable sort of proposals by node, segmented prefix sums in pod order,
 //                 S <= free test (a13), free -= admitted, stable compaction of the active list.
 // In the in-library loop (k8sgpu_place / _run) finalize, admit and the next round's node_prep are
-// ONE cooperative launch (admit_coop_kernel); the round-at-a-time API used across GPUs runs them
-// as separate kernels.  k8sgpu_place_gang wraps the same loop in reject / release / retry
+// ONE cooperative launch (admit_coop_kernel); the round-at-a-time API used across GPUs feeds the
+// same kernel the exchanged proposals (K8SGPU_COOP=0: separate kernels).  k8sgpu_place_gang wraps the same loop in reject / release / retry
 // iterations.  Integer only; no atomics decide any result except commutative max / add.
 #include <cstdlib>
 
@@ -1065,11 +1065,8 @@ static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_bes
 #define K8S_SCORE(P, R, B)                                                                                         \
     K8S_LAUNCH(ctx, (score_kernel<P, R, B>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
                st.active[st.cur].as<uint32_t>(), lo, hi, bk, st.n, use_atomic, 0xFFFFFFFFu)
-    int mb = 0;
-    if (const char *e = getenv("K8SGPU_MB")) mb = atoi(e);
-    if (ppt == 4 && mb == 2) K8S_SCORE(4, 4, 2);
-    else if (ppt == 4) K8S_SCORE(4, 4, 3);
-    else if (ppt == 2 && res >= 4 && mb == 5) K8S_SCORE(2, 4, 5);
+    // third argument: resident CTAs per SM the register budget is set for (measured best per variant)
+    if (ppt == 4) K8S_SCORE(4, 4, 3);
     else if (ppt == 2 && res >= 4) K8S_SCORE(2, 4, 4);
     else if (ppt == 2 && res == 3) K8S_SCORE(2, 3, 5);
     else if (ppt == 2 && res == 2) K8S_SCORE(2, 2, 5);
