@@ -169,7 +169,8 @@ int k8sgpu_place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out);
  *   3. pods still unplaced (-1) whose gang is not rejected are retried against the released
  *      capacity; back to 2 until an iteration rejects no new gang.
  * gang_id[p] == K8SGPU_NONE_U32: the pod is on its own.  gang_ok[g] (may be NULL) = 1 if kept.
- * Queues (`queue: default`, :650) are not modelled.  Single GPU. */
+ * Queues (`queue: default`, :650) are not modelled.  k8sgpu_place_gang is the one-call form on
+ * one GPU; the stepwise form below lets one process per GPU shard the rounds. */
 #define K8SGPU_ASSIGN_GANG (-3)
 typedef struct {
     uint32_t n_gangs;
@@ -199,6 +200,20 @@ int k8sgpu_place_round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, void 
 int k8sgpu_place_round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, void *stream);
 int k8sgpu_place_round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, void *stream, uint32_t *n_active);
 int k8sgpu_place_round_end(k8sgpu_ctx *ctx, void *stream);
+
+/* Gang placement one step at a time, for the same cooperating processes.  After
+ * k8sgpu_place_upload:
+ *   gang_begin    : gang table in, state reset; *n_active = m
+ *   (rounds)      : k8sgpu_place_round_score / _score_p2p + _admit until the active count is 0
+ *   gang_verdicts : steps 2 and 3 of k8sgpu_place_gang on this replica; *n_active = length of the
+ *                   retry list -- 0 means final, otherwise run the rounds again and call it again
+ *   gang_end      : as k8sgpu_place_round_end; gang_ok[n_gangs] (host, may be NULL) = 1 if kept.
+ * The verdict kernels are deterministic functions of the replicated state, so every rank reaches
+ * the same verdicts without a collective. */
+int k8sgpu_place_gang_begin(k8sgpu_ctx *ctx, const k8sgpu_gang_table *gangs, const k8sgpu_policy *policy,
+                            void *stream, uint32_t *n_active);
+int k8sgpu_place_gang_verdicts(k8sgpu_ctx *ctx, void *stream, uint32_t *n_active);
+int k8sgpu_place_gang_end(k8sgpu_ctx *ctx, void *stream, int32_t *gang_ok);
 
 /* Peer exchange for the round-at-a-time form: instead of an NCCL all-gather of the proposal
  * slices, the kernel that decodes the scores stores every proposal directly into EVERY rank's

@@ -26,6 +26,7 @@ EXPORTS = (
     "k8sgpu_place_round_begin", "k8sgpu_place_round_score", "k8sgpu_place_round_admit", "k8sgpu_place_round_end",
     "k8sgpu_debug_sort_pairs", "k8sgpu_debug_exclusive_scan", "k8sgpu_exclusive_scan_noalloc",
     "k8sgpu_place_gang", "k8sgpu_peer_export", "k8sgpu_peer_import", "k8sgpu_place_round_score_p2p",
+    "k8sgpu_place_gang_begin", "k8sgpu_place_gang_verdicts", "k8sgpu_place_gang_end",
 )
 ASSIGN_GANG = -3
 SCAN_NOALLOC_MAX_N = 1 << 24
@@ -123,6 +124,9 @@ def load() -> C.CDLL:
         L.k8sgpu_peer_export.argtypes = [vp, C.c_uint32, vp, C.POINTER(vp)]
         L.k8sgpu_peer_import.argtypes = [vp, C.c_int, C.c_int, vp]
         L.k8sgpu_place_round_score_p2p.argtypes = [vp, C.c_uint32, C.c_uint32, vp]
+        L.k8sgpu_place_gang_begin.argtypes = [vp, C.POINTER(GangTable), C.POINTER(Policy), vp, u32p]
+        L.k8sgpu_place_gang_verdicts.argtypes = [vp, vp, u32p]
+        L.k8sgpu_place_gang_end.argtypes = [vp, vp, i32p]
         L.k8sgpu_debug_sort_pairs.argtypes = [vp, u32p, u32p, C.c_uint32, C.c_int, u32p, u32p]
         L.k8sgpu_debug_exclusive_scan.argtypes = [vp, u32p, C.c_uint32, u32p, u32p]
         L.k8sgpu_exclusive_scan_noalloc.argtypes = [vp, vp, C.c_uint32, vp, vp, vp]
@@ -268,6 +272,29 @@ class Context:
         self._check(self._L.k8sgpu_place_round_admit(self._h, C.c_void_p(d_best_all_ptr), C.c_void_p(stream),
                                                      C.byref(na)))
         return na.value
+
+    # gang placement one step at a time (see placement.ShardedPlacer.run_gang)
+    def gang_begin(self, gang_id, min_available, flags: int = 0, max_rounds: int = 0, stream: int = 0) -> int:
+        gid, gidp = _u32(gang_id)
+        mn, mnp = _u32(min_available)
+        self._n_gangs = len(mn)
+        gt = GangTable(len(mn), gidp, mnp)
+        pol = Policy(flags, max_rounds)
+        na = C.c_uint32()
+        self._check(self._L.k8sgpu_place_gang_begin(self._h, C.byref(gt), C.byref(pol), C.c_void_p(stream), C.byref(na)))
+        return na.value
+
+    def gang_verdicts(self, stream: int = 0) -> int:
+        na = C.c_uint32()
+        self._check(self._L.k8sgpu_place_gang_verdicts(self._h, C.c_void_p(stream), C.byref(na)))
+        return na.value
+
+    def gang_end(self, stream: int = 0) -> dict:
+        ok = np.zeros(self._n_gangs, np.int32)
+        self._check(self._L.k8sgpu_place_gang_end(self._h, C.c_void_p(stream), ok.ctypes.data_as(i32p)))
+        st = self.stats()
+        st["gang_ok"] = ok
+        return st
 
     def peer_export(self, m: int):
         """-> (64-byte IPC handle of this rank's exchange buffer, its device pointer)."""

@@ -76,6 +76,7 @@ struct PlaceState {
     uint32_t rounds = 0;
     uint64_t evals = 0;
     uint32_t policy_flags = 0, max_rounds = 0;
+    uint32_t n_gangs = 0, gang_iters = 0;  // gang placement: table size, round loops run so far
     int score_res = 2;  // eval_pair variant the pod records are laid out for
     bool nodeq_stale = true;  // packed node records do not reflect free_cols yet
     DevBuf peer_local;        // exchange buffer other ranks store their proposals into (IPC-exported)

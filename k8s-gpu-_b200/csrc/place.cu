@@ -1371,9 +1371,10 @@ __global__ void gang_ok_kernel(const uint32_t *__restrict__ state, uint32_t n_ga
     if (g < n_gangs) ok[g] = state[g] ? 0 : 1;
 }
 
-static int place_gang_run(k8sgpu_ctx *ctx, const k8sgpu_gang_table *gangs, const k8sgpu_policy *policy) {
+// Gang table to the device, verdict state cleared.
+static int gang_setup(k8sgpu_ctx *ctx, const k8sgpu_gang_table *gangs, cudaStream_t s) {
     PlaceState &st = ctx->place;
-    cudaStream_t s = ctx->stream;
+    if (!st.uploaded) return fail(ctx, K8SGPU_E_ARG, "place_gang: no tables uploaded");
     const uint32_t G = gangs->n_gangs, M = st.m;
     if (M && !gangs->gang_id) return fail(ctx, K8SGPU_E_ARG, "place_gang: gang_id is NULL");
     if (G && !gangs->min_available) return fail(ctx, K8SGPU_E_ARG, "place_gang: min_available is NULL");
@@ -1385,55 +1386,88 @@ static int place_gang_run(k8sgpu_ctx *ctx, const k8sgpu_gang_table *gangs, const
     if (G) K8S_CUDA(ctx, cudaMemcpyAsync(st.gang_min.p, gangs->min_available, (size_t)G * 4, cudaMemcpyHostToDevice, s));
     ctx->stats.h2d_bytes += ((uint64_t)M + G) * 4;
     K8S_CUDA(ctx, cudaMemsetAsync(st.gang_state.p, 0, (size_t)G * 8 + 16, s));
-    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
-    int rc = round_begin(ctx, policy, s);
-    if (rc) return rc;
+    st.n_gangs = G;
+    st.gang_iters = 1;
+    return K8SGPU_OK;
+}
+
+// After a round loop that left no pod active: count placed members, reject gangs below
+// min_available for good, release their reservations, and build the retry list (unplaced pods of
+// surviving gangs, ascending pod index).  *n_retry == 0 means the placement is final.
+static int gang_verdicts(k8sgpu_ctx *ctx, cudaStream_t s, uint32_t *n_retry_out) {
+    PlaceState &st = ctx->place;
+    const uint32_t G = st.n_gangs, M = st.m;
     uint32_t *cnts = st.counters.as<uint32_t>();
-    uint32_t iters = 0;
+    *n_retry_out = 0;
+    if (M == 0) return K8SGPU_OK;
+    K8S_CUDA(ctx, cudaMemsetAsync(st.gang_count.p, 0, (size_t)G * 4 + 16, s));
+    K8S_CUDA(ctx, cudaMemsetAsync(cnts + 3, 0, 4, s));
+    K8S_LAUNCH(ctx, gang_count_kernel, ceil_div(M, 256), 256, 0, s, st.assign.as<int32_t>(),
+               st.gang_id.as<uint32_t>(), M, G, st.gang_count.as<uint32_t>(), cnts);
+    if (G)
+        K8S_LAUNCH(ctx, gang_decide_kernel, ceil_div(G, 256), 256, 0, s, st.gang_count.as<uint32_t>(),
+                   st.gang_min.as<uint32_t>(), G, st.gang_state.as<uint32_t>(), cnts);
+    uint32_t *flags = st.flags.as<uint32_t>(), *offs = flags + st.m;
+    K8S_LAUNCH(ctx, gang_release_kernel, ceil_div(M, 256), 256, 0, s, st.assign.as<int32_t>(),
+               st.gang_id.as<uint32_t>(), st.podq.as<PodQ>(), M, G, st.n, st.gang_state.as<uint32_t>(),
+               st.free_cols.as<uint32_t>(), flags);
+    int rc = exclusive_scan_u32(ctx, s, flags, offs, M, st.scan_tmp, cnts + 1);
+    if (rc) return rc;
+    K8S_LAUNCH(ctx, gang_retry_compact_kernel, ceil_div(M, 256), 256, 0, s, flags, offs, M,
+               st.active[st.cur].as<uint32_t>());
+    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, cnts, 16, cudaMemcpyDeviceToHost, s));
+    K8S_CUDA(ctx, cudaStreamSynchronize(s));
+    if (ctx->h_pinned[0] != 0u)
+        return fail(ctx, K8SGPU_E_ARG, "place_gang: a gang id is >= n_gangs, or a table is outside the input domain");
+    const uint32_t n_new = ctx->h_pinned[3], n_retry = ctx->h_pinned[1];
+    if (n_new == 0) {  // nothing was rejected: the flagged pods keep their verdict (-1)
+        if (n_retry)   // they were marked PENDING for a retry that will not happen: restore -1
+            K8S_LAUNCH(ctx, gang_unretry_kernel, ceil_div(M, 256), 256, 0, s, st.assign.as<int32_t>(), flags, M);
+        return K8SGPU_OK;
+    }
+    st.n_active = n_retry;
+    st.nodeq_stale = true;  // free columns changed under the packed records
+    if (n_retry) st.gang_iters++;
+    *n_retry_out = n_retry;
+    return K8SGPU_OK;
+}
+
+static int place_gang_run(k8sgpu_ctx *ctx, const k8sgpu_gang_table *gangs, const k8sgpu_policy *policy) {
+    PlaceState &st = ctx->place;
+    cudaStream_t s = ctx->stream;
+    int rc = gang_setup(ctx, gangs, s);
+    if (rc) return rc;
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
+    rc = round_begin(ctx, policy, s);
+    if (rc) return rc;
     for (;;) {
         rc = run_rounds(ctx, s);  // step 1: policy v0 rounds over the current candidates
         if (rc) return rc;
-        ++iters;
-        if (st.n_active > 0 || M == 0) break;  // max_rounds reached: no verdicts on half a placement
-        // step 2: count placed members, reject gangs below min_available, release their reservations
-        K8S_CUDA(ctx, cudaMemsetAsync(st.gang_count.p, 0, (size_t)G * 4 + 16, s));
-        K8S_CUDA(ctx, cudaMemsetAsync(cnts + 3, 0, 4, s));
-        K8S_LAUNCH(ctx, gang_count_kernel, ceil_div(M, 256), 256, 0, s, st.assign.as<int32_t>(),
-                   st.gang_id.as<uint32_t>(), M, G, st.gang_count.as<uint32_t>(), cnts);
-        if (G)
-            K8S_LAUNCH(ctx, gang_decide_kernel, ceil_div(G, 256), 256, 0, s, st.gang_count.as<uint32_t>(),
-                       st.gang_min.as<uint32_t>(), G, st.gang_state.as<uint32_t>(), cnts);
-        uint32_t *flags = st.flags.as<uint32_t>(), *offs = flags + st.m;
-        K8S_LAUNCH(ctx, gang_release_kernel, ceil_div(M, 256), 256, 0, s, st.assign.as<int32_t>(),
-                   st.gang_id.as<uint32_t>(), st.podq.as<PodQ>(), M, G, st.n, st.gang_state.as<uint32_t>(),
-                   st.free_cols.as<uint32_t>(), flags);
-        // step 3: the retry list, ascending in pod index (stable compaction)
-        rc = exclusive_scan_u32(ctx, s, flags, offs, M, st.scan_tmp, cnts + 1);
+        if (st.n_active > 0) break;  // max_rounds reached: no verdicts on half a placement
+        uint32_t n_retry = 0;
+        rc = gang_verdicts(ctx, s, &n_retry);  // steps 2 and 3
         if (rc) return rc;
-        K8S_LAUNCH(ctx, gang_retry_compact_kernel, ceil_div(M, 256), 256, 0, s, flags, offs, M,
-                   st.active[st.cur].as<uint32_t>());
-        K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, cnts, 16, cudaMemcpyDeviceToHost, s));
-        K8S_CUDA(ctx, cudaStreamSynchronize(s));
-        if (ctx->h_pinned[0] != 0u) return fail(ctx, K8SGPU_E_ARG, "place_gang: a gang id is >= n_gangs, or a table is outside the input domain");
-        const uint32_t n_new = ctx->h_pinned[3], n_retry = ctx->h_pinned[1];
-        if (n_new == 0) {  // nothing was rejected: the flagged pods keep their verdict (-1)
-            if (n_retry) {
-                // they were marked PENDING for a retry that will not happen: restore -1
-                K8S_LAUNCH(ctx, gang_unretry_kernel, ceil_div(M, 256), 256, 0, s, st.assign.as<int32_t>(), flags, M);
-            }
-            break;
-        }
-        st.n_active = n_retry;
-        st.nodeq_stale = true;  // free columns changed under the packed records
         if (n_retry == 0) break;
     }
     K8S_CUDA(ctx, cudaEventRecord(ctx->ev_end, s));
     rc = round_end(ctx, s);
     if (rc) return rc;
-    ctx->stats.gang_iterations = iters;
+    ctx->stats.gang_iterations = st.gang_iters;
     float ms = 0.f;
     K8S_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
     ctx->stats.device_ms = ms;
+    return K8SGPU_OK;
+}
+
+// gang_ok[g] = 1 unless gang g was rejected; host buffer of n_gangs entries.
+static int gang_ok_download(k8sgpu_ctx *ctx, cudaStream_t s, int32_t *gang_ok) {
+    PlaceState &st = ctx->place;
+    if (!gang_ok || !st.n_gangs) return K8SGPU_OK;
+    int32_t *d_ok = reinterpret_cast<int32_t *>(st.gang_count.p);  // reuse: counts are no longer needed
+    K8S_LAUNCH(ctx, gang_ok_kernel, ceil_div(st.n_gangs, 256), 256, 0, s, st.gang_state.as<uint32_t>(), st.n_gangs, d_ok);
+    K8S_CUDA(ctx, cudaMemcpyAsync(gang_ok, d_ok, (size_t)st.n_gangs * 4, cudaMemcpyDeviceToHost, s));
+    K8S_CUDA(ctx, cudaStreamSynchronize(s));
+    ctx->stats.d2h_bytes += (uint64_t)st.n_gangs * 4;
     return K8SGPU_OK;
 }
 
@@ -1503,15 +1537,42 @@ extern "C" int k8sgpu_place_gang(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes
     if (rc) return rc;
     rc = place_gang_run(ctx, gangs, policy);
     if (rc) return rc;
-    if (gang_ok && gangs->n_gangs) {
-        PlaceState &st = ctx->place;
-        int32_t *d_ok = reinterpret_cast<int32_t *>(st.gang_count.p);  // reuse: counts are no longer needed
-        K8S_LAUNCH(ctx, gang_ok_kernel, ceil_div(gangs->n_gangs, 256), 256, 0, ctx->stream,
-                   st.gang_state.as<uint32_t>(), gangs->n_gangs, d_ok);
-        K8S_CUDA(ctx, cudaMemcpyAsync(gang_ok, d_ok, (size_t)gangs->n_gangs * 4, cudaMemcpyDeviceToHost, ctx->stream));
-        ctx->stats.d2h_bytes += (uint64_t)gangs->n_gangs * 4;
-    }
+    rc = gang_ok_download(ctx, ctx->stream, gang_ok);
+    if (rc) return rc;
     return place_download(ctx, out);
+}
+
+// Gang placement one step at a time (one process per GPU): begin, then rounds through the
+// k8sgpu_place_round_* entries until no pod is active, then verdicts; repeat while verdicts
+// returns a retry list; end.  Every rank runs the verdict kernels on its own (identical) replica.
+extern "C" int k8sgpu_place_gang_begin(k8sgpu_ctx *ctx, const k8sgpu_gang_table *gangs, const k8sgpu_policy *policy,
+                                       void *stream, uint32_t *n_active) {
+    K8S_ENTER(ctx);
+    reset_call_stats(ctx);
+    if (!gangs) return fail(ctx, K8SGPU_E_ARG, "place_gang: NULL gang table");
+    cudaStream_t s = pick_stream(ctx, stream);
+    int rc = gang_setup(ctx, gangs, s);
+    if (rc) return rc;
+    rc = round_begin(ctx, policy, s);
+    if (rc) return rc;
+    if (n_active) *n_active = ctx->place.n_active;
+    return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_place_gang_verdicts(k8sgpu_ctx *ctx, void *stream, uint32_t *n_active) {
+    K8S_ENTER(ctx);
+    if (!n_active) return fail(ctx, K8SGPU_E_ARG, "place_gang_verdicts: NULL n_active");
+    if (ctx->place.n_active != 0) return fail(ctx, K8SGPU_E_ARG, "place_gang_verdicts: %u pods are still active", ctx->place.n_active);
+    return gang_verdicts(ctx, pick_stream(ctx, stream), n_active);
+}
+
+extern "C" int k8sgpu_place_gang_end(k8sgpu_ctx *ctx, void *stream, int32_t *gang_ok) {
+    K8S_ENTER(ctx);
+    cudaStream_t s = pick_stream(ctx, stream);
+    int rc = round_end(ctx, s);
+    if (rc) return rc;
+    ctx->stats.gang_iterations = ctx->place.gang_iters;
+    return gang_ok_download(ctx, s, gang_ok);
 }
 
 extern "C" int k8sgpu_score_once(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, int32_t *best_node) {

@@ -82,6 +82,16 @@ class CudaEngine:
     def end(self):
         return self.ctx.round_end(self._stream())
 
+    # ---- gang placement, one step at a time (k8sgpu_place_gang_begin / _verdicts / _end)
+    def gang_begin(self, gang_id, min_available, flags, max_rounds):
+        return self.ctx.gang_begin(gang_id, min_available, flags, max_rounds, self._stream())
+
+    def gang_verdicts(self):
+        return self.ctx.gang_verdicts(self._stream())
+
+    def gang_end(self):
+        return self.ctx.gang_end(self._stream())
+
     def download(self):
         return self.ctx.place_download()
 
@@ -121,24 +131,9 @@ class ShardedPlacer:
         lo = min(rank * slice_len, n_active)
         return lo, min(lo + slice_len, n_active), slice_len
 
-    def run(self, flags=0, max_rounds=0):
-        """One whole placement from the uploaded tables.  Returns the library's stats dict plus
-        step_ms (device time of the step on this rank)."""
-        if self.world == 1 and isinstance(self.engine, CudaEngine):
-            st = self.ctx.place_run(flags, max_rounds)  # the in-library loop: fewer host round trips
-            st["step_ms"] = st["device_ms"]
-            return st
+    def _rounds(self, na, rounds, max_rounds):
+        """Score / exchange / admit until no pod is active (or max_rounds); returns (active, rounds)."""
         eng = self.engine
-        torch = getattr(eng, "torch", None)
-        ev = None
-        if torch is not None and isinstance(eng, CudaEngine):
-            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-            ev[0].record()
-        if self.p2p:
-            # no rank may start storing into a peer that is still reading the previous run's last round
-            self.dist.all_reduce(eng._bar)
-        na = eng.begin(flags, max_rounds)
-        rounds = 0
         while na and (max_rounds == 0 or rounds < max_rounds):
             lo, hi, slice_len = self.slice_of(na, self.rank, self.world)
             if self.p2p:
@@ -157,12 +152,59 @@ class ShardedPlacer:
                     allb = mine
                 na = eng.admit(allb)
             rounds += 1
-        st = eng.end()
+        return na, rounds
+
+    def _timed(self):
+        eng = self.engine
+        torch = getattr(eng, "torch", None)
+        if torch is not None and isinstance(eng, CudaEngine):
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record()
+            return ev
+        return None
+
+    @staticmethod
+    def _stop(ev, st):
         if ev is not None:
             ev[1].record()
             ev[1].synchronize()
             st["step_ms"] = ev[0].elapsed_time(ev[1])
         return st
+
+    def run(self, flags=0, max_rounds=0):
+        """One whole placement from the uploaded tables.  Returns the library's stats dict plus
+        step_ms (device time of the step on this rank)."""
+        if self.world == 1 and isinstance(self.engine, CudaEngine):
+            st = self.ctx.place_run(flags, max_rounds)  # the in-library loop: fewer host round trips
+            st["step_ms"] = st["device_ms"]
+            return st
+        eng = self.engine
+        ev = self._timed()
+        if self.p2p:
+            # no rank may start storing into a peer that is still reading the previous run's last round
+            self.dist.all_reduce(eng._bar)
+        na = eng.begin(flags, max_rounds)
+        self._rounds(na, 0, max_rounds)
+        return self._stop(ev, eng.end())
+
+    def run_gang(self, gang_id, min_available, flags=0, max_rounds=0):
+        """Gang placement (k8sgpu.h, "gang placement") with the rounds sharded like run(): rounds
+        until no pod is active, then the verdict step on every replica (deterministic, so no
+        collective), repeated while verdicts hands back a retry list.  The result has gang_ok."""
+        eng = self.engine
+        ev = self._timed()
+        if self.p2p:
+            self.dist.all_reduce(eng._bar)
+        na = eng.gang_begin(gang_id, min_available, flags, max_rounds)
+        rounds = 0
+        while True:
+            na, rounds = self._rounds(na, rounds, max_rounds)
+            if na:  # max_rounds reached: no verdicts on half a placement
+                break
+            na = eng.gang_verdicts()
+            if na == 0:
+                break
+        return self._stop(ev, eng.gang_end())
 
     def download(self):
         return self.engine.download()

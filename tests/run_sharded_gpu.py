@@ -68,6 +68,28 @@ def main():
             if rank == 0:
                 print(f"[sharded x{world}] {name}: rounds={st['rounds']} placed={st['placed']} evals={st['evals']} "
                       f"== single-GPU: {same_single}  all ranks equal: {same_ranks}  == oracle: {same_oracle}", flush=True)
+        # gang placement with the rounds sharded (stepwise C-ABI) vs. the one-call form and the oracle
+        rng = np.random.default_rng(33)
+        nodes, pods = synth.gen_nodes(400, 5), synth.gen_pods(6000, 5)
+        gang = rng.integers(0, 300, 6000).astype(np.uint32)
+        gang[rng.random(6000) < 0.3] = 0xFFFFFFFF
+        mins = rng.integers(0, 14, 300).astype(np.uint32)
+        pl.upload(nodes, pods)
+        st = pl.run_gang(gang, mins)
+        got = pl.download()
+        single = ctx.place_gang(nodes, pods, gang, mins)
+        same = all(np.array_equal(got[k], single[k]) for k in ("assign", "free_gpu", "free_mcpu", "free_mib"))
+        same = same and np.array_equal(st["gang_ok"], single["gang_ok"]) and st["rounds"] == single["rounds"]
+        same = same and st["gang_iterations"] == single["gang_iterations"]
+        same_oracle = None
+        if rank == 0:
+            import oracle as orc
+
+            want = orc.place_gang(nodes, pods, gang, mins, nthreads=os.cpu_count() or 1)
+            same_oracle = np.array_equal(got["assign"], want["assign"]) and np.array_equal(st["gang_ok"], want["gang_ok"])
+            print(f"[sharded x{world}] gangs [{pl.exchange}]: rounds={st['rounds']} iterations={st['gang_iterations']} "
+                  f"placed={st['placed']} == one-call single-GPU: {same}  == oracle: {same_oracle}", flush=True)
+        ok_all = ok_all and same and same_oracle is not False
     flag = torch.tensor([1 if ok_all else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()

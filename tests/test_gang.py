@@ -134,3 +134,29 @@ def test_gpu_gang_chain_path(orc, monkeypatch):
     with capi.Context(0) as ctx:
         got, want = ctx.place_gang(nodes, pods, gang, mins), orc.place_gang(nodes, pods, gang, mins)
         assert np.array_equal(got["assign"], want["assign"]) and np.array_equal(got["gang_ok"], want["gang_ok"])
+
+
+@pytest.mark.gpu
+def test_gpu_gang_stepwise_equals_one_call(orc):
+    """k8sgpu_place_gang_begin / rounds / _verdicts / _end (what one process per GPU runs, here with
+    a world of one and the peer-store scoring entry as well) equals the one-call k8sgpu_place_gang."""
+    import k8sgpu_b200  # noqa: F401
+    from k8sgpu_b200 import capi, placement
+
+    rng = np.random.default_rng(9)
+    with capi.Context(0) as ctx:
+        for n, m, g in ((40, 300, 25), (300, 5000, 200)):
+            nodes, pods, gang, mins = random_case(rng, n, m, g)
+            want = orc.place_gang(nodes, pods, gang, mins, nthreads=8)
+            pl = placement.ShardedPlacer(ctx)
+            pl.upload(nodes, pods)
+            st = pl.run_gang(gang, mins)
+            got = pl.download()
+            for k in ("assign", "free_gpu", "free_mcpu", "free_mib"):
+                assert np.array_equal(got[k], want[k]), k
+            assert np.array_equal(st["gang_ok"], want["gang_ok"])
+            assert (st["rounds"], st["placed"], st["evals"], st["gang_iterations"]) == \
+                (want["rounds"], want["placed"], want["evals"], want["iterations"])
+        with pytest.raises(capi.K8sGpuError):  # verdicts are refused while pods are still active
+            ctx.gang_begin(gang, mins)
+            ctx.gang_verdicts()

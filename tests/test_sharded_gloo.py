@@ -54,6 +54,40 @@ class OracleEngine:
     def end(self):
         return {"rounds": self.rounds, "evals": self.evals, "placed": int((self.assign >= 0).sum())}
 
+    # gang steps, restated from k8sgpu.h "gang placement" (steps 2 and 3)
+    def gang_begin(self, gang_id, min_available, flags, max_rounds):
+        self.gang = np.asarray(gang_id, np.uint32)
+        self.gmin = np.asarray(min_available, np.uint32)
+        self.rejected = np.zeros(len(self.gmin), bool)
+        self.iterations = 1
+        return self.begin(flags, max_rounds)
+
+    def gang_verdicts(self):
+        has = self.gang != 0xFFFFFFFF
+        gid = np.where(has, self.gang, 0).astype(np.int64)
+        count = np.bincount(gid[has & (self.assign >= 0)], minlength=len(self.gmin))
+        newly = ~self.rejected & (count < self.gmin)
+        if not newly.any():
+            return 0
+        self.rejected |= newly
+        hit = has & newly[gid]
+        rel = hit & (self.assign >= 0)
+        for col, req in zip(self.free, ("req_gpu", "req_mcpu", "req_mib")):
+            np.add.at(col, self.assign[rel], self.pods[req][rel])
+        self.assign[hit] = -3
+        retry = (self.assign == -1) & (~has | ~self.rejected[gid])
+        self.assign[retry] = -2
+        self.active = np.nonzero(retry)[0].astype(np.uint32)
+        if len(self.active):
+            self.iterations += 1
+        return len(self.active)
+
+    def gang_end(self):
+        st = self.end()
+        st["gang_ok"] = (~self.rejected).astype(np.int32)
+        st["gang_iterations"] = self.iterations
+        return st
+
     def download(self):
         return {"assign": self.assign, "free_gpu": self.free[0], "free_mcpu": self.free[1], "free_mib": self.free[2]}
 
@@ -74,11 +108,25 @@ def _worker(rank, world, port, case, q):
             nodes, pods = synth.gen_identical(40, 400)
             flags = 1 if case == "ties_rot0" else 0
         pl = placement.ShardedPlacer(dist=dist, rank=rank, world=world, engine=OracleEngine(orc))
-        pl.upload(nodes, pods)
-        st = pl.run(flags=flags)
-        got = pl.download()
-        want = orc.place(nodes, pods, flags=flags)
-        ok = all(np.array_equal(got[k], want[k]) for k in ("assign", "free_gpu", "free_mcpu", "free_mib"))
+        if case == "gang":
+            rng = np.random.default_rng(21)
+            nodes, pods = synth.gen_nodes(60, config_id=5), synth.gen_pods(700, config_id=5)
+            gang = rng.integers(0, 40, 700).astype(np.uint32)
+            gang[rng.random(700) < 0.3] = 0xFFFFFFFF
+            mins = rng.integers(0, 12, 40).astype(np.uint32)
+            pl.upload(nodes, pods)
+            st = pl.run_gang(gang, mins)
+            got = pl.download()
+            want = orc.place_gang(nodes, pods, gang, mins)
+            ok = np.array_equal(st["gang_ok"], want["gang_ok"]) and st["gang_iterations"] == want["iterations"]
+            ok = ok and want["iterations"] > 1  # the case must exercise a retry
+        else:
+            pl.upload(nodes, pods)
+            st = pl.run(flags=flags)
+            got = pl.download()
+            want = orc.place(nodes, pods, flags=flags)
+            ok = True
+        ok = ok and all(np.array_equal(got[k], want[k]) for k in ("assign", "free_gpu", "free_mcpu", "free_mib"))
         ok = ok and st["rounds"] == want["rounds"] and st["evals"] == want["evals"] and st["placed"] == want["placed"]
         q.put((rank, bool(ok)))
     finally:
@@ -93,7 +141,7 @@ def _free_port():
     return p
 
 
-@pytest.mark.parametrize("world,case", [(2, "hetero"), (2, "ties_rot0"), (3, "hetero"), (2, "ties_rot")])
+@pytest.mark.parametrize("world,case", [(2, "hetero"), (2, "ties_rot0"), (3, "hetero"), (2, "ties_rot"), (2, "gang")])
 def test_sharded_placement_is_rank_count_invariant(orc, world, case):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
