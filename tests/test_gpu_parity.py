@@ -134,6 +134,14 @@ def test_place_heterogeneous_sweep(ctx, orc, synth, h100, taint, m):
     same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
 
 
+@pytest.mark.parametrize("n,m", [(200, 140_000), (150, 300_000)])
+def test_place_long_active_list(ctx, orc, synth, n, m):
+    """More proposals than the single-launch admission handles with its per-CTA local scans
+    (> 64 sort tiles; > 1024 segment blocks): the grid-wide scan / carry phases, against the oracle."""
+    nodes, pods = synth.gen_nodes(n, config_id=5), synth.gen_pods(m, config_id=5)
+    same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
+
+
 @pytest.mark.parametrize("name", ["c3_small", "ties_rot_zero", "c5_all_h100"])
 def test_place_single_launch_admission(ctx, name, monkeypatch):
     """K8SGPU_COOP=1: the cooperative one-launch admission path gives the golden result too."""
