@@ -404,6 +404,10 @@ def main():
                     best, best_nt = dt, nt
             line["reconcile"]["cpu_baseline"] = {"value": C2["p"] / best, "unit": "decisions/s", "cores": best_nt,
                                                  "kind": "port", "sample": "whole config 2, best of 1 and all threads"}
+            # BASELINE.json config 1 is CPU only (one pool against the fake ARM client: nothing to batch)
+            line["reconcile"]["config1_cpu"] = {
+                "ns_per_reconcile": orc.config1_ns_per_reconcile(), "cores": 1, "kind": "port",
+                "sample": "replicas 3->5->2 with a settle pass each (K1-K5, 6 Reconciles) x 20000, fake in-memory ARM"}
 
     if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1

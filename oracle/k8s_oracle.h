@@ -178,6 +178,8 @@ typedef struct {
 } orc_result;
 
 orc_result orc_reconcile_one(orc_cluster *, orc_arm *, const char *ns, const char *name);
+/* BASELINE.json config 1 (replicas 3 -> 5 -> 2, K1..K5) `iterations` times; returns Reconcile calls made, -1 on a wrong outcome */
+long orc_config1_loop(int iterations);
 
 #ifdef __cplusplus
 }

@@ -268,6 +268,23 @@ def reconcile_batch(desired, pool_owner_id, vm_owner_id, vm_flags, n_owner_ids, 
     return o
 
 
+def config1_ns_per_reconcile(iterations: int = 20000) -> float:
+    """BASELINE.json config 1 on the CPU state machine: nanoseconds per Reconcile call (K1..K5 loop in C)."""
+    import time
+
+    L = lib()
+    L.orc_config1_loop.argtypes = [C.c_int]
+    L.orc_config1_loop.restype = C.c_long
+    if L.orc_config1_loop(100) != 600:
+        raise RuntimeError("config 1 sequence did not end as K1..K5 say")
+    t0 = time.perf_counter()
+    calls = L.orc_config1_loop(iterations)
+    dt = time.perf_counter() - t0
+    if calls != 6 * iterations:
+        raise RuntimeError("config 1 sequence did not end as K1..K5 say")
+    return 1e9 * dt / calls
+
+
 class FakeArm:
     """Fake Azure resource group (insertion-ordered VM list with tags + failure injection)."""
 

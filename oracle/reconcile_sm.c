@@ -274,3 +274,34 @@ orc_result orc_reconcile_one(orc_cluster *c, orc_arm *a, const char *ns, const c
     r.requeue_after_s = 60; /* README.md:234 */
     return r;
 }
+
+/* BASELINE.json config 1 as a timing loop (bench.py cpu leg): a fresh fake cluster per iteration,
+ * 3 VMs, replicas 3 -> 5 -> 2 with a settle Reconcile after each change (K1..K5: six Reconciles).
+ * Returns the number of Reconcile calls made, or -1 if a step did not end as K1..K5 say. */
+long orc_config1_loop(int iterations) {
+    long calls = 0;
+    for (int it = 0; it < iterations; ++it) {
+        orc_arm *a = orc_arm_new();
+        orc_cluster *c = orc_cluster_new();
+        if (!a || !c) return -1;
+        orc_cluster_put_pool(c, "default", "pool", 3);
+        orc_arm_add_vm(a, "v0", "azurevmpool-operator", "default-pool");
+        orc_arm_add_vm(a, "v1", "azurevmpool-operator", "default-pool");
+        orc_arm_add_vm(a, "v2", "azurevmpool-operator", "default-pool");
+        static const int32_t seq[3] = {3, 5, 2};
+        static const int want_vms[3] = {3, 5, 2};
+        for (int s = 0; s < 3; ++s) {
+            orc_cluster_set_replicas(c, "default", "pool", seq[s]);
+            for (int k = 0; k < 2; ++k) { /* the change, then the settle pass */
+                orc_result r = orc_reconcile_one(c, a, "default", "pool");
+                ++calls;
+                if (r.err != ORC_OK || r.requeue_after_s != 60) return -1;
+            }
+            if (orc_arm_vm_count(a) != want_vms[s] || orc_cluster_ready_replicas(c, "default", "pool") != want_vms[s])
+                return -1;
+        }
+        orc_arm_free(a);
+        orc_cluster_free(c);
+    }
+    return calls;
+}
