@@ -66,6 +66,8 @@ def case_place(rng, ctx):
                K8SGPU_COOP=str(rng.integers(0, 2)))
     if rng.random() < 0.5:
         env["K8SGPU_SPLITS"] = str(rng.integers(1, 9))
+    if rng.random() < 0.5:  # few CTAs in the single-launch admission: every CTA loops over several tiles
+        env["K8SGPU_COOP_GRID"] = str(rng.choice([1, 2, 3, 5, 17, 64]))
     os.environ.update(env)
     try:
         if rng.random() < 0.3:
@@ -82,7 +84,7 @@ def case_place(rng, ctx):
             ok = same(got, want, ("assign", "free_gpu", "free_mcpu", "free_mib"))
         ok = ok and (got["rounds"], got["evals"], got["placed"]) == (want["rounds"], want["evals"], want["placed"])
     finally:
-        for k in ("K8SGPU_RES", "K8SGPU_PPT", "K8SGPU_COOP", "K8SGPU_SPLITS"):
+        for k in ("K8SGPU_RES", "K8SGPU_PPT", "K8SGPU_COOP", "K8SGPU_SPLITS", "K8SGPU_COOP_GRID"):
             os.environ.pop(k, None)
     return ok, f"place n={n} m={m} flags={flags} env={env}"
 
@@ -90,6 +92,8 @@ def case_place(rng, ctx):
 def case_reconcile(rng, ctx):
     P, V = pick_size(rng, 4000), pick_size(rng, 150_000)
     os.environ["K8SGPU_REC_COOP"] = str(rng.integers(0, 2))
+    if rng.random() < 0.5:
+        os.environ["K8SGPU_REC_GRID"] = str(rng.choice([1, 2, 3, 5, 17, 64]))
     try:
         n_ids = P + int(rng.integers(0, 50))
         powner = rng.permutation(n_ids)[:P].astype(np.uint32)
@@ -107,6 +111,7 @@ def case_reconcile(rng, ctx):
         ok = all(np.array_equal(got[k], want[k]) for k in want)
     finally:
         os.environ.pop("K8SGPU_REC_COOP", None)
+        os.environ.pop("K8SGPU_REC_GRID", None)
     return ok, f"reconcile P={P} V={V}"
 
 

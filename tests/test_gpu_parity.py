@@ -142,10 +142,23 @@ def test_place_long_active_list(ctx, orc, synth, n, m):
     same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
 
 
+@pytest.mark.parametrize("grid", ["1", "3", "7"])
+def test_place_few_ctas_many_tiles(ctx, orc, synth, grid, monkeypatch):
+    """30 sort tiles / 240 segment blocks handled by 1, 3 or 7 CTAs: every per-CTA loop of the
+    single-launch admission runs many iterations (shared scratch is reused across them)."""
+    monkeypatch.setenv("K8SGPU_COOP_GRID", grid)
+    nodes, pods = synth.gen_nodes(500, config_id=5), synth.gen_pods(60_000, config_id=5)
+    same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
+
+
+@pytest.mark.parametrize("grid", [None, "1", "3", "40"])
 @pytest.mark.parametrize("name", ["c3_small", "ties_rot_zero", "c5_all_h100"])
-def test_place_single_launch_admission(ctx, name, monkeypatch):
-    """K8SGPU_COOP=1: the cooperative one-launch admission path gives the golden result too."""
+def test_place_single_launch_admission(ctx, name, grid, monkeypatch):
+    """K8SGPU_COOP=1: the cooperative one-launch admission path gives the golden result too --
+    also with so few CTAs that each one loops over several tiles in every phase."""
     monkeypatch.setenv("K8SGPU_COOP", "1")
+    if grid:
+        monkeypatch.setenv("K8SGPU_COOP_GRID", grid)
     nodes, pods, flags = mg.place_inputs(name)
     g = np.load(os.path.join(HERE, "golden", f"place_{name}.npz"))
     got = ctx.place(nodes, pods, flags=flags)
@@ -320,8 +333,11 @@ def same_reconcile(got, want):
         assert np.array_equal(got[k], want[k]), k
 
 
+@pytest.mark.parametrize("grid", [None, "1", "3"])
 @pytest.mark.parametrize("name", list(mg.RECONCILE_CASES))
-def test_reconcile_matches_golden(ctx, synth, name):
+def test_reconcile_matches_golden(ctx, synth, name, grid, monkeypatch):
+    if grid:  # few CTAs in the one-launch pass: every CTA loops over several tiles
+        monkeypatch.setenv("K8SGPU_REC_GRID", grid)
     c = mg.RECONCILE_CASES[name]
     t = synth.gen_reconcile(c["p"], c["v"], c["config_id"])
     got = ctx.reconcile_batch(t["desired"], t["pool_owner_id"], t["vm_owner_id"], t["vm_flags"], t["n_owner_ids"],
