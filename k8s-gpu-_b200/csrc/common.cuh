@@ -78,6 +78,7 @@ struct PlaceState {
     uint32_t policy_flags = 0, max_rounds = 0;
     uint32_t n_gangs = 0, gang_iters = 0;  // gang placement: table size, round loops run so far
     int score_res = 2;  // eval_pair variant the pod records are laid out for
+    uint32_t best_cleared_len = 0;  // best_key[0 .. this) is known to be zero (left so by the admission kernel)
     bool nodeq_stale = true;  // packed node records do not reflect free_cols yet
     DevBuf peer_local;        // exchange buffer other ranks store their proposals into (IPC-exported)
     int32_t *peer_ptr[16] = {};  // every rank's exchange buffer as seen from this GPU (own included)

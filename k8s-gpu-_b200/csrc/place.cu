@@ -503,7 +503,7 @@ __global__ void admit_keys_kernel(const int32_t *__restrict__ best, const uint32
     }
     if (b < 0) assign[active[i]] = K8SGPU_ASSIGN_NONE;  // no feasible node: final
     keys[i] = b < 0 ? n_nodes : (uint32_t)b;           // non-proposers sort behind every node
-    vals[i] = i;
+    vals[i] = active[i];  // payload = pod id: the stable sort keeps pod order inside each node
 }
 
 struct Seg {  // running (saturating) demand of one node's proposers, in pod order
@@ -586,7 +586,7 @@ __device__ __forceinline__ Seg load_seg(const uint32_t *__restrict__ keys, const
     *key_out = 0xFFFFFFFFu;
     if (i < na) {
         uint32_t k = keys[i];
-        const PodQ *q = podq + active[vals[i]];
+        const PodQ *q = podq + vals[i];
         x.g = q->req_gpu;
         x.c = q->req_mcpu;
         x.m = q->req_mib;
@@ -640,7 +640,7 @@ __global__ void __launch_bounds__(kSegThreads) admit_apply_kernel(
     uint32_t ok = 0;
     if (key < n_nodes) {
         ok = (s.g <= freec[key]) & (s.c <= freec[(size_t)n_nodes + key]) & (s.m <= freec[2 * (size_t)n_nodes + key]);
-        if (ok) assign[active[vals[i]]] = (int32_t)key;
+        if (ok) assign[vals[i]] = (int32_t)key;
     }
     admitted[i] = ok;
 }
@@ -654,7 +654,7 @@ __global__ void admit_free_update_kernel(const uint32_t *__restrict__ keys, cons
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= na || !admitted[i]) return;
     uint32_t key = keys[i];
-    const PodQ *q = podq + active[vals[i]];
+    const PodQ *q = podq + vals[i];
     if (q->req_gpu) atomicSub(&freec[key], q->req_gpu);
     if (q->req_mcpu) atomicSub(&freec[(size_t)n_nodes + key], q->req_mcpu);
     if (q->req_mib) atomicSub(&freec[2 * (size_t)n_nodes + key], q->req_mib);
@@ -688,6 +688,7 @@ __global__ void count_placed_kernel(const int32_t *__restrict__ assign, uint32_t
 
 struct AdmitArgs {
     const unsigned long long *best_key;  // by active position (score_kernel output)
+    unsigned long long *best_key_clear;  // the same array: cleared at the end for the next round's atomicMax
     const int32_t *proposals;            // or: node row per active position (exchanged between GPUs); else null
     const PodQ *podq;
     const uint32_t *active;
@@ -759,7 +760,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
                     a.assign[pod[r]] = K8SGPU_ASSIGN_NONE;
                 }
                 a.keys[i] = key;
-                a.vals[i] = i;
+                a.vals[i] = pod[r];  // payload = pod id
             }
         }
         __syncthreads();
@@ -818,7 +819,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
             uint32_t ok = 0;
             if (key < N) {
                 ok = (s.g <= a.freec[key]) & (s.c <= a.freec[(size_t)N + key]) & (s.m <= a.freec[2 * (size_t)N + key]);
-                if (ok) a.assign[a.active[sv[i]]] = (int32_t)key;
+                if (ok) a.assign[sv[i]] = (int32_t)key;
             }
             a.offs[i] = ok;
         }
@@ -838,7 +839,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
         if (i < na) {
             if (a.offs[i]) {
                 uint32_t key = sk[i];
-                const PodQ *q = a.podq + a.active[sv[i]];
+                const PodQ *q = a.podq + sv[i];
                 if (q->req_gpu) atomicSub(&a.freec[key], q->req_gpu);
                 if (q->req_mcpu) atomicSub(&a.freec[(size_t)N + key], q->req_mcpu);
                 if (q->req_mib) atomicSub(&a.freec[2 * (size_t)N + key], q->req_mib);
@@ -921,9 +922,11 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
         for (uint32_t i = cta * 256 + tid; i < na; i += G * 256)
             if (a.flags[i]) a.next_active[a.offs[i]] = a.active[i];
     }
-    // the next round's packed node records
+    // the next round's packed node records, and its (shorter) key array cleared: one stream
+    // operation fewer between this kernel and the next scoring launch
     for (uint32_t i = cta * 256 + tid; i < a.n_pad; i += G * 256)
         a.nodeq[i] = make_nodeq(a.node_cols, a.freec, N, i, nullptr, 0);
+    for (uint32_t i = cta * 256 + tid; i < na; i += G * 256) a.best_key_clear[i] = 0ull;
     prof_mark(a, 8);
 }
 
@@ -1002,6 +1005,7 @@ static int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_
     st.timed = 0;
     st.timed_evals = 0;
     st.nodeq_stale = true;
+    st.best_cleared_len = 0;
     st.score_res = kDefaultRes;  // which eval_pair variant (see its comment); all are bit-identical
     if (const char *e = getenv("K8SGPU_RES")) st.score_res = atoi(e);
     K8S_CUDA(ctx, cudaMemsetAsync(st.counters.p, 0, 64 * 4, s));
@@ -1057,7 +1061,9 @@ static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_bes
     }
     const int use_atomic = splits > 1;
     unsigned long long *bk = st.best_key.as<unsigned long long>();
-    if (use_atomic) K8S_CUDA(ctx, cudaMemsetAsync(bk + lo, 0, (size_t)cnt * 8, s));
+    if (use_atomic && !(st.best_cleared_len >= hi))  // (the single-launch admission leaves it cleared)
+        K8S_CUDA(ctx, cudaMemsetAsync(bk + lo, 0, (size_t)cnt * 8, s));
+    st.best_cleared_len = 0;
     const bool timed = st.timed < kMaxTimedRounds;  // (the two event records cost ~4 us per round)
     if (timed) K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed], s));
     dim3 grid(xb, splits);
@@ -1154,6 +1160,7 @@ static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *prop
     const uint32_t nb = ceil_div(na, kSortTile);
     AdmitArgs a;
     a.best_key = st.best_key.as<unsigned long long>();
+    a.best_key_clear = st.best_key.as<unsigned long long>();
     a.proposals = proposals;
     a.podq = st.podq.as<PodQ>();
     a.active = st.active[st.cur].as<uint32_t>();
@@ -1231,6 +1238,7 @@ static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *prop
     st.cur ^= 1;
     st.n_active = ctx->h_pinned[1];
     st.nodeq_stale = false;  // the kernel rebuilt the packed node records from the new free columns
+    st.best_cleared_len = na;  // ... and cleared best_key[0 .. na)
     return K8SGPU_OK;
 }
 
