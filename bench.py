@@ -247,14 +247,29 @@ def main():
     # end to end through the drop-in call: pinned host tables -> H2D -> rounds -> D2H of results
     e2e = None
     if world == 1:
-        pin = lambda d: {k: torch.from_numpy(v).pin_memory().numpy() for k, v in d.items()}
-        hn, hp = pin(nodes), pin(pods)
-        ctx.place(hn, hp)
+        def slab(cols, order, dtype=np.uint32):
+            """One pinned block with the columns back to back (the layout the device keeps): the library
+            then moves a table with one copy instead of eight."""
+            n = len(cols[order[0]])
+            blk = torch.empty(len(order) * max(n, 1), dtype=torch.int32).pin_memory().numpy().view(dtype)
+            out = {}
+            for c, k in enumerate(order):
+                out[k] = blk[c * n:(c + 1) * n]
+                out[k][:] = cols[k]
+            return out
+
+        hn = slab(nodes, ("free_gpu", "free_mcpu", "free_mib", "cap_gpu", "sku_id", "zone_id", "taint_mask", "flags"))
+        hp = slab(pods, ("req_gpu", "req_mcpu", "req_mib", "sku_mask", "zone_mask", "tol_mask", "pref_zone", "priority"))
+        n_, m_ = len(nodes["flags"]), len(pods["req_gpu"])
+        ho = slab({k: np.zeros(n_, np.uint32) for k in ("free_gpu", "free_mcpu", "free_mib")},
+                  ("free_gpu", "free_mcpu", "free_mib"))
+        ho["assign"] = torch.empty(max(m_, 1), dtype=torch.int32).pin_memory().numpy()[:m_]
+        ctx.place(hn, hp, out=ho)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         e_evals = 0
         for _ in range(args.steps):
-            r = ctx.place(hn, hp)
+            r = ctx.place(hn, hp, out=ho)
             e_evals += r["evals"]
         e_dt = time.perf_counter() - t0
         e2e = {"value": e_evals / e_dt, "unit": "evals/s", "h2d_bytes_per_step": int(r["h2d_bytes"]),

@@ -202,11 +202,12 @@ class Context:
         return s.as_dict()
 
     # ------------------------------------------------------------ placement
-    def place(self, nodes: dict, pods: dict, flags: int = 0, max_rounds: int = 0) -> dict:
-        """Host tables in, host results out (the drop-in call)."""
+    def place(self, nodes: dict, pods: dict, flags: int = 0, max_rounds: int = 0, out: dict = None) -> dict:
+        """Host tables in, host results out (the drop-in call).  `out` may hold caller-owned result
+        arrays (assign i32[m], free_gpu / free_mcpu / free_mib u32[n]), e.g. pinned ones."""
         nt, k1 = node_table(nodes)
         pt, k2 = pod_table(pods)
-        out, res = self._place_out(nt.n, pt.m)
+        out, res = self._place_out(nt.n, pt.m, out)
         pol = Policy(flags, max_rounds)
         self._check(self._L.k8sgpu_place(self._h, C.byref(nt), C.byref(pt), C.byref(pol), C.byref(out)))
         res.update(self.stats())
@@ -228,9 +229,17 @@ class Context:
         res.update(self.stats())
         return res
 
-    def _place_out(self, n, m):
-        res = {"assign": np.empty(m, np.int32), "free_gpu": np.empty(n, np.uint32),
-               "free_mcpu": np.empty(n, np.uint32), "free_mib": np.empty(n, np.uint32)}
+    def _place_out(self, n, m, given=None):
+        if given is not None:
+            res = {k: given[k] for k in ("assign", "free_gpu", "free_mcpu", "free_mib")}
+            ok = res["assign"].dtype == np.int32 and len(res["assign"]) == m and res["assign"].flags.c_contiguous
+            ok = ok and all(res[k].dtype == np.uint32 and len(res[k]) == n and res[k].flags.c_contiguous
+                            for k in ("free_gpu", "free_mcpu", "free_mib"))
+            if not ok:
+                raise ValueError("out: need contiguous assign int32[m] and free_* uint32[n]")
+        else:
+            res = {"assign": np.empty(m, np.int32), "free_gpu": np.empty(n, np.uint32),
+                   "free_mcpu": np.empty(n, np.uint32), "free_mib": np.empty(n, np.uint32)}
         out = PlaceOut(res["assign"].ctypes.data_as(i32p), res["free_gpu"].ctypes.data_as(u32p),
                        res["free_mcpu"].ctypes.data_as(u32p), res["free_mib"].ctypes.data_as(u32p))
         return out, res

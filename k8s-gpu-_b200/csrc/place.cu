@@ -963,9 +963,20 @@ static int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k
                              nodes->sku_id,   nodes->zone_id,   nodes->taint_mask, nodes->flags};
     const uint32_t *pc[8] = {pods->req_gpu,  pods->req_mcpu, pods->req_mib,   pods->sku_mask,
                              pods->zone_mask, pods->tol_mask, pods->pref_zone, pods->priority};
+    // A caller that keeps the eight columns of a table back to back in one block (the layout
+    // the device uses) gets one copy per table instead of eight: fewer, larger transfers.
+    bool nslab = n > 0, pslab = m > 0;
+    for (int c = 0; c + 1 < 8; ++c) {
+        nslab = nslab && nc[c + 1] == nc[c] + n;
+        pslab = pslab && pc[c + 1] == pc[c] + m;
+    }
+    if (nslab) K8S_CUDA(ctx, cudaMemcpyAsync(st.node_cols.p, nc[0], 8 * n * 4, cudaMemcpyHostToDevice, s));
+    if (pslab) K8S_CUDA(ctx, cudaMemcpyAsync(st.pod_cols.p, pc[0], 8 * m * 4, cudaMemcpyHostToDevice, s));
     for (int c = 0; c < 8; ++c) {
-        if (n) K8S_CUDA(ctx, cudaMemcpyAsync(st.node_cols.as<uint32_t>() + c * n, nc[c], n * 4, cudaMemcpyHostToDevice, s));
-        if (m) K8S_CUDA(ctx, cudaMemcpyAsync(st.pod_cols.as<uint32_t>() + c * m, pc[c], m * 4, cudaMemcpyHostToDevice, s));
+        if (n && !nslab)
+            K8S_CUDA(ctx, cudaMemcpyAsync(st.node_cols.as<uint32_t>() + c * n, nc[c], n * 4, cudaMemcpyHostToDevice, s));
+        if (m && !pslab)
+            K8S_CUDA(ctx, cudaMemcpyAsync(st.pod_cols.as<uint32_t>() + c * m, pc[c], m * 4, cudaMemcpyHostToDevice, s));
     }
     ctx->stats.h2d_bytes += 8 * (n + m) * 4;
     // run-state buffers
@@ -1489,6 +1500,11 @@ static int place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out) {
         ctx->stats.d2h_bytes += (uint64_t)st.m * 4;
     }
     uint32_t *dst[3] = {out->free_gpu, out->free_mcpu, out->free_mib};
+    if (st.n && dst[0] && dst[1] == dst[0] + st.n && dst[2] == dst[1] + st.n) {  // one block: one copy
+        K8S_CUDA(ctx, cudaMemcpyAsync(dst[0], st.free_cols.p, 3 * (size_t)st.n * 4, cudaMemcpyDeviceToHost, s));
+        ctx->stats.d2h_bytes += 3 * (uint64_t)st.n * 4;
+        dst[0] = dst[1] = dst[2] = nullptr;
+    }
     for (int c = 0; c < 3; ++c)
         if (dst[c] && st.n) {
             K8S_CUDA(ctx, cudaMemcpyAsync(dst[c], st.free_cols.as<uint32_t>() + (size_t)c * st.n, (size_t)st.n * 4,

@@ -125,6 +125,33 @@ def test_place_matches_golden_and_oracle(ctx, orc, name):
     same_placement(got, orc.place(nodes, pods, flags=flags, nthreads=NCPU))
 
 
+def test_place_tables_in_one_block_and_caller_outputs(ctx, synth):
+    """Columns kept back to back in one block travel as one copy per table; results land in the
+    caller's arrays (also one block for the three free columns).  Same answer as separate columns."""
+    nodes, pods = synth.gen_nodes(777, config_id=5), synth.gen_pods(4321, config_id=5)
+    want = ctx.place(nodes, pods)
+
+    def block(cols, order):
+        n = len(cols[order[0]])
+        blk = np.empty(len(order) * n, np.uint32)
+        out = {}
+        for c, k in enumerate(order):
+            out[k] = blk[c * n:(c + 1) * n]
+            out[k][:] = cols[k]
+        return out
+
+    bn = block(nodes, ("free_gpu", "free_mcpu", "free_mib", "cap_gpu", "sku_id", "zone_id", "taint_mask", "flags"))
+    bp = block(pods, ("req_gpu", "req_mcpu", "req_mib", "sku_mask", "zone_mask", "tol_mask", "pref_zone", "priority"))
+    out = block({k: np.zeros(777, np.uint32) for k in ("free_gpu", "free_mcpu", "free_mib")},
+                ("free_gpu", "free_mcpu", "free_mib"))
+    out["assign"] = np.full(4321, 99, np.int32)
+    got = ctx.place(bn, bp, out=out)
+    for k in ("assign", "free_gpu", "free_mcpu", "free_mib"):
+        assert got[k] is out[k] and np.array_equal(got[k], want[k]), k
+    with pytest.raises(ValueError):
+        ctx.place(bn, bp, out={**out, "assign": np.zeros(5, np.int32)})
+
+
 @pytest.mark.parametrize("h100,taint,m", [(0, 0, 10), (50, 5, 100), (100, 50, 1000), (30, 5, 10_000),
                                           (50, 0, 40_000)])
 def test_place_heterogeneous_sweep(ctx, orc, synth, h100, taint, m):
