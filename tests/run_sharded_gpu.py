@@ -40,6 +40,7 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     cases = [("small-hetero", synth.gen_nodes(3000, 5), synth.gen_pods(20_000, 5), 0, True),
              ("ties-rot0", *synth.gen_identical(500, 4100), 1, True),
+             ("ties-rotated", *synth.gen_identical(500, 4100), 0, True),  # K12: G-invariant with rotation on
              ("c4-slice", synth.gen_nodes(100_000, 4), synth.gen_pods(60_000, 4), 0, False)]
     ok_all = True
     with capi.Context(local) as ctx:
