@@ -811,15 +811,20 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
     prof_mark(a, 4);
     for (uint32_t vb = cta; vb < nb2; vb += G) {  // S <= free (a13); admitted flags go to offs[] for now
         const uint32_t i = vb * kSegThreads + tid;
-        const Seg carry = local_carry ? seg_carry_local(a.seg, vb) : a.seg[vb];
+        // this thread's loads first, so that they are in flight while the carry is folded
         uint32_t key;
         Seg x = load_seg(sk, sv, a.active, a.podq, i, na, &key);
+        const bool real = i < na && key < N;
+        const uint32_t pod = i < na ? sv[i] : 0u;
+        const uint32_t fg = real ? a.freec[key] : 0u, fc = real ? a.freec[(size_t)N + key] : 0u,
+                       fm = real ? a.freec[2 * (size_t)N + key] : 0u;
+        const Seg carry = local_carry ? seg_carry_local(a.seg, vb) : a.seg[vb];
         Seg s = seg_combine(carry, seg_block_scan(x, nullptr));
         if (i < na) {
             uint32_t ok = 0;
-            if (key < N) {
-                ok = (s.g <= a.freec[key]) & (s.c <= a.freec[(size_t)N + key]) & (s.m <= a.freec[2 * (size_t)N + key]);
-                if (ok) a.assign[sv[i]] = (int32_t)key;
+            if (real) {
+                ok = (s.g <= fg) & (s.c <= fc) & (s.m <= fm);
+                if (ok) a.assign[pod] = (int32_t)key;
             }
             a.offs[i] = ok;
         }
@@ -837,14 +842,17 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
         const uint32_t i = c * 256 + tid;
         uint32_t f = 0;
         if (i < na) {
-            if (a.offs[i]) {
-                uint32_t key = sk[i];
-                const PodQ *q = a.podq + sv[i];
-                if (q->req_gpu) atomicSub(&a.freec[key], q->req_gpu);
-                if (q->req_mcpu) atomicSub(&a.freec[(size_t)N + key], q->req_mcpu);
-                if (q->req_mib) atomicSub(&a.freec[2 * (size_t)N + key], q->req_mib);
+            // independent loads first (the two chains then overlap instead of running back to back)
+            const uint32_t admitted = a.offs[i], key = sk[i], pod_sorted = sv[i], pod_here = a.active[i];
+            const int32_t state = a.assign[pod_here];
+            if (admitted) {
+                const PodQ *q = a.podq + pod_sorted;
+                const uint32_t rg = q->req_gpu, rc = q->req_mcpu, rm = q->req_mib;
+                if (rg) atomicSub(&a.freec[key], rg);
+                if (rc) atomicSub(&a.freec[(size_t)N + key], rc);
+                if (rm) atomicSub(&a.freec[2 * (size_t)N + key], rm);
             }
-            f = a.assign[a.active[i]] == K8SGPU_ASSIGN_PENDING ? 1u : 0u;
+            f = state == K8SGPU_ASSIGN_PENDING ? 1u : 0u;
             a.flags[i] = f;
         }
         const uint32_t cnt = (uint32_t)__syncthreads_count((int)f);
