@@ -14,19 +14,20 @@
  */
 #ifndef K8SGPU_H
 #define K8SGPU_H
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-#define K8SGPU_ABI_VERSION 1
+#define K8SGPU_ABI_VERSION 2
 
 /* error codes: every export returns 0 or one of these; text via k8sgpu_last_error */
 #define K8SGPU_OK 0
 #define K8SGPU_E_ARG (-1)      /* NULL pointer, table outside the input domain, duplicate owner id */
 #define K8SGPU_E_CUDA (-2)     /* CUDA runtime error or no device */
-#define K8SGPU_E_NCCL (-3)     /* reserved: collective layer */
+#define K8SGPU_E_NCCL (-3)     /* NCCL missing, or a communicator / collective call failed */
 #define K8SGPU_E_CAPACITY (-4) /* a caller-sized output buffer is too small */
 
 #define K8SGPU_NONE_U32 0xFFFFFFFFu
@@ -78,6 +79,17 @@ typedef struct {
     uint64_t create_capacity; /* elements available in create_ordinal                          */
 } k8sgpu_reconcile_out;
 
+/* Where each output array starts (in 4-byte elements) inside ONE caller block of `total` elements
+ * that holds them all, capacities as listed above.  A caller that allocates its outputs this way
+ * (k8sgpu_reconcile_out_size) gets them back in as few device->host copies as possible: the library
+ * keeps the same layout in HBM and merges adjacent transfers -- the tag-filter result and everything
+ * sized by P travel as one copy.  The three lists (victim_vm, member_vm, create_ordinal) come last
+ * because only their used prefixes are copied.  Any other placement of the buffers works too. */
+typedef struct {
+    uint64_t pool_of, current, ready, delta, create_count, victim_off, member_off, create_off;
+    uint64_t victim_vm, member_vm, create_ordinal, total;
+} k8sgpu_reconcile_layout;
+
 /* Node and pod records: 8 u32 columns each (DESIGN.md "tables").  The reference holds no
  * scheduler source; the pod shape comes from GPU调度平台搭建.md:665-667 (nvidia.com/gpu: 1)
  * and :534 (gpu-1x-16c-32g-1gpu), the node attributes from README.md:99-100 (location, vmSize).
@@ -89,6 +101,9 @@ typedef struct {
     const uint32_t *free_gpu, *free_mcpu, *free_mib, *cap_gpu, *sku_id, *zone_id, *taint_mask, *flags;
 } k8sgpu_node_table;
 
+/* priority is RESERVED: policy v0 admits in plain pod-index order and never reads it.  It may be
+ * NULL; a caller that sets priorities must order its pod table accordingly (row order IS the
+ * admission order). */
 typedef struct {
     uint32_t m;
     const uint32_t *req_gpu, *req_mcpu, *req_mib, *sku_mask, *zone_mask, *tol_mask, *pref_zone, *priority;
@@ -122,15 +137,47 @@ typedef struct {
 
 /* ------------------------------------------------------------------ context */
 
-/* Opens devices[0] (ndev must be 1: one process per GPU; several processes cooperate through
- * the k8sgpu_place_round_* entry points below).  Replaces nothing in the reference; it is
- * what SetupWithManager would call once. */
+/* Opens the listed CUDA devices (1 <= ndev <= 16, all distinct, all sm_100) as ONE context.
+ * Replaces nothing in the reference; it is what SetupWithManager would call once.
+ *   ndev == 1: one GPU.  Several such contexts, one per process, can still share a placement
+ *              (k8sgpu_comm_init_rank below).
+ *   ndev  > 1: a placement group inside this process -- what a single controller process with
+ *              eight B200s uses.  The library owns one NCCL communicator per device (NCCL is
+ *              loaded at this point; K8SGPU_E_NCCL if it cannot be) and enables peer access.
+ *              k8sgpu_place / _place_gang / _place_upload / _place_run then shard the pods of
+ *              every round across the devices (tables replicated, proposals exchanged by
+ *              ncclAllGather) and return byte-identical results to ndev == 1.  Batch reconcile
+ *              and the other entry points run on devices[0] ("replicas only").
+ * k8sgpu_create_ex is the same with the failure text copied into a caller buffer (errbuf may be
+ * NULL), for callers that create contexts from several threads at once. */
 int k8sgpu_create(const int *devices, int ndev, k8sgpu_ctx **out);
+int k8sgpu_create_ex(const int *devices, int ndev, k8sgpu_ctx **out, char *errbuf, size_t errcap);
 int k8sgpu_destroy(k8sgpu_ctx *ctx);
-/* Message of the last failing call on ctx (ctx may be NULL: creation errors). */
+/* Message of the last failing call on ctx.  ctx == NULL: the most recent k8sgpu_create failure
+ * of this process (one process-wide buffer; use k8sgpu_create_ex when creations can overlap). */
 const char *k8sgpu_last_error(const k8sgpu_ctx *ctx);
 int k8sgpu_get_stats(const k8sgpu_ctx *ctx, k8sgpu_stats *out);
 int k8sgpu_abi_version(void);
+
+/* One process per GPU (torchrun, MPI): every process creates a one-device context, rank 0 makes
+ * an id with k8sgpu_comm_unique_id (an ncclUniqueId, K8SGPU_UNIQUE_ID_BYTES bytes), hands it to the
+ * others by whatever channel the job has, and all call k8sgpu_comm_init_rank -- a collective call:
+ * it returns once all `world` ranks have joined.  From then on k8sgpu_place and friends on these
+ * contexts are collective too: every rank passes the same tables and gets the same result.
+ * K8SGPU_E_NCCL when NCCL cannot be loaded or reports an error.  No reference counterpart. */
+#define K8SGPU_UNIQUE_ID_BYTES 128
+int k8sgpu_comm_unique_id(void *id128);
+int k8sgpu_comm_init_rank(k8sgpu_ctx *ctx, int rank, int world, const void *id128);
+/* world / rank / devices driven by this process / NCCL version in use (0 while NCCL is not loaded);
+ * any pointer may be NULL. */
+int k8sgpu_group_info(const k8sgpu_ctx *ctx, int *world, int *rank, int *nlocal, int *nccl_version);
+
+/* Developer and test knobs by name ("res", "ppt", "splits", "coop", "coop_grid", "rec_path",
+ * "rec_grid", "rec_segments", "coop_prof", "rec_prof", "exchange", "shard_admit"; -1 = automatic).
+ * Every setting gives bit-identical results: they select kernel variants and launch shapes.  The
+ * K8SGPU_<NAME> environment variables seed them once, inside k8sgpu_create; nothing reads the
+ * environment afterwards.  No reference counterpart. */
+int k8sgpu_set_tuning(k8sgpu_ctx *ctx, const char *key, int value);
 
 /* ------------------------------------------------------------------ batch reconcile */
 
@@ -140,6 +187,11 @@ int k8sgpu_abi_version(void);
  * owner ids (ids >= n_owner_ids are foreign).  Host buffers in, host buffers out. */
 int k8sgpu_reconcile_batch(k8sgpu_ctx *ctx, const k8sgpu_pool_table *pools, const k8sgpu_vm_table *vms,
                            uint32_t n_owner_ids, k8sgpu_reconcile_out *out);
+
+/* Capacities and the single-block layout of k8sgpu_reconcile_out for p pools, v VM rows and
+ * room for create_capacity new-VM ordinals (the sum of the scale-up counts; the sum of all desired
+ * replicas is always enough).  See k8sgpu_reconcile_layout.  Needs no context and no GPU. */
+int k8sgpu_reconcile_out_size(uint32_t p, uint32_t v, uint64_t create_capacity, k8sgpu_reconcile_layout *out);
 
 /* The same split in three: tables stay resident in HBM between calls (bench `value`). */
 int k8sgpu_reconcile_upload(k8sgpu_ctx *ctx, const k8sgpu_pool_table *pools, const k8sgpu_vm_table *vms,

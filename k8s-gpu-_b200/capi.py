@@ -27,7 +27,12 @@ EXPORTS = (
     "k8sgpu_debug_sort_pairs", "k8sgpu_debug_exclusive_scan", "k8sgpu_exclusive_scan_noalloc",
     "k8sgpu_place_gang", "k8sgpu_peer_export", "k8sgpu_peer_import", "k8sgpu_place_round_score_p2p",
     "k8sgpu_place_gang_begin", "k8sgpu_place_gang_verdicts", "k8sgpu_place_gang_end",
+    "k8sgpu_create_ex", "k8sgpu_set_tuning", "k8sgpu_reconcile_out_size", "k8sgpu_comm_unique_id",
+    "k8sgpu_comm_init_rank", "k8sgpu_group_info",
 )
+UNIQUE_ID_BYTES = 128
+TUNING_KEYS = ("res", "ppt", "splits", "coop", "coop_grid", "rec_path", "rec_grid", "rec_segments", "coop_prof",
+               "rec_prof", "shard_admit", "exchange")
 ASSIGN_GANG = -3
 SCAN_NOALLOC_MAX_N = 1 << 24
 
@@ -47,6 +52,12 @@ class ReconcileOut(C.Structure):
     _fields_ = [("pool_of", i32p), ("current", i32p), ("delta", i32p), ("ready", i32p), ("create_count", i32p),
                 ("victim_off", i32p), ("victim_vm", u32p), ("member_off", i32p), ("member_vm", u32p),
                 ("create_off", i32p), ("create_ordinal", u32p), ("create_capacity", C.c_uint64)]
+
+
+class ReconcileLayout(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("pool_of", "current", "ready", "delta", "create_count", "victim_off",
+                                          "member_off", "create_off", "victim_vm", "member_vm", "create_ordinal",
+                                          "total")]
 
 
 class NodeTable(C.Structure):
@@ -130,6 +141,13 @@ def load() -> C.CDLL:
         L.k8sgpu_debug_sort_pairs.argtypes = [vp, u32p, u32p, C.c_uint32, C.c_int, u32p, u32p]
         L.k8sgpu_debug_exclusive_scan.argtypes = [vp, u32p, C.c_uint32, u32p, u32p]
         L.k8sgpu_exclusive_scan_noalloc.argtypes = [vp, vp, C.c_uint32, vp, vp, vp]
+        L.k8sgpu_create_ex.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp), C.c_char_p, C.c_size_t]
+        L.k8sgpu_set_tuning.argtypes = [vp, C.c_char_p, C.c_int]
+        L.k8sgpu_reconcile_out_size.argtypes = [C.c_uint32, C.c_uint32, C.c_uint64, C.POINTER(ReconcileLayout)]
+        L.k8sgpu_comm_unique_id.argtypes = [vp]
+        L.k8sgpu_comm_init_rank.argtypes = [vp, C.c_int, C.c_int, vp]
+        L.k8sgpu_group_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                        C.POINTER(C.c_int)]
         for name in EXPORTS:
             if name != "k8sgpu_last_error":
                 getattr(L, name).restype = C.c_int
@@ -161,23 +179,65 @@ def pod_table(pods: dict):
     t, keep = PodTable(), []
     t.m = len(pods[POD_COLS[0]])
     for c in POD_COLS:
+        if c == "priority" and pods.get(c) is None:  # reserved column: may be left out
+            continue
         a, p = _u32(pods[c])
         keep.append(a)
         setattr(t, c, p)
     return t, keep
 
 
-class Context:
-    """One k8sgpu_ctx on one GPU.  Not re-entrant: one call at a time."""
+def unique_id() -> bytes:
+    """A fresh ncclUniqueId (rank 0 makes it and hands it to the other ranks)."""
+    buf = (C.c_ubyte * UNIQUE_ID_BYTES)()
+    rc = load().k8sgpu_comm_unique_id(C.cast(buf, C.c_void_p))
+    if rc != OK:
+        raise K8sGpuError(rc, "k8sgpu_comm_unique_id failed (is NCCL loadable?)")
+    return bytes(buf)
 
-    def __init__(self, device: int = 0):
+
+def reconcile_out_size(p: int, v: int, create_capacity: int) -> dict:
+    """Element offsets of every output array inside one block (k8sgpu_reconcile_out_size)."""
+    lay = ReconcileLayout()
+    rc = load().k8sgpu_reconcile_out_size(p, v, create_capacity, C.byref(lay))
+    if rc != OK:
+        raise K8sGpuError(rc, "k8sgpu_reconcile_out_size")
+    return {k: int(getattr(lay, k)) for k, _ in ReconcileLayout._fields_}
+
+
+class Context:
+    """One k8sgpu_ctx: one GPU (device: int) or a placement group of several GPUs of this
+    process (device: a list of ints).  Not re-entrant: one call at a time."""
+
+    def __init__(self, device=0):
         self._L = load()
         self._h = C.c_void_p()
-        dev = (C.c_int * 1)(device)
-        rc = self._L.k8sgpu_create(dev, 1, C.byref(self._h))
+        devs = [int(device)] if isinstance(device, (int, np.integer)) else [int(d) for d in device]
+        dev = (C.c_int * len(devs))(*devs)
+        err = C.create_string_buffer(512)
+        rc = self._L.k8sgpu_create_ex(dev, len(devs), C.byref(self._h), err, len(err))
         if rc != OK:
-            raise K8sGpuError(rc, self._L.k8sgpu_last_error(None).decode())
-        self.device = device
+            raise K8sGpuError(rc, err.value.decode())
+        self.device = devs[0]
+        self.devices = devs
+
+    def set_tuning(self, **knobs):
+        """Developer / test knobs (k8sgpu_set_tuning); None or -1 = automatic."""
+        for k, v in knobs.items():
+            self._check(self._L.k8sgpu_set_tuning(self._h, k.encode(), -1 if v is None else int(v)))
+
+    def reset_tuning(self):
+        self.set_tuning(**{k: (0 if k.endswith("_prof") else -1) for k in TUNING_KEYS})
+
+    def comm_init_rank(self, rank: int, world: int, uid: bytes):
+        """Join `world` one-GPU contexts (one per process) into a placement group; collective."""
+        buf = (C.c_ubyte * UNIQUE_ID_BYTES).from_buffer_copy(uid)
+        self._check(self._L.k8sgpu_comm_init_rank(self._h, rank, world, C.cast(buf, C.c_void_p)))
+
+    def group_info(self) -> dict:
+        w, r, nl, v = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        self._check(self._L.k8sgpu_group_info(self._h, C.byref(w), C.byref(r), C.byref(nl), C.byref(v)))
+        return {"world": w.value, "rank": r.value, "nlocal": nl.value, "nccl_version": v.value}
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:

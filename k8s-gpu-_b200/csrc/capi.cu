@@ -1,4 +1,6 @@
 // capi.cu -- context lifetime, errors, statistics and the primitive test hooks of libk8sgpu.so.
+#include <cstdlib>
+#include <mutex>
 #include <new>
 
 #include "common.cuh"
@@ -9,42 +11,77 @@ static char g_create_err[512] = "";
 
 extern "C" int k8sgpu_abi_version(void) { return K8SGPU_ABI_VERSION; }
 
+// Developer / test knobs, by name.  The K8SGPU_<NAME> environment variables seed them once, when
+// the context is created; after that only k8sgpu_set_tuning changes them.
+static int *tuning_slot(Tuning &t, const char *key) {
+    struct {
+        const char *name;
+        int *slot;
+    } table[] = {{"res", &t.res}, {"ppt", &t.ppt}, {"splits", &t.splits}, {"coop", &t.coop},
+                 {"coop_grid", &t.coop_grid}, {"rec_path", &t.rec_path}, {"rec_grid", &t.rec_grid},
+                 {"rec_segments", &t.rec_segments}, {"coop_prof", &t.coop_prof}, {"rec_prof", &t.rec_prof},
+                 {"shard_admit", &t.shard_admit}, {"exchange", &t.exchange}};
+    for (auto &e : table)
+        if (strcmp(e.name, key) == 0) return e.slot;
+    return nullptr;
+}
+
+static void tuning_from_env(Tuning &t) {
+    static const char *names[] = {"res", "ppt", "splits", "coop", "coop_grid", "rec_path", "rec_grid",
+                                  "rec_segments", "coop_prof", "rec_prof", "shard_admit", "exchange"};
+    for (const char *n : names) {
+        char env[64] = "K8SGPU_";
+        size_t k = strlen(env);
+        for (const char *c = n; *c && k + 1 < sizeof env; ++c) env[k++] = (char)(*c >= 'a' && *c <= 'z' ? *c - 32 : *c);
+        env[k] = 0;
+        if (const char *v = getenv(env)) *tuning_slot(t, n) = atoi(v);
+    }
+}
+
+extern "C" int k8sgpu_set_tuning(k8sgpu_ctx *ctx, const char *key, int value) {
+    if (!ctx || !key) return K8SGPU_E_ARG;
+    int *slot = tuning_slot(ctx->tune, key);
+    if (!slot) return fail(ctx, K8SGPU_E_ARG, "set_tuning: unknown knob '%s'", key);
+    *slot = value;
+    for (int i = 1; i < ctx->nlocal; ++i) *tuning_slot(ctx->local[i]->tune, key) = value;
+    return K8SGPU_OK;
+}
+
+// With ctx == NULL: the message of the most recent failed k8sgpu_create in this process (a
+// process-wide buffer, written under a lock; concurrent creators should use k8sgpu_create_ex).
 extern "C" const char *k8sgpu_last_error(const k8sgpu_ctx *ctx) { return ctx ? ctx->err : g_create_err; }
 
-extern "C" int k8sgpu_create(const int *devices, int ndev, k8sgpu_ctx **out) {
-    if (!out) return K8SGPU_E_ARG;
-    *out = nullptr;
-    if (ndev != 1 || !devices) {
-        snprintf(g_create_err, sizeof g_create_err,
-                 "k8sgpu_create: ndev must be 1 (one process per GPU; see k8sgpu_place_round_*)");
-        return K8SGPU_E_ARG;
-    }
-    int count = 0;
-    cudaError_t e = cudaGetDeviceCount(&count);
-    if (e != cudaSuccess || count <= 0) {  // no CPU fallback: this is an error, not a mode
-        snprintf(g_create_err, sizeof g_create_err, "k8sgpu_create: no CUDA device (%s)",
-                 e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
-        return K8SGPU_E_CUDA;
-    }
-    if (devices[0] < 0 || devices[0] >= count) {
-        snprintf(g_create_err, sizeof g_create_err, "k8sgpu_create: device %d out of range [0,%d)", devices[0], count);
-        return K8SGPU_E_ARG;
-    }
+static std::mutex g_create_mu;  // guards g_create_err (messages of failed k8sgpu_create calls)
+
+static void create_err(char *errbuf, size_t errcap, const char *fmt, ...) {
+    char msg[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(msg, sizeof msg, fmt, ap);
+    va_end(ap);
+    if (errbuf && errcap) snprintf(errbuf, errcap, "%s", msg);
+    std::lock_guard<std::mutex> lock(g_create_mu);
+    snprintf(g_create_err, sizeof g_create_err, "%s", msg);
+}
+
+static int create_one(int device, k8sgpu_ctx **out, char *errbuf, size_t errcap) {
+    cudaError_t e;
     k8sgpu_ctx *ctx = new (std::nothrow) k8sgpu_ctx();
     if (!ctx) return K8SGPU_E_CUDA;
-    ctx->device = devices[0];
-#define CREATE_TRY(expr)                                                                             \
-    if ((e = (expr)) != cudaSuccess) {                                                               \
-        snprintf(g_create_err, sizeof g_create_err, "k8sgpu_create: %s: %s", #expr, cudaGetErrorString(e)); \
-        k8sgpu_destroy(ctx);                                                                         \
-        return K8SGPU_E_CUDA;                                                                        \
+    ctx->device = device;
+    ctx->local[0] = ctx;
+#define CREATE_TRY(expr)                                                                   \
+    if ((e = (expr)) != cudaSuccess) {                                                     \
+        create_err(errbuf, errcap, "k8sgpu_create: %s: %s", #expr, cudaGetErrorString(e)); \
+        k8sgpu_destroy(ctx);                                                               \
+        return K8SGPU_E_CUDA;                                                              \
     }
     CREATE_TRY(cudaSetDevice(ctx->device));
     cudaDeviceProp prop;
     CREATE_TRY(cudaGetDeviceProperties(&prop, ctx->device));
     if (prop.major < 10) {
-        snprintf(g_create_err, sizeof g_create_err, "k8sgpu_create: device %d is sm_%d%d; this library is sm_100a only",
-                 ctx->device, prop.major, prop.minor);
+        create_err(errbuf, errcap, "k8sgpu_create: device %d is sm_%d%d; this library is sm_100a only", ctx->device,
+                   prop.major, prop.minor);
         k8sgpu_destroy(ctx);
         return K8SGPU_E_CUDA;
     }
@@ -57,8 +94,64 @@ extern "C" int k8sgpu_create(const int *devices, int ndev, k8sgpu_ctx **out) {
     memset(ctx->h_pinned, 0, 64 * sizeof(uint32_t));
     CREATE_TRY(cudaHostGetDevicePointer((void **)&ctx->d_mailbox, ctx->h_pinned + 32, 0));
 #undef CREATE_TRY
+    tuning_from_env(ctx->tune);  // the only place the environment is read
     *out = ctx;
     return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_create_ex(const int *devices, int ndev, k8sgpu_ctx **out, char *errbuf, size_t errcap) {
+    if (!out) return K8SGPU_E_ARG;
+    *out = nullptr;
+    if (errbuf && errcap) errbuf[0] = 0;
+    if (ndev < 1 || ndev > 16 || !devices) {
+        create_err(errbuf, errcap, "k8sgpu_create: ndev must be 1..16 (got %d)", ndev);
+        return K8SGPU_E_ARG;
+    }
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0) {  // no CPU fallback: this is an error, not a mode
+        create_err(errbuf, errcap, "k8sgpu_create: no CUDA device (%s)",
+                   e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+        return K8SGPU_E_CUDA;
+    }
+    for (int i = 0; i < ndev; ++i) {
+        if (devices[i] < 0 || devices[i] >= count) {
+            create_err(errbuf, errcap, "k8sgpu_create: device %d out of range [0,%d)", devices[i], count);
+            return K8SGPU_E_ARG;
+        }
+        for (int j = 0; j < i; ++j)
+            if (devices[j] == devices[i]) {
+                create_err(errbuf, errcap, "k8sgpu_create: device %d listed twice", devices[i]);
+                return K8SGPU_E_ARG;
+            }
+    }
+    k8sgpu_ctx *lead = nullptr;
+    int rc = create_one(devices[0], &lead, errbuf, errcap);
+    if (rc) return rc;
+    for (int i = 1; i < ndev; ++i) {
+        k8sgpu_ctx *c = nullptr;
+        rc = create_one(devices[i], &c, errbuf, errcap);
+        if (rc) {
+            k8sgpu_destroy(lead);
+            return rc;
+        }
+        lead->local[lead->nlocal++] = c;
+    }
+    if (ndev > 1) {  // one process drives all the GPUs: communicators and peer access now
+        rc = group_init_local(lead);
+        if (rc) {
+            create_err(errbuf, errcap, "%s", lead->err);
+            k8sgpu_destroy(lead);
+            return rc;
+        }
+        cudaSetDevice(lead->device);
+    }
+    *out = lead;
+    return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_create(const int *devices, int ndev, k8sgpu_ctx **out) {
+    return k8sgpu_create_ex(devices, ndev, out, nullptr, 0);
 }
 
 static void release_sort(SortScratch &s) {
@@ -70,8 +163,15 @@ static void release_sort(SortScratch &s) {
 
 extern "C" int k8sgpu_destroy(k8sgpu_ctx *ctx) {
     if (!ctx) return K8SGPU_OK;
+    for (int i = ctx->nlocal - 1; i >= 1; --i) {  // the other GPUs of an in-process group first
+        k8sgpu_ctx *c = ctx->local[i];
+        ctx->local[i] = nullptr;
+        if (c) k8sgpu_destroy(c);
+    }
+    ctx->nlocal = 1;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    group_destroy(ctx);
     PlaceState &p = ctx->place;
     DevBuf *pb[] = {&p.node_cols, &p.pod_cols, &p.free_cols, &p.nodeq,     &p.podq,      &p.assign, &p.active[0],
                     &p.active[1], &p.best_key, &p.best,      &p.sort_keys, &p.sort_vals, &p.seg,    &p.flags,
@@ -82,10 +182,8 @@ extern "C" int k8sgpu_destroy(k8sgpu_ctx *ctx) {
     for (DevBuf *b : pb) b->release();
     release_sort(p.sort);
     ReconcileState &r = ctx->rec;
-    DevBuf *rb[] = {&r.desired,    &r.pool_owner, &r.vm_owner,  &r.vm_flags,  &r.vm_ordinal,     &r.lut,    &r.pool_of,
-                    &r.current,    &r.delta,      &r.create_count, &r.kvict,  &r.victim_off,     &r.member_off,
-                    &r.create_off, &r.span_off,   &r.sort_keys, &r.sort_vals, &r.victim_vm,      &r.create_ordinal,
-                    &r.bitmap,     &r.counters,   &r.scan_tmp};
+    DevBuf *rb[] = {&r.in_slab, &r.out_slab,  &r.lut,       &r.pool_tmp, &r.tot,     &r.bitmap,
+                    &r.sort_keys, &r.sort_vals, &r.cta_cnt, &r.counters, &r.scan_tmp};
     for (DevBuf *b : rb) b->release();
     release_sort(r.sort);
     for (DevBuf &b : ctx->dbg) b.release();

@@ -4,9 +4,12 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <thread>
+#include <time.h>
 
 #include "../../include/k8sgpu.h"
 
@@ -85,6 +88,7 @@ struct PlaceState {
     int peer_world = 0, peer_rank = -1;
     uint32_t peer_m = 0;         // proposals per half of the exchange buffer
     DevBuf gang_id, gang_min, gang_count, gang_state;  // gang placement: [m], [g], [g], [2g] (rejected, newly)
+    uint32_t coop_seq = 0, coop_grid = 0;  // admission launch in flight: mailbox sequence number, CTAs
     int timed = 0;        // scoring launches timed so far in this run
     uint64_t timed_evals = 0;
 };
@@ -92,15 +96,44 @@ struct PlaceState {
 struct ReconcileState {
     uint32_t p = 0, v = 0, n_owner_ids = 0;
     bool uploaded = false, ran = false, has_ordinal = false, want_members = false, want_ordinals = false;
-    DevBuf desired, pool_owner, vm_owner, vm_flags, vm_ordinal;
-    DevBuf lut, pool_of, current, delta, create_count, kvict, victim_off, member_off, create_off, span_off;
-    DevBuf sort_keys, sort_vals, victim_vm, create_ordinal, bitmap;
-    DevBuf counters;  // [0]=error flag
+    // One block per direction, so that a caller whose host columns lie back to back gets one copy.
+    // in_slab : desired[P] | pool_owner[P] | vm_owner[V] | vm_flags[V] | vm_ordinal[V]   (each padded to 16 B)
+    // out_slab: the k8sgpu_reconcile_layout sections, same order and padding as k8sgpu_reconcile_out_size
+    DevBuf in_slab, out_slab;
+    uint64_t in_off[6] = {}, out_off[12] = {};  // element offsets of the sections (out_off[11] = total)
+    uint64_t create_cap = 0;                     // elements reserved for create_ordinal (sum of desired)
+    DevBuf lut;       // owner id -> pool row, built at upload
+    DevBuf pool_tmp;  // kvict[P] | span_words[P] | word_off[P+1] | remaining[P] | seen[P] | cand_off[P+1]
+    DevBuf tot;       // small path: per-CTA member counts, pool major [P][G]
+    DevBuf bitmap;    // used-ordinal bits of the pools that scale up
+    DevBuf sort_keys, sort_vals;  // general path: (pool, row) pairs
+    DevBuf cta_cnt;   // pruning pass: candidates per CTA of the current segment
+    DevBuf counters;  // [0]=error flags, [1]=arrival ticket, [2]=pools still short of victims, [3]=candidates, [4..7]=totals
     SortScratch sort;
     DevBuf scan_tmp;
     uint32_t n_victims = 0, n_members = 0, n_creates = 0;
-    const uint32_t *sorted_vals = nullptr;  // rows grouped by pool (member_vm) after the last run
-    int coop_blocks_per_sm = 0;             // occupancy of reconcile_coop_kernel (0 = not queried)
+    const uint32_t *members_src = nullptr;  // rows grouped by pool after the last run (member_vm)
+    int small_occ = 0;                      // occupancy of the one-launch kernel at small_occ_smem bytes (0 = not queried)
+    size_t small_occ_smem = 0;
+    bool small_attr_set = false;
+    int prune_occ = 0;
+    uint32_t last_path = 0, last_grid = 0, last_segments = 0, last_candidates = 0;  // what the last run used
+};
+
+// Developer / test knobs.  Seeded once from K8SGPU_* environment variables at k8sgpu_create and
+// changed only through k8sgpu_set_tuning: nothing reads the environment after that.  -1 = automatic.
+struct Tuning {
+    int res = -1;        // eval_pair variant 0..4
+    int ppt = -1;        // pods per thread 1/2/4
+    int splits = -1;     // node splits of the scoring grid
+    int coop = -1;       // 1: one-launch admission, 0: kernel chain
+    int coop_grid = -1;  // CTAs of the cooperative admission launch
+    int rec_path = -1;   // 0: one-launch small-pool kernel, 1: pruned ranking, 2: full stable sort
+    int rec_grid = -1;   // CTAs of the cooperative reconcile launches
+    int rec_segments = -1;  // row segments of the pruned ranking pass
+    int coop_prof = 0, rec_prof = 0;  // print phase times (stderr)
+    int shard_admit = -1;   // multi-GPU: 1 = admission sharded by node range, 0 = replicated
+    int exchange = -1;      // multi-GPU: 0 = NCCL all-gather, 1 = peer stores
 };
 
 }  // namespace k8sgpu
@@ -121,6 +154,20 @@ struct k8sgpu_ctx {
     k8sgpu::ReconcileState rec;
     k8sgpu::DevBuf dbg[6];
     k8sgpu::SortScratch dbg_sort;
+    k8sgpu::Tuning tune;
+    // Placement group: the contexts (one per GPU) that shard one placement between them.  A context
+    // made by k8sgpu_create with ndev > 1 leads ndev - 1 more contexts of this process (local[0] is
+    // the leader itself); a context joined to other processes by k8sgpu_comm_init_rank is one rank
+    // of `world`.  comm is this device's NCCL communicator (ncclComm_t), null while single.
+    int world = 1, rank = 0, nlocal = 1;
+    k8sgpu_ctx *local[16] = {};
+    void *comm = nullptr;
+    k8sgpu::DevBuf xchg;      // proposals of all ranks (all-gather target / peer-store target, two halves)
+    k8sgpu::DevBuf xsend;     // this rank's proposals of the round (all-gather source)
+    k8sgpu::DevBuf xsmall;    // barrier word, IPC handles
+    uint32_t xchg_m = 0;      // proposals per half of xchg
+    int32_t *xpeer[16] = {};  // every rank's xchg as seen from this GPU (peer-store exchange)
+    bool xpeer_ready = false, xpeer_ipc = false;
 };
 
 namespace k8sgpu {
@@ -176,12 +223,64 @@ inline cudaStream_t pick_stream(const k8sgpu_ctx *ctx, void *stream) {
     return stream == K8SGPU_STREAM_OWN ? ctx->stream : (cudaStream_t)stream;
 }
 
+// Kernels post small results to mapped, pinned host memory ({seq, values...}: the values first,
+// a system-wide fence, then the sequence number) so that the host need not wait for the whole
+// kernel, or pay a copy plus a stream synchronise, to learn them.  This is the host side: a short
+// busy wait (the post usually lands within microseconds), then yields, then sleeps, so that a
+// controller sharing its cores with other work is not starved; the stream is queried now and then
+// so that a failed or finished kernel cannot leave the caller waiting for ever.
+inline int wait_mailbox(k8sgpu_ctx *ctx, volatile uint32_t *mb, uint32_t seq, cudaStream_t s, const char *what) {
+    for (uint32_t spins = 0; mb[0] != seq; ++spins) {
+        if (spins < 20000u) {
+#if defined(__x86_64__) || defined(__i386__)
+            __builtin_ia32_pause();
+#endif
+            if ((spins & 0x3FFu) != 0x3FFu) continue;
+        } else if (spins < 24000u) {
+            std::this_thread::yield();
+        } else {
+            timespec ts = {0, 50000};  // 50 us
+            nanosleep(&ts, nullptr);
+        }
+        cudaError_t q = cudaStreamQuery(s);
+        if (q == cudaSuccess) {
+            if (mb[0] == seq) break;
+            return fail(ctx, K8SGPU_E_CUDA, "%s: kernel finished without posting its result", what);
+        }
+        if (q != cudaErrorNotReady) return fail(ctx, K8SGPU_E_CUDA, "%s: kernel failed: %s", what, cudaGetErrorString(q));
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);  // the values were written before the sequence number
+    return K8SGPU_OK;
+}
+
 inline uint32_t ceil_div(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
 inline int key_bits(uint32_t max_key) {  // bits needed to hold values 0..max_key
     int b = 1;
     while (b < 32 && (max_key >> b)) ++b;
     return b;
 }
+
+// place.cu (host side of the round loop; group.cu drives them across GPUs)
+int check_tables(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods);
+int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods);
+int place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out);
+int place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy);
+int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s);
+int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cudaStream_t s, bool prep = true,
+                bool finalize = true);
+int round_finalize_peers(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *const *peer, int world, cudaStream_t s);
+int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t s, uint32_t *n_active_out);
+int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals);
+int round_admit_coop_launch(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals);
+int round_admit_coop_finish(k8sgpu_ctx *ctx, cudaStream_t s);
+int round_end(k8sgpu_ctx *ctx, cudaStream_t s);
+bool coop_admission(const k8sgpu_ctx *ctx);
+// group.cu
+int group_place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, const k8sgpu_gang_table *gangs /* may be null */);
+int group_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods);
+int group_sync(k8sgpu_ctx *ctx);
+int group_init_local(k8sgpu_ctx *ctx);
+void group_destroy(k8sgpu_ctx *ctx);
 
 // primitives.cu
 int exclusive_scan_u32(k8sgpu_ctx *ctx, cudaStream_t s, const uint32_t *d_in, uint32_t *d_out, uint32_t n,

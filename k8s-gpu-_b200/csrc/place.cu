@@ -14,8 +14,6 @@
 // ONE cooperative launch (admit_coop_kernel); the round-at-a-time API used across GPUs feeds the
 // same kernel the exchanged proposals (K8SGPU_COOP=0: separate kernels).  k8sgpu_place_gang wraps the same loop in reject / release / retry
 // iterations.  Integer only; no atomics decide any result except commutative max / add.
-#include <cstdlib>
-
 #include "prims.cuh"
 
 namespace k8sgpu {
@@ -940,7 +938,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
 
 // ------------------------------------------------------------------ host side
 
-static int check_tables(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods) {
+int check_tables(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods) {
     if (!nodes || !pods) return fail(ctx, K8SGPU_E_ARG, "place: NULL table");
     if (nodes->n >= 0x80000000u - 4096u || pods->m >= 0x80000000u)
         return fail(ctx, K8SGPU_E_ARG, "place: table too large (n=%u m=%u)", nodes->n, pods->m);
@@ -950,12 +948,13 @@ static int check_tables(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k
                              pods->zone_mask, pods->tol_mask, pods->pref_zone, pods->priority};
     for (int c = 0; c < 8; ++c) {
         if (nodes->n && !nc[c]) return fail(ctx, K8SGPU_E_ARG, "place: node column %d is NULL", c);
-        if (pods->m && !pc[c]) return fail(ctx, K8SGPU_E_ARG, "place: pod column %d is NULL", c);
+        if (pods->m && !pc[c] && c != 7)  // priority (column 7) is reserved and may be NULL
+            return fail(ctx, K8SGPU_E_ARG, "place: pod column %d is NULL", c);
     }
     return K8SGPU_OK;
 }
 
-static int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods) {
+int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods) {
     int rc = check_tables(ctx, nodes, pods);
     if (rc) return rc;
     PlaceState &st = ctx->place;
@@ -973,20 +972,19 @@ static int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k
                              pods->zone_mask, pods->tol_mask, pods->pref_zone, pods->priority};
     // A caller that keeps the eight columns of a table back to back in one block (the layout
     // the device uses) gets one copy per table instead of eight: fewer, larger transfers.
+    const int npc = pc[7] ? 8 : 7;  // the reserved priority column is not read by any kernel: NULL = not sent
     bool nslab = n > 0, pslab = m > 0;
-    for (int c = 0; c + 1 < 8; ++c) {
-        nslab = nslab && nc[c + 1] == nc[c] + n;
-        pslab = pslab && pc[c + 1] == pc[c] + m;
-    }
+    for (int c = 0; c + 1 < 8; ++c) nslab = nslab && nc[c + 1] == nc[c] + n;
+    for (int c = 0; c + 1 < npc; ++c) pslab = pslab && pc[c + 1] == pc[c] + m;
     if (nslab) K8S_CUDA(ctx, cudaMemcpyAsync(st.node_cols.p, nc[0], 8 * n * 4, cudaMemcpyHostToDevice, s));
-    if (pslab) K8S_CUDA(ctx, cudaMemcpyAsync(st.pod_cols.p, pc[0], 8 * m * 4, cudaMemcpyHostToDevice, s));
+    if (pslab) K8S_CUDA(ctx, cudaMemcpyAsync(st.pod_cols.p, pc[0], (size_t)npc * m * 4, cudaMemcpyHostToDevice, s));
     for (int c = 0; c < 8; ++c) {
         if (n && !nslab)
             K8S_CUDA(ctx, cudaMemcpyAsync(st.node_cols.as<uint32_t>() + c * n, nc[c], n * 4, cudaMemcpyHostToDevice, s));
-        if (m && !pslab)
+        if (m && !pslab && c < npc)
             K8S_CUDA(ctx, cudaMemcpyAsync(st.pod_cols.as<uint32_t>() + c * m, pc[c], m * 4, cudaMemcpyHostToDevice, s));
     }
-    ctx->stats.h2d_bytes += 8 * (n + m) * 4;
+    ctx->stats.h2d_bytes += (8 * n + (size_t)npc * m) * 4;
     // run-state buffers
     K8S_CUDA(ctx, st.free_cols.reserve(3 * n * 4 + 16));
     K8S_CUDA(ctx, st.nodeq.reserve((size_t)st.n_pad * sizeof(NodeQ)));
@@ -1012,7 +1010,7 @@ static int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k
     return K8SGPU_OK;
 }
 
-static int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
+int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
     PlaceState &st = ctx->place;
     if (!st.uploaded) return fail(ctx, K8SGPU_E_ARG, "place: no tables uploaded");
     st.policy_flags = policy ? policy->flags : 0u;
@@ -1026,7 +1024,7 @@ static int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_
     st.nodeq_stale = true;
     st.best_cleared_len = 0;
     st.score_res = kDefaultRes;  // which eval_pair variant (see its comment); all are bit-identical
-    if (const char *e = getenv("K8SGPU_RES")) st.score_res = atoi(e);
+    if (ctx->tune.res >= 0) st.score_res = ctx->tune.res;
     K8S_CUDA(ctx, cudaMemsetAsync(st.counters.p, 0, 64 * 4, s));
     if (st.n)
         K8S_CUDA(ctx, cudaMemcpyAsync(st.free_cols.p, st.node_cols.p, 3 * (size_t)st.n * 4, cudaMemcpyDeviceToDevice, s));
@@ -1040,8 +1038,7 @@ static int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_
 // Scores active positions [lo,hi) into d_best[0 .. hi-lo).
 // prep: rebuild the packed node records first; finalize: decode the packed keys into d_best.
 // (The single-launch admission path needs neither after round 0.)
-static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cudaStream_t s, bool prep = true,
-                       bool finalize = true) {
+int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cudaStream_t s, bool prep, bool finalize) {
     PlaceState &st = ctx->place;
     if (hi > st.n_active || lo > hi) return fail(ctx, K8SGPU_E_ARG, "score: bad slice [%u,%u) of %u", lo, hi, st.n_active);
     // node records from the current free columns (validated on the first round)
@@ -1063,12 +1060,12 @@ static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_bes
     // eval.  Four pay only on wide node tables, where few 64-node groups contain some pod's rot(p)
     // (profiles/r01_sweep_res4_ppt.txt).
     int ppt = st.score_res == 4 ? ((st.n >= 65536u && cnt >= 4u * 256u * 2u * sms) ? 4 : 2) : 1;
-    if (const char *e = getenv("K8SGPU_PPT")) ppt = atoi(e) >= 4 ? 4 : atoi(e) >= 2 ? 2 : 1;
+    if (ctx->tune.ppt >= 1) ppt = ctx->tune.ppt >= 4 ? 4 : ctx->tune.ppt >= 2 ? 2 : 1;
     if (ppt == 4 && st.score_res != 4) ppt = 2;
     const uint32_t xb = ceil_div(cnt, 256u * ppt);
     uint32_t splits = ceil_div(64u * sms, xb);
     if (splits > n_tiles) splits = n_tiles;
-    if (const char *e = getenv("K8SGPU_SPLITS")) splits = (uint32_t)atoi(e);
+    if (ctx->tune.splits >= 1) splits = (uint32_t)ctx->tune.splits;
     if (splits < 1) splits = 1;
     if (splits > n_tiles) splits = n_tiles;
     uint32_t tps = ceil_div(n_tiles, splits);
@@ -1116,7 +1113,7 @@ static int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_bes
 
 // Admission over all n_active proposals; leaves the next active list in active[cur^1] and its
 // length (device) in counters[1].  Synchronises the stream to read the count back.
-static int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t s, uint32_t *n_active_out) {
+int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t s, uint32_t *n_active_out) {
     PlaceState &st = ctx->place;
     const uint32_t na = st.n_active;
     uint32_t *cnts = st.counters.as<uint32_t>();
@@ -1166,7 +1163,9 @@ static int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t 
 
 // Single-launch admission (admit_coop_kernel) for the in-library single-GPU loop: consumes
 // best_key[0..n_active) as score_kernel left it, and leaves the next round's node records ready.
-static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals = nullptr) {
+// Launch half: returns as soon as the kernel is queued, so that a caller driving several GPUs can
+// queue all of them before it waits for any (round_admit_coop_finish).
+int round_admit_coop_launch(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals) {
     PlaceState &st = ctx->place;
     const uint32_t na = st.n_active;
     uint32_t *cnts = st.counters.as<uint32_t>();
@@ -1204,36 +1203,34 @@ static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *prop
     a.n_pad = st.n_pad;
     a.bits = key_bits(st.n);
     a.prof = nullptr;
-    static const bool want_prof = getenv("K8SGPU_COOP_PROF") != nullptr;
+    const bool want_prof = ctx->tune.coop_prof != 0;
     if (want_prof) a.prof = reinterpret_cast<unsigned long long *>(cnts + 16);  // counters[16..34)
     // enough CTAs to spread the tiles, few enough that the grid barriers stay cheap
     uint32_t want = ceil_div(na, 512u), prep = ceil_div(st.n_pad, 2048u);
     if (prep > want) want = prep;
     uint32_t cap = (uint32_t)ctx->sm_count * (uint32_t)(ctx->coop_blocks_per_sm < 2 ? ctx->coop_blocks_per_sm : 2);
     uint32_t grid = want < 1 ? 1 : (want > cap ? cap : want);
-    if (const char *e = getenv("K8SGPU_COOP_GRID")) {  // developer knob: CTAs in the cooperative grid
-        uint32_t g = (uint32_t)atoi(e);
-        if (g >= 1 && g <= cap) grid = g;
-    }
+    if (ctx->tune.coop_grid >= 1 && (uint32_t)ctx->tune.coop_grid <= cap) grid = (uint32_t)ctx->tune.coop_grid;
     a.mailbox = ctx->d_mailbox;
     a.seq = ++ctx->mail_seq;
     void *args[] = {&a};
     K8S_CUDA(ctx, cudaLaunchCooperativeKernel((void *)admit_coop_kernel, dim3(grid), dim3(256), args, 0, s));
     ctx->stats.kernel_launches++;
-    // The kernel posts {seq, count, flags} to mapped host memory as soon as the count is known;
-    // poll that instead of a copy + stream synchronise (saves a stream op and the wake-up).
+    st.coop_seq = a.seq;
+    st.coop_grid = grid;
+    return K8SGPU_OK;
+}
+
+// Wait half: the kernel posts {seq, count, flags} to mapped host memory as soon as the count is
+// known; the host waits for that instead of a copy + stream synchronise.
+int round_admit_coop_finish(k8sgpu_ctx *ctx, cudaStream_t s) {
+    PlaceState &st = ctx->place;
+    const uint32_t na = st.n_active, grid = st.coop_grid;
+    uint32_t *cnts = st.counters.as<uint32_t>();
+    const bool want_prof = ctx->tune.coop_prof != 0;
     volatile uint32_t *mb = ctx->h_pinned + 32;
-    for (uint32_t spins = 0; mb[0] != a.seq; ++spins) {
-        if ((spins & 0x3FFu) == 0x3FFu) {
-            cudaError_t q = cudaStreamQuery(s);
-            if (q == cudaSuccess) {
-                if (mb[0] == a.seq) break;
-                return fail(ctx, K8SGPU_E_CUDA, "place: admission kernel finished without posting its result");
-            }
-            if (q != cudaErrorNotReady)
-                return fail(ctx, K8SGPU_E_CUDA, "place: admission kernel failed: %s", cudaGetErrorString(q));
-        }
-    }
+    int wrc = wait_mailbox(ctx, mb, st.coop_seq, s, "place: admission");
+    if (wrc) return wrc;
     const uint32_t next_count = mb[1], err_flags = mb[2];
     if (err_flags & kErrProposal)
         return fail(ctx, K8SGPU_E_ARG, "place: proposal buffer holds values outside [-1, n): was it written on "
@@ -1261,7 +1258,27 @@ static int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *prop
     return K8SGPU_OK;
 }
 
-static int round_end(k8sgpu_ctx *ctx, cudaStream_t s) {
+
+int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals) {
+    int rc = round_admit_coop_launch(ctx, s, proposals);
+    if (rc) return rc;
+    return round_admit_coop_finish(ctx, s);
+}
+
+// Decode the packed best keys of active positions [lo, hi) and store each proposal at its
+// position in every buffer of `peer` (this GPU's own and the other ranks', mapped peer memory).
+int round_finalize_peers(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *const *peer, int world, cudaStream_t s) {
+    PlaceState &st = ctx->place;
+    if (hi <= lo) return K8SGPU_OK;
+    PeerPtrs pp;
+    for (int r = 0; r < 16; ++r) pp.p[r] = r < world ? peer[r] : nullptr;
+    pp.world = world;
+    K8S_LAUNCH(ctx, score_finalize_p2p_kernel, ceil_div(hi - lo, 256), 256, 0, s, st.best_key.as<unsigned long long>(),
+               st.podq.as<PodQ>(), st.active[st.cur].as<uint32_t>(), lo, hi - lo, st.n, pp);
+    return K8SGPU_OK;
+}
+
+int round_end(k8sgpu_ctx *ctx, cudaStream_t s) {
     PlaceState &st = ctx->place;
     uint32_t *cnts = st.counters.as<uint32_t>();
     K8S_CUDA(ctx, cudaMemsetAsync(cnts + 2, 0, 4, s));
@@ -1285,10 +1302,7 @@ static int round_end(k8sgpu_ctx *ctx, cudaStream_t s) {
     return K8SGPU_OK;
 }
 
-static bool coop_admission() {
-    if (const char *e = getenv("K8SGPU_COOP")) return atoi(e) != 0;
-    return true;
-}
+bool coop_admission(const k8sgpu_ctx *ctx) { return ctx->tune.coop < 0 ? true : ctx->tune.coop != 0; }
 
 // Rounds of score + admit until no pod is active (or max_rounds is reached).
 static int run_rounds(k8sgpu_ctx *ctx, cudaStream_t s) {
@@ -1296,13 +1310,13 @@ static int run_rounds(k8sgpu_ctx *ctx, cudaStream_t s) {
     // Admission as ONE cooperative launch per round (two launches per round in all): measured
     // ~3 % faster per config-3 step than the chain of ~20 small kernels.  K8SGPU_COOP=0 selects
     // the chain (the round-at-a-time API always uses it); both give identical results.
-    const bool coop = coop_admission();
+    const bool coop = coop_admission(ctx);
     int rc = K8SGPU_OK;
     while (st.n_active > 0 && (st.max_rounds == 0 || st.rounds < st.max_rounds)) {
         if (coop) {
             rc = round_score(ctx, 0, st.n_active, nullptr, s, /*prep=*/st.nodeq_stale, /*finalize=*/false);
             if (rc) return rc;
-            rc = round_admit_coop(ctx, s);  // leaves the next round's node records ready
+            rc = round_admit_coop(ctx, s, nullptr);  // leaves the next round's node records ready
         } else {
             rc = round_score(ctx, 0, st.n_active, st.best.as<int32_t>(), s);
             if (rc) return rc;
@@ -1313,7 +1327,7 @@ static int run_rounds(k8sgpu_ctx *ctx, cudaStream_t s) {
     return K8SGPU_OK;
 }
 
-static int place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy) {
+int place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy) {
     cudaStream_t s = ctx->stream;
     K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
     int rc = round_begin(ctx, policy, s);
@@ -1399,7 +1413,7 @@ __global__ void gang_ok_kernel(const uint32_t *__restrict__ state, uint32_t n_ga
 }
 
 // Gang table to the device, verdict state cleared.
-static int gang_setup(k8sgpu_ctx *ctx, const k8sgpu_gang_table *gangs, cudaStream_t s) {
+int gang_setup(k8sgpu_ctx *ctx, const k8sgpu_gang_table *gangs, cudaStream_t s) {
     PlaceState &st = ctx->place;
     if (!st.uploaded) return fail(ctx, K8SGPU_E_ARG, "place_gang: no tables uploaded");
     const uint32_t G = gangs->n_gangs, M = st.m;
@@ -1421,7 +1435,7 @@ static int gang_setup(k8sgpu_ctx *ctx, const k8sgpu_gang_table *gangs, cudaStrea
 // After a round loop that left no pod active: count placed members, reject gangs below
 // min_available for good, release their reservations, and build the retry list (unplaced pods of
 // surviving gangs, ascending pod index).  *n_retry == 0 means the placement is final.
-static int gang_verdicts(k8sgpu_ctx *ctx, cudaStream_t s, uint32_t *n_retry_out) {
+int gang_verdicts(k8sgpu_ctx *ctx, cudaStream_t s, uint32_t *n_retry_out) {
     PlaceState &st = ctx->place;
     const uint32_t G = st.n_gangs, M = st.m;
     uint32_t *cnts = st.counters.as<uint32_t>();
@@ -1498,7 +1512,7 @@ static int gang_ok_download(k8sgpu_ctx *ctx, cudaStream_t s, int32_t *gang_ok) {
     return K8SGPU_OK;
 }
 
-static int place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out) {
+int place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out) {
     PlaceState &st = ctx->place;
     cudaStream_t s = ctx->stream;
     if (!out) return fail(ctx, K8SGPU_E_ARG, "place: NULL out");
@@ -1530,16 +1544,15 @@ using namespace k8sgpu;
 extern "C" int k8sgpu_place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods) {
     K8S_ENTER(ctx);
     reset_call_stats(ctx);
-    int rc = place_upload(ctx, nodes, pods);
+    int rc = group_upload(ctx, nodes, pods);  // every GPU of the group gets a replica (one GPU: just this one)
     if (rc) return rc;
-    K8S_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return K8SGPU_OK;
+    return group_sync(ctx);
 }
 
 extern "C" int k8sgpu_place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy) {
     K8S_ENTER(ctx);
     reset_call_stats(ctx);
-    return place_run(ctx, policy);
+    return ctx->world > 1 ? group_place_run(ctx, policy, nullptr) : place_run(ctx, policy);
 }
 
 extern "C" int k8sgpu_place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out) {
@@ -1552,11 +1565,11 @@ extern "C" int k8sgpu_place(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, con
                             const k8sgpu_policy *policy, k8sgpu_place_out *out) {
     K8S_ENTER(ctx);
     reset_call_stats(ctx);
-    int rc = place_upload(ctx, nodes, pods);
+    int rc = group_upload(ctx, nodes, pods);
     if (rc) return rc;
-    rc = place_run(ctx, policy);
+    rc = ctx->world > 1 ? group_place_run(ctx, policy, nullptr) : place_run(ctx, policy);
     if (rc) return rc;
-    return place_download(ctx, out);
+    return place_download(ctx, out);  // the replicas are identical: the leader's copy is the result
 }
 
 extern "C" int k8sgpu_place_gang(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods,
@@ -1565,9 +1578,9 @@ extern "C" int k8sgpu_place_gang(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes
     K8S_ENTER(ctx);
     reset_call_stats(ctx);
     if (!gangs) return fail(ctx, K8SGPU_E_ARG, "place_gang: NULL gang table");
-    int rc = place_upload(ctx, nodes, pods);
+    int rc = group_upload(ctx, nodes, pods);
     if (rc) return rc;
-    rc = place_gang_run(ctx, gangs, policy);
+    rc = ctx->world > 1 ? group_place_run(ctx, policy, gangs) : place_gang_run(ctx, gangs, policy);
     if (rc) return rc;
     rc = gang_ok_download(ctx, ctx->stream, gang_ok);
     if (rc) return rc;
@@ -1653,7 +1666,7 @@ extern "C" int k8sgpu_place_round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_a
     K8S_ENTER(ctx);
     if (!d_best_all && ctx->place.n_active) return fail(ctx, K8SGPU_E_ARG, "round_admit: NULL device buffer");
     cudaStream_t s = ::k8sgpu::pick_stream(ctx, stream);
-    if (!coop_admission() || ctx->place.n_active == 0) return round_admit(ctx, d_best_all, s, n_active);
+    if (!coop_admission(ctx) || ctx->place.n_active == 0) return round_admit(ctx, d_best_all, s, n_active);
     int rc = round_admit_coop(ctx, s, d_best_all);  // one launch; also rebuilds the packed node records
     if (rc == K8SGPU_OK && n_active) *n_active = ctx->place.n_active;
     return rc;
@@ -1719,12 +1732,10 @@ extern "C" int k8sgpu_place_round_score_p2p(k8sgpu_ctx *ctx, uint32_t lo, uint32
         // Rounds alternate between the two halves of every exchange buffer: a fast rank's stores of
         // round r+1 must not land in the half a slower rank is still reading for round r.
         const size_t half = (size_t)(st.rounds & 1u) * st.peer_m;
-        PeerPtrs pp;
-        for (int r = 0; r < 16; ++r) pp.p[r] = r < st.peer_world ? st.peer_ptr[r] + half : nullptr;
-        pp.world = st.peer_world;
-        K8S_LAUNCH(ctx, score_finalize_p2p_kernel, ceil_div(hi - lo, 256), 256, 0, s,
-                   st.best_key.as<unsigned long long>(), st.podq.as<PodQ>(), st.active[st.cur].as<uint32_t>(), lo,
-                   hi - lo, st.n, pp);
+        int32_t *pp[16];
+        for (int r = 0; r < 16; ++r) pp[r] = r < st.peer_world ? st.peer_ptr[r] + half : nullptr;
+        rc = round_finalize_peers(ctx, lo, hi, pp, st.peer_world, s);
+        if (rc) return rc;
     }
     return K8SGPU_OK;
 }

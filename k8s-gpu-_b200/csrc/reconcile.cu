@@ -1,22 +1,91 @@
 // reconcile.cu -- steps 3-5 of AzureVmPoolReconciler.Reconcile (README.md:187-230) for every
 // pool of a snapshot at once.
 //
-//   tag filter (listManagedVMs, README.md:188-189,238)     -> match_kernel (128-bit SoA loads)
-//   existingVMs of each pool, in list order                -> stable sort of rows by pool
-//   currentCount := len(existingVMs)  (README.md:195)      -> per-pool counters filled by the tag filter
-//                                                             (chain of kernels: segment bounds of the sort)
-//   scaleUp / scaleDown counts (README.md:199-201,210-212) -> pool_kernel
-//   vmsToDelete := existingVMs[:scaleDownCount] (:214)     -> victim_gather_kernel
+//   tag filter (listManagedVMs, README.md:188-189,238)     -> owner id -> pool row table, one gather per VM row
+//   currentCount := len(existingVMs)  (README.md:195)      -> per-pool member counts (counts only: order-free)
+//   scaleUp / scaleDown counts (README.md:199-201,210-212) -> pool_math
+//   vmsToDelete := existingVMs[:scaleDownCount] (:214)     -> RANK of each row among the earlier rows of its
+//                                                             pool, in list order; rank < scaleDownCount = victim
 //   names of new VMs (README.md:204)         -> ordinal bitmap kernels
 //   Status.ReadyReplicas = currentCount (README.md:225)    -> ready == current
 // createVM / deleteVM themselves are ARM calls (network) and stay on the host.
-#include <cstdlib>
-
+//
+// The rank is all that list order is needed for, so nothing is sorted unless the caller asks for
+// the full member lists of a large table.  Three paths, all bit-identical (tests run each):
+//   0  one cooperative launch (pools <= kSmallMaxPools): every warp owns a contiguous run of rows
+//      and a private per-pool counter array in shared memory; per-CTA totals are prefix-summed over
+//      CTAs per pool, which turns the private counters into running global ranks.  Two grid
+//      barriers (three with create names).  Config 2 (1k pools x 100k VMs) runs here.
+//   1  many pools, victims only: global per-pool counts (RED), then a pruning pass over row
+//      segments that keeps only rows of pools still short of victims (a deterministic prefix of
+//      each such pool's rows), and the stable sort of just those candidates.
+//   2  many pools with member lists: the full stable sort by pool (rows grouped = Status.VMs).
 #include "prims.cuh"
 
 namespace k8sgpu {
 
 constexpr uint32_t kErrNegDesired = 1u, kErrDupOwner = 2u;
+constexpr uint32_t kSmallWarps = 8;          // warps per CTA of the one-launch kernel
+constexpr uint32_t kSmallMaxPools = 6144;    // 8 warps x 6144 pools x 4 B = 192 KB of shared memory
+constexpr uint32_t kRecMailbox = 8;          // reconcile's words of the mapped mailbox start here
+
+enum { kOutPoolOf = 0, kOutCurrent, kOutReady, kOutDelta, kOutCreateCount, kOutVictimOff, kOutMemberOff,
+       kOutCreateOff, kOutVictimVm, kOutMemberVm, kOutCreateOrdinal, kOutTotal };
+enum { kInVmOwner = 0, kInVmFlags, kInVmOrdinal, kInDesired, kInPoolOwner, kInTotal };
+
+// Section offsets (4-byte elements) of the output block: the V-sized tag-filter result first (so
+// that it is 16-byte aligned), then everything whose length is fixed by P, then the three lists
+// whose used length depends on the data.  Tightly packed: a caller that lays its host buffers out
+// the same way (k8sgpu_reconcile_out_size) gets one device->host copy for the fixed part.
+static void rec_out_layout(uint64_t P, uint64_t V, uint64_t C, uint64_t off[12]) {
+    uint64_t o = 0;
+    const uint64_t len[11] = {V, P, P, P, P, P + 1, P + 1, P + 1, V, V, C};
+    for (int i = 0; i < 11; ++i) {
+        off[i] = o;
+        o += len[i];
+    }
+    off[kOutTotal] = o;
+}
+
+static void rec_in_layout(uint64_t P, uint64_t V, uint64_t off[6]) {
+    uint64_t o = 0;
+    const uint64_t len[5] = {V, V, V, P, P};
+    for (int i = 0; i < 5; ++i) {
+        off[i] = o;
+        o += len[i];
+    }
+    off[kInTotal] = o;
+}
+
+// Copies queued back to back on one stream; entries whose source AND destination are adjacent
+// are merged into one transfer.
+struct CopyList {
+    struct E {
+        char *dst;
+        const char *src;
+        size_t bytes;
+    } e[16];
+    int n = 0;
+    uint64_t total = 0;
+    void add(void *dst, const void *src, size_t bytes) {
+        if (!bytes) return;
+        total += bytes;
+        if (n && e[n - 1].dst + e[n - 1].bytes == (char *)dst && e[n - 1].src + e[n - 1].bytes == (const char *)src) {
+            e[n - 1].bytes += bytes;
+            return;
+        }
+        e[n++] = {(char *)dst, (const char *)src, bytes};
+    }
+    cudaError_t issue(cudaMemcpyKind kind, cudaStream_t s) const {
+        for (int i = 0; i < n; ++i) {
+            cudaError_t err = cudaMemcpyAsync(e[i].dst, e[i].src, e[i].bytes, kind, s);
+            if (err != cudaSuccess) return err;
+        }
+        return cudaSuccess;
+    }
+};
+
+// ------------------------------------------------------------------ upload time: owner id -> pool row
 
 __global__ void pool_lut_kernel(const int32_t *__restrict__ desired, const uint32_t *__restrict__ owner, uint32_t P,
                                 uint32_t n_owner_ids, int32_t *__restrict__ lut, uint32_t *__restrict__ err) {
@@ -36,128 +105,47 @@ __device__ __forceinline__ int32_t match_one(uint32_t owner, uint32_t flags, uin
     return ((flags & 1u) && owner < n_owner_ids) ? __ldg(&lut[owner]) : -1;
 }
 
-// 4 VM rows per thread: one 128-bit load per input column, one 128-bit store per output column.
-__global__ void __launch_bounds__(256) match_kernel(const uint32_t *__restrict__ owner,
-                                                    const uint32_t *__restrict__ flags, uint32_t V,
-                                                    uint32_t n_owner_ids, const int32_t *__restrict__ lut, uint32_t P,
-                                                    int32_t *__restrict__ pool_of, uint32_t *__restrict__ keys,
-                                                    uint32_t *__restrict__ vals) {
-    const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;  // quad index
-    const uint32_t v0 = q * 4u;
-    if (v0 >= V) return;
-    if (v0 + 4u <= V) {
-        const uint4 o = __ldg(reinterpret_cast<const uint4 *>(owner) + q);
-        const uint4 f = __ldg(reinterpret_cast<const uint4 *>(flags) + q);
-        int4 p;
-        p.x = match_one(o.x, f.x, n_owner_ids, lut);
-        p.y = match_one(o.y, f.y, n_owner_ids, lut);
-        p.z = match_one(o.z, f.z, n_owner_ids, lut);
-        p.w = match_one(o.w, f.w, n_owner_ids, lut);
-        reinterpret_cast<int4 *>(pool_of)[q] = p;
-        uint4 k;
-        k.x = p.x < 0 ? P : (uint32_t)p.x;
-        k.y = p.y < 0 ? P : (uint32_t)p.y;
-        k.z = p.z < 0 ? P : (uint32_t)p.z;
-        k.w = p.w < 0 ? P : (uint32_t)p.w;
-        reinterpret_cast<uint4 *>(keys)[q] = k;
-        reinterpret_cast<uint4 *>(vals)[q] = make_uint4(v0, v0 + 1, v0 + 2, v0 + 3);
-    } else {
-        for (uint32_t v = v0; v < V; ++v) {
-            int32_t p = match_one(owner[v], flags[v], n_owner_ids, lut);
-            pool_of[v] = p;
-            keys[v] = p < 0 ? P : (uint32_t)p;
-            vals[v] = v;
-        }
-    }
-}
-
-// member_off[p] = first sorted position whose key >= p, for p in [0, P].
-__global__ void segment_bounds_kernel(const uint32_t *__restrict__ keys, uint32_t V, uint32_t P,
-                                      int32_t *__restrict__ member_off) {
-    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p > P) return;
-    uint32_t lo = 0, hi = V;
-    while (lo < hi) {
-        uint32_t mid = lo + ((hi - lo) >> 1);
-        if (__ldg(&keys[mid]) < p) lo = mid + 1;
-        else hi = mid;
-    }
-    member_off[p] = (int32_t)lo;
-}
-
-__global__ void pool_kernel(const int32_t *__restrict__ desired, const int32_t *__restrict__ member_off, uint32_t P,
-                            int32_t *__restrict__ current, int32_t *__restrict__ delta,
-                            int32_t *__restrict__ create_count, uint32_t *__restrict__ kvict,
-                            uint32_t *__restrict__ span_words) {
-    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= P) return;
-    int32_t cur = member_off[p + 1] - member_off[p];  // README.md:195
-    int32_t des = desired[p];                         // README.md:196
-    int32_t d = des - cur;
-    current[p] = cur;
-    delta[p] = d;
-    int32_t cc = d > 0 ? d : 0;                       // scaleUpCount, README.md:201
-    create_count[p] = cc;
-    kvict[p] = d < 0 ? (uint32_t)(-d) : 0u;           // scaleDownCount, README.md:212
-    // the cc lowest free ordinals all lie in [0, cur + cc)
-    span_words[p] = cc ? ((uint32_t)cur + (uint32_t)cc + 31u) / 32u : 0u;
-}
-
-// vmsToDelete := existingVMs[:scaleDownCount]  (README.md:214)
-__global__ void victim_gather_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals,
-                                     uint32_t n_members_upper, uint32_t P, const int32_t *__restrict__ member_off,
-                                     const uint32_t *__restrict__ kvict, const int32_t *__restrict__ victim_off,
-                                     uint32_t *__restrict__ victim_vm) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_members_upper) return;
-    uint32_t p = keys[i];
-    if (p >= P) return;  // unmanaged rows sort behind every pool
-    uint32_t r = i - (uint32_t)member_off[p];
-    if (r < kvict[p]) victim_vm[(uint32_t)victim_off[p] + r] = vals[i];
-}
-
-__global__ void ordinal_mark_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals, uint32_t V,
-                                    uint32_t P, const uint32_t *__restrict__ ordinal,
-                                    const int32_t *__restrict__ current, const int32_t *__restrict__ create_count,
-                                    const uint32_t *__restrict__ word_off, uint32_t *__restrict__ bitmap) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= V) return;
-    uint32_t p = keys[i];
-    if (p >= P) return;
-    uint32_t cc = (uint32_t)create_count[p];
-    if (!cc) return;
-    uint32_t o = ordinal[vals[i]];
-    if (o < (uint32_t)current[p] + cc) atomicOr(&bitmap[word_off[p] + (o >> 5)], 1u << (o & 31u));
+// README.md:195-212 for one pool, from its member count.  scaleDownCount can never exceed the
+// member count for a valid (non-negative) desired; the clamp keeps every later offset inside its
+// buffer even if an invalid table slipped through.
+struct PoolVerdict {
+    int32_t delta, create_count;
+    uint32_t kvict, span_words;
+};
+__device__ __forceinline__ PoolVerdict pool_math(int32_t cur, int32_t des) {
+    PoolVerdict r;
+    const long long d = (long long)des - (long long)cur;
+    r.delta = des - cur;                                        // README.md:201 / :212
+    r.create_count = d > 0 ? (int32_t)d : 0;                    // scaleUpCount
+    const long long k = d < 0 ? -d : 0;                         // scaleDownCount
+    r.kvict = (uint32_t)(k > cur ? cur : k);
+    // the create_count lowest free ordinals all lie in [0, cur + create_count)
+    r.span_words = r.create_count ? ((uint32_t)cur + (uint32_t)r.create_count + 31u) / 32u : 0u;
+    return r;
 }
 
 // One warp per pool: emit the create_count lowest clear bits of the pool's ordinal bitmap.
-__device__ __forceinline__ void ordinal_emit_pool(uint32_t p, const int32_t *__restrict__ current,
-                                                  const int32_t *__restrict__ create_count,
-                                                  const uint32_t *__restrict__ word_off,
-                                                  const uint32_t *__restrict__ bitmap,
-                                                  const int32_t *__restrict__ create_off,
-                                                  uint32_t *__restrict__ create_ordinal) {
+// (No __restrict__ / read-only loads here: the one-launch kernel calls this on arrays other CTAs
+// wrote earlier in the same launch, so every input is read from L2.)
+__device__ __forceinline__ void ordinal_emit_pool(uint32_t p, const int32_t *current, const int32_t *create_count,
+                                                  const uint32_t *word_off, const uint32_t *bitmap,
+                                                  const int32_t *create_off, uint32_t *create_ordinal) {
     const int lane = threadIdx.x & 31;
-    const uint32_t cc = (uint32_t)create_count[p];
+    const uint32_t cc = (uint32_t)__ldcg(&create_count[p]);
     if (!cc) return;
-    const uint32_t span = (uint32_t)current[p] + cc, words = (span + 31u) / 32u;
-    const uint32_t *bm = bitmap + word_off[p];
-    uint32_t *out = create_ordinal + (uint32_t)create_off[p];
+    const uint32_t span = (uint32_t)__ldcg(&current[p]) + cc, words = (span + 31u) / 32u;
+    const uint32_t *bm = bitmap + __ldcg(&word_off[p]);
+    uint32_t *out = create_ordinal + (uint32_t)__ldcg(&create_off[p]);
     uint32_t emitted = 0;
     for (uint32_t w0 = 0; w0 < words && emitted < cc; w0 += 32) {
         uint32_t w = w0 + lane;
         uint32_t free_bits = 0;
         if (w < words) {
-            free_bits = ~bm[w];
+            free_bits = ~__ldcg(&bm[w]);  // set by atomics of this launch: read it where they landed (L2)
             uint32_t rem = span - w * 32u;
             if (rem < 32u) free_bits &= (1u << rem) - 1u;
         }
-        uint32_t c = __popc(free_bits), inc = c;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
-            if (lane >= d) inc += y;
-        }
+        uint32_t c = __popc(free_bits), inc = warp_incl_scan(c, lane);
         uint32_t pos = emitted + inc - c;
         while (free_bits && pos < cc) {
             uint32_t b = __ffs(free_bits) - 1u;
@@ -176,198 +164,413 @@ __global__ void ordinal_emit_kernel(uint32_t P, const int32_t *__restrict__ curr
     if (p < P) ordinal_emit_pool(p, current, create_count, word_off, bitmap, create_off, create_ordinal);
 }
 
-// ------------------------------------------------------------------ one launch for the whole pass
-//
-// Config 2 (1k pools x 100k VMs) is 1.2 MB of work: as ~16 dependent kernels it is pure launch
-// latency.  reconcile_coop_kernel runs the same phases inside ONE cooperative launch with grid
-// barriers between them (same tile functions as the chain, so the results are identical).
-
-struct RecArgs {
-    const int32_t *desired;
-    const uint32_t *pool_owner, *vm_owner, *vm_flags, *vm_ordinal;  // vm_ordinal may be null
-    int32_t *lut;  // pre-set to -1 by the host
-    int32_t *pool_of, *current, *delta, *create_count, *member_off, *victim_off, *create_off;
-    uint32_t *keys, *vals, *keys_alt, *vals_alt, *hist, *hist_scan, *scan_sums;
-    uint32_t *kvict, *span_words, *word_off, *victim_vm, *bitmap /* pre-zeroed */, *create_ordinal, *counters;
-    uint32_t P, V, n_owner_ids;
-    int bits, want_ordinals;
-    unsigned long long *prof;  // optional (K8SGPU_REC_PROF): %globaltimer at each phase boundary, else null
-};
-
-__device__ __forceinline__ void rec_mark(const RecArgs &a, int slot) {
-    if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) {
-        unsigned long long t;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-        a.prof[slot] = t;
-    }
-}
-
-// README.md:195-212 for pool p, from its member count.
-__device__ __forceinline__ void pool_math(const RecArgs &a, uint32_t p) {
-    int32_t cur = a.current[p], d = a.desired[p] - cur;
-    a.delta[p] = d;
-    int32_t cc = d > 0 ? d : 0;
-    a.create_count[p] = cc;
-    a.kvict[p] = d < 0 ? (uint32_t)(-d) : 0u;
-    a.span_words[p] = cc ? ((uint32_t)cur + (uint32_t)cc + 31u) / 32u : 0u;
-}
-
-// Exclusive scan of n <= 16 tiles by the calling CTA alone; out[n] = total.
-__device__ __forceinline__ void cta_exclusive_scan(const uint32_t *in, uint32_t *out, uint32_t n) {
+// Exclusive scan of n elements by the calling CTA alone (256 threads); out[n] = total.
+__device__ __forceinline__ uint32_t cta_exclusive_scan(const uint32_t *in, uint32_t *out, uint32_t n) {
     uint32_t carry = 0;
     for (uint32_t t = 0; t * kScanTile < n; ++t) carry = block_scan_tile(in, out, t * kScanTile, n, carry, true);
     if (threadIdx.x == 0) out[n] = carry;
+    return carry;
+}
+
+// ------------------------------------------------------------------ path 0: one launch, few pools
+
+struct RecSmallArgs {
+    const uint32_t *vm_owner, *vm_flags, *vm_ordinal;  // vm_ordinal may be null
+    const int32_t *desired, *lut;
+    int32_t *pool_of, *current, *ready, *delta, *create_count, *victim_off, *member_off, *create_off;
+    uint32_t *victim_vm, *member_vm, *create_ordinal;
+    uint32_t *tot;  // [P][G] members of pool p among CTA c's rows; prefix-summed over c in place
+    uint32_t *kvict, *span_words, *word_off, *bitmap, *counters, *mailbox;
+    uint32_t P, V, n_owner_ids, rows_per_warp /* multiple of 32 */, bitmap_words, seq;
+    int want_members, want_ordinals;
+    unsigned long long *prof;  // optional: %globaltimer at each phase boundary (CTA 0), else null
+};
+
+__device__ __forceinline__ void rec_mark(unsigned long long *prof, int slot) {
+    if (prof && blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        prof[slot] = t;
+    }
 }
 
 // Phases (each line ends in a grid barrier):
-//   1. owner id -> pool row table; member counters zeroed
-//   2. tag filter, sort keys, digit-0 histogram, per-pool member count (warp-aggregated atomics:
-//      counts only, order-free)
-//   3. per 8-bit digit: histogram (after digit 0), its scan, the stable scatter.  While CTA 0
-//      scans the first histogram, the LAST CTA does everything that needs only the counts --
-//      currentCount, the diff, and the offsets of every output list -- so none of that costs a
-//      barrier of its own (when P is too large for one CTA, the whole grid does it instead).
-//   4. victims = first -delta rows of each pool's run of the sorted list; used-ordinal bits
-//   5. names of the VMs to create (lowest free ordinals)
-__global__ void __launch_bounds__(256) reconcile_coop_kernel(RecArgs a) {
+//   A. tag filter of this warp's rows -> pool_of; members per (warp, pool) in shared memory;
+//      members per (CTA, pool) to global memory; ordinal bitmap cleared
+//   B. one warp per pool: prefix sum of the per-CTA counts (= rank base of each CTA's rows),
+//      currentCount, the diff, scale-up / scale-down counts.  The CTA that finishes last also
+//      turns the per-pool counts into the offsets of every output list and tells the host the
+//      list lengths -- no barrier of its own.
+//   C. the per-(warp, pool) counts become running ranks; second walk over the same rows in list
+//      order: rank < scaleDownCount -> victim slot (README.md:214); member slot; used-ordinal bit
+//   D. names of the VMs to create (lowest free ordinals), one warp per pool
+__global__ void __launch_bounds__(kSmallWarps * 32) reconcile_small_kernel(RecSmallArgs a) {
     cg::grid_group grid = cg::this_grid();
-    const uint32_t tid = threadIdx.x, cta = blockIdx.x, G = gridDim.x, gtid = cta * 256 + tid, gsz = G * 256;
+    extern __shared__ uint32_t cnt[];  // [kSmallWarps][P]
+    __shared__ uint32_t is_last;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5, cta = blockIdx.x, G = gridDim.x;
     const uint32_t P = a.P, V = a.V;
-    const uint32_t nb = (V + kSortTile - 1) / kSortTile;
-    const bool one_cta_pools = (P + kScanTile - 1) / kScanTile <= 16;
-    constexpr uint32_t kSmallP = 4096;  // pools whose member counters fit in shared memory
-    __shared__ uint32_t pcount[kSmallP];
-    const bool small_p = P <= kSmallP;
-    if (small_p)
-        for (uint32_t p = tid; p < P; p += 256) pcount[p] = 0;
-    rec_mark(a, 0);
+    const uint32_t lt = (1u << lane) - 1u;
+    rec_mark(a.prof, 0);
 
-    for (uint32_t p = gtid; p < P; p += gsz) {  // owner id -> pool row
-        if (a.desired[p] < 0) atomicOr(a.counters, kErrNegDesired);
-        uint32_t o = a.pool_owner[p];
-        if (o < a.n_owner_ids && atomicCAS(&a.lut[o], -1, (int32_t)p) != -1) atomicOr(a.counters, kErrDupOwner);
-        a.current[p] = 0;
+    for (uint32_t i = tid; i < kSmallWarps * P; i += blockDim.x) cnt[i] = 0;
+    if (a.want_ordinals)
+        for (uint32_t i = cta * blockDim.x + tid; i < a.bitmap_words; i += G * blockDim.x) a.bitmap[i] = 0;
+    if (cta == 0 && tid == 0) a.counters[1] = 0;  // arrival ticket of phase B
+    __syncthreads();
+
+    uint32_t *mine = cnt + warp * P;
+    const uint64_t gw = (uint64_t)cta * kSmallWarps + warp;
+    const uint64_t r0_64 = gw * a.rows_per_warp;
+    const uint32_t r0 = r0_64 < V ? (uint32_t)r0_64 : V;
+    const uint32_t r1 = (uint64_t)r0 + a.rows_per_warp < V ? r0 + a.rows_per_warp : V;
+    constexpr int U = 4;  // steps of 32 rows whose loads are issued together
+    for (uint32_t v0 = r0; v0 < r1; v0 += 32 * U) {
+        uint32_t ow[U], fl[U];
+        int32_t pp[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint32_t v = v0 + u * 32 + lane;
+            ow[u] = v < r1 ? __ldg(&a.vm_owner[v]) : K8SGPU_NONE_U32;
+            fl[u] = v < r1 ? __ldg(&a.vm_flags[v]) : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) pp[u] = match_one(ow[u], fl[u], a.n_owner_ids, a.lut);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint32_t v = v0 + u * 32 + lane;
+            if (v < r1) a.pool_of[v] = pp[u];
+            const uint32_t key = (v < r1 && pp[u] >= 0) ? (uint32_t)pp[u] : K8SGPU_NONE_U32;
+            const uint32_t peers = __match_any_sync(0xFFFFFFFFu, key);
+            // currentCount := len(existingVMs), README.md:195.  The lowest lane of each pool's
+            // group adds the group's size: distinct pools, distinct words, no atomics.
+            if (key != K8SGPU_NONE_U32 && (peers & lt) == 0u) mine[key] += (uint32_t)__popc(peers);
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+    for (uint32_t p = tid; p < P; p += blockDim.x) {
+        uint32_t t = 0;
+#pragma unroll
+        for (uint32_t w = 0; w < kSmallWarps; ++w) t += cnt[w * P + p];
+        a.tot[(size_t)p * G + cta] = t;
     }
     grid.sync();
-    rec_mark(a, 1);
-    for (uint32_t vt = cta; vt < nb; vt += G) {  // tag filter + sort keys + digit-0 histogram + member counts
-        // all loads of the tile first (the stores below would otherwise fence each row's loads
-        // behind the previous row's stores: 8 dependent round trips instead of 2)
-        uint32_t ow[kSortTile / 256], fl[kSortTile / 256];
-        int32_t pp[kSortTile / 256];
+    rec_mark(a.prof, 1);
+
+    for (uint32_t p = cta * kSmallWarps + warp; p < P; p += G * kSmallWarps) {
+        uint32_t *row = a.tot + (size_t)p * G;
+        uint32_t run = 0;
+        for (uint32_t c0 = 0; c0 < G; c0 += 32) {
+            const uint32_t c = c0 + lane;
+            const uint32_t x = c < G ? __ldcg(&row[c]) : 0u;
+            const uint32_t inc = warp_incl_scan(x, lane);
+            if (c < G) row[c] = run + inc - x;
+            run += __shfl_sync(0xFFFFFFFFu, inc, 31);
+        }
+        if (lane == 0) {
+            const int32_t cur = (int32_t)run;
+            const PoolVerdict r = pool_math(cur, a.desired[p]);
+            a.current[p] = cur;
+            a.ready[p] = cur;  // README.md:225: ReadyReplicas = currentCount, the pre-action count
+            a.delta[p] = r.delta;
+            a.create_count[p] = r.create_count;
+            a.kvict[p] = r.kvict;
+            a.span_words[p] = r.span_words;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        is_last = atomicAdd(&a.counters[1], 1u) == G - 1 ? 1u : 0u;
+    }
+    __syncthreads();
+    if (is_last) {  // every pool's counts are in global memory, and visible: offsets of the output lists
+        __threadfence();
+        const uint32_t nm = cta_exclusive_scan((const uint32_t *)a.current, (uint32_t *)a.member_off, P);
+        const uint32_t nv = cta_exclusive_scan(a.kvict, (uint32_t *)a.victim_off, P);
+        const uint32_t nc = cta_exclusive_scan((const uint32_t *)a.create_count, (uint32_t *)a.create_off, P);
+        if (a.want_ordinals) cta_exclusive_scan(a.span_words, a.word_off, P);
+        if (tid == 0) {  // the host can size its copies while phases C and D run
+            volatile uint32_t *mb = a.mailbox;
+            mb[1] = a.counters[0];
+            mb[2] = nv;
+            mb[3] = nm;
+            mb[4] = nc;
+            __threadfence_system();
+            mb[0] = a.seq;
+        }
+    }
+    grid.sync();
+    rec_mark(a.prof, 2);
+
+    for (uint32_t p = tid; p < P; p += blockDim.x) {  // counts -> running ranks of each warp's next row
+        uint32_t b = __ldcg(&a.tot[(size_t)p * G + cta]);
 #pragma unroll
-        for (uint32_t r = 0; r < kSortTile / 256; ++r) {
-            uint32_t v = vt * kSortTile + r * 256 + tid;
-            ow[r] = v < V ? a.vm_owner[v] : K8SGPU_NONE_U32;
-            fl[r] = v < V ? a.vm_flags[v] : 0u;
+        for (uint32_t w = 0; w < kSmallWarps; ++w) {
+            const uint32_t t = cnt[w * P + p];
+            cnt[w * P + p] = b;
+            b += t;
+        }
+    }
+    __syncthreads();
+    const bool ords = a.want_ordinals && a.vm_ordinal;
+    for (uint32_t v0 = r0; v0 < r1; v0 += 32 * U) {
+        int32_t pp[U];
+        uint32_t kv[U], voff[U], moff[U], cc[U], cur[U], woff[U], ord[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint32_t v = v0 + u * 32 + lane;
+            pp[u] = v < r1 ? a.pool_of[v] : -1;  // this thread's own store of phase A
         }
 #pragma unroll
-        for (uint32_t r = 0; r < kSortTile / 256; ++r)  // README.md:238; the table was written in phase 1: L2 load
-            pp[r] = ((fl[r] & 1u) && ow[r] < a.n_owner_ids) ? __ldcg(&a.lut[ow[r]]) : -1;
+        for (int u = 0; u < U; ++u) {
+            const bool m = pp[u] >= 0;
+            const uint32_t p = m ? (uint32_t)pp[u] : 0u, v = v0 + u * 32 + lane;
+            kv[u] = m ? __ldcg(&a.kvict[p]) : 0u;
+            voff[u] = m ? (uint32_t)__ldcg(&a.victim_off[p]) : 0u;
+            moff[u] = (m && a.want_members) ? (uint32_t)__ldcg(&a.member_off[p]) : 0u;
+            cc[u] = (m && ords) ? (uint32_t)__ldcg(&a.create_count[p]) : 0u;
+            cur[u] = (m && ords) ? (uint32_t)__ldcg(&a.current[p]) : 0u;
+            woff[u] = (m && ords) ? __ldcg(&a.word_off[p]) : 0u;
+            ord[u] = (m && ords) ? __ldg(&a.vm_ordinal[v]) : K8SGPU_NONE_U32;
+        }
 #pragma unroll
-        for (uint32_t r = 0; r < kSortTile / 256; ++r) {
-            uint32_t v = vt * kSortTile + r * 256 + tid;
-            uint32_t key = 0xFFFFFFFFu;  // rows past the end: no pool, nothing stored
-            if (v < V) {
-                int32_t p = pp[r];
-                a.pool_of[v] = p;
-                key = p < 0 ? P : (uint32_t)p;
-                a.keys[v] = key;
-                a.vals[v] = v;
+        for (int u = 0; u < U; ++u) {
+            const uint32_t v = v0 + u * 32 + lane;
+            const uint32_t key = pp[u] >= 0 ? (uint32_t)pp[u] : K8SGPU_NONE_U32;
+            const uint32_t peers = __match_any_sync(0xFFFFFFFFu, key);
+            uint32_t rank = 0;
+            if (key != K8SGPU_NONE_U32) rank = mine[key] + (uint32_t)__popc(peers & lt);  // rows of this pool before v
+            __syncwarp();
+            if (key != K8SGPU_NONE_U32) {
+                if ((peers & lt) == 0u) mine[key] += (uint32_t)__popc(peers);
+                if (rank < kv[u]) a.victim_vm[voff[u] + rank] = v;  // existingVMs[:scaleDownCount], README.md:214
+                if (a.want_members) a.member_vm[moff[u] + rank] = v;
+                if (cc[u] && ord[u] < cur[u] + cc[u]) atomicOr(&a.bitmap[woff[u] + (ord[u] >> 5)], 1u << (ord[u] & 31u));
             }
-            // currentCount := len(existingVMs), README.md:195 (counts only: order-free)
-            if (small_p) {
-                if (key < P) atomicAdd(&pcount[key], 1u);
-            } else {  // one global atomic per distinct pool per warp
-                const uint32_t peers = __match_any_sync(0xFFFFFFFFu, key);
-                if (key < P && (tid & 31u) == (uint32_t)__ffs(peers) - 1u)
-                    atomicAdd(&a.current[key], (int32_t)__popc(peers));
+            __syncwarp();
+        }
+    }
+    if (!a.want_ordinals) {
+        rec_mark(a.prof, 3);
+        return;
+    }
+    grid.sync();
+    rec_mark(a.prof, 3);
+    for (uint32_t p = cta * kSmallWarps + warp; p < P; p += G * kSmallWarps)  // one warp per pool
+        ordinal_emit_pool(p, a.current, a.create_count, a.word_off, a.bitmap, a.create_off, a.create_ordinal);
+    rec_mark(a.prof, 4);
+}
+
+// ------------------------------------------------------------------ paths 1 and 2: many pools
+
+// Tag filter, 4 VM rows per thread (128-bit loads and stores when the columns are 16-byte
+// aligned), and currentCount by one RED per managed row (counts only: order-free).
+__global__ void __launch_bounds__(256) match_count_kernel(const uint32_t *__restrict__ owner,
+                                                          const uint32_t *__restrict__ flags, uint32_t V,
+                                                          uint32_t n_owner_ids, const int32_t *__restrict__ lut,
+                                                          int32_t *__restrict__ pool_of, int32_t *__restrict__ current,
+                                                          int vec) {
+    const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;  // quad index
+    const uint32_t v0 = q * 4u;
+    if (v0 >= V) return;
+    if (vec && v0 + 4u <= V) {
+        const uint4 o = __ldg(reinterpret_cast<const uint4 *>(owner) + q);
+        const uint4 f = __ldg(reinterpret_cast<const uint4 *>(flags) + q);
+        int4 p;
+        p.x = match_one(o.x, f.x, n_owner_ids, lut);
+        p.y = match_one(o.y, f.y, n_owner_ids, lut);
+        p.z = match_one(o.z, f.z, n_owner_ids, lut);
+        p.w = match_one(o.w, f.w, n_owner_ids, lut);
+        reinterpret_cast<int4 *>(pool_of)[q] = p;
+        if (p.x >= 0) atomicAdd(&current[p.x], 1);
+        if (p.y >= 0) atomicAdd(&current[p.y], 1);
+        if (p.z >= 0) atomicAdd(&current[p.z], 1);
+        if (p.w >= 0) atomicAdd(&current[p.w], 1);
+    } else {
+        for (uint32_t v = v0; v < V && v < v0 + 4u; ++v) {
+            int32_t p = match_one(owner[v], flags[v], n_owner_ids, lut);
+            pool_of[v] = p;
+            if (p >= 0) atomicAdd(&current[p], 1);
+        }
+    }
+}
+
+// counters[2] += pools that scale down (the pruning pass stops when it reaches 0)
+__global__ void pool_kernel(const int32_t *__restrict__ desired, uint32_t P, const int32_t *__restrict__ current,
+                            int32_t *__restrict__ ready, int32_t *__restrict__ delta,
+                            int32_t *__restrict__ create_count, uint32_t *__restrict__ kvict,
+                            uint32_t *__restrict__ span_words, uint32_t *__restrict__ remaining,
+                            uint32_t *__restrict__ seen, uint32_t *__restrict__ counters) {
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t down = 0;
+    if (p < P) {
+        const int32_t cur = current[p];  // README.md:195
+        const PoolVerdict r = pool_math(cur, desired[p]);
+        ready[p] = cur;  // README.md:225
+        delta[p] = r.delta;
+        create_count[p] = r.create_count;
+        kvict[p] = r.kvict;
+        span_words[p] = r.span_words;
+        remaining[p] = r.kvict;
+        seen[p] = 0;
+        down = r.kvict ? 1u : 0u;
+    }
+    const uint32_t n = __popc(__ballot_sync(0xFFFFFFFFu, down));
+    if ((threadIdx.x & 31u) == 0 && n) atomicAdd(&counters[2], n);
+}
+
+__global__ void keys_from_pool_kernel(const int32_t *__restrict__ pool_of, uint32_t V, uint32_t P,
+                                      uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= V) return;
+    const int32_t p = pool_of[v];
+    keys[v] = p < 0 ? P : (uint32_t)p;  // unmanaged rows sort behind every pool
+    vals[v] = v;
+}
+
+// vmsToDelete := existingVMs[:scaleDownCount]  (README.md:214).  (keys, vals) = rows grouped by
+// pool in list order; first[p] = where pool p's run starts.
+__global__ void victim_gather_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals, uint32_t n,
+                                     uint32_t P, const uint32_t *__restrict__ first,
+                                     const uint32_t *__restrict__ kvict, const int32_t *__restrict__ victim_off,
+                                     uint32_t *__restrict__ victim_vm) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t p = keys[i];
+    if (p >= P) return;
+    uint32_t r = i - first[p];
+    if (r < kvict[p]) victim_vm[(uint32_t)victim_off[p] + r] = vals[i];
+}
+
+__global__ void ordinal_mark_kernel(const int32_t *__restrict__ pool_of, uint32_t V,
+                                    const uint32_t *__restrict__ ordinal, const int32_t *__restrict__ current,
+                                    const int32_t *__restrict__ create_count, const uint32_t *__restrict__ word_off,
+                                    uint32_t *__restrict__ bitmap) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= V) return;
+    const int32_t p = pool_of[v];
+    if (p < 0) return;
+    const uint32_t cc = (uint32_t)create_count[p];
+    if (!cc) return;
+    const uint32_t o = ordinal[v];
+    if (o < (uint32_t)current[p] + cc) atomicOr(&bitmap[word_off[p] + (o >> 5)], 1u << (o & 31u));
+}
+
+// Pruning pass of path 1.  A row can only be a victim while its pool has seen fewer than
+// scaleDownCount rows, so the table is walked in S row segments, in order, and a row of segment s
+// is kept as a CANDIDATE iff its pool was still short of victims when segment s began
+// (remaining[p] > 0, a value that depends only on the counts of earlier segments).  The
+// candidates of a pool are therefore a prefix, in list order, of that pool's rows, at least
+// scaleDownCount long: their stable sort by pool yields the victims.  The pass stops at the first
+// segment boundary where no pool is short any more -- on config-2-like data after about half the
+// table, with ~10 % of the rows kept.
+//   phase 1 of a segment: candidate flags (bit mask in shared memory), seen[p] += 1 per candidate
+//   phase 2: candidates written in list order (CTA bases from the per-CTA counts), remaining[p]
+//            refreshed from seen[p]; pools that reached their count leave counters[2]
+struct PruneArgs {
+    const int32_t *pool_of;
+    const uint32_t *kvict;
+    uint32_t *remaining, *seen, *cta_cnt, *cand_keys, *cand_vals, *counters;
+    uint32_t V, segments, rows_per_cta;  // rows_per_cta: multiple of 256, per segment
+};
+constexpr uint32_t kPruneMaxRowsPerCta = 65536;  // 2048 mask words
+
+__global__ void __launch_bounds__(256) prune_kernel(PruneArgs a) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ uint32_t mask[kPruneMaxRowsPerCta / 32];
+    __shared__ uint32_t red[8], red2[8];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5, cta = blockIdx.x, G = gridDim.x;
+    const uint32_t words = a.rows_per_cta / 32u;
+    const uint64_t seg_rows = (uint64_t)a.rows_per_cta * G;
+    uint32_t total = 0;  // candidates of all earlier segments (every CTA computes the same number)
+    for (uint32_t s = 0; s < a.segments; ++s) {
+        const uint64_t lo64 = (uint64_t)s * seg_rows + (uint64_t)cta * a.rows_per_cta;
+        const uint32_t lo = lo64 < a.V ? (uint32_t)lo64 : a.V;
+        const uint32_t hi = (uint64_t)lo + a.rows_per_cta < a.V ? lo + a.rows_per_cta : a.V;
+        uint32_t mine = 0;
+        for (uint32_t t = 0; t * 256u < a.rows_per_cta; ++t) {
+            const uint32_t v = lo + t * 256u + tid;
+            bool cand = false;
+            int32_t p = -1;
+            if (v < hi) p = a.pool_of[v];
+            if (p >= 0) cand = __ldcg(&a.remaining[p]) > 0u;
+            if (cand) atomicAdd(&a.seen[p], 1u);
+            const uint32_t m = __ballot_sync(0xFFFFFFFFu, cand);
+            if (lane == 0) {
+                mask[t * 8u + warp] = m;
+                mine += (uint32_t)__popc(m);
             }
         }
-        if (small_p) {  // flush this tile's per-pool counts
-            __syncthreads();
-            for (uint32_t p = tid; p < P; p += 256) {
-                const uint32_t c = pcount[p];
-                if (c) {
-                    atomicAdd(&a.current[p], (int32_t)c);
-                    pcount[p] = 0;
-                }
-            }
+        if (lane == 0) red[warp] = mine;
+        __syncthreads();
+        if (tid == 0) {
+            uint32_t c = 0;
+            for (int w = 0; w < 8; ++w) c += red[w];
+            a.cta_cnt[cta] = c;
+        }
+        grid.sync();
+        // my base = candidates so far + those of the CTAs before me in this segment
+        uint32_t before = 0, all = 0;
+        for (uint32_t c = tid; c < G; c += 256u) {
+            const uint32_t x = __ldcg(&a.cta_cnt[c]);
+            all += x;
+            before += c < cta ? x : 0u;
+        }
+        before = __reduce_add_sync(0xFFFFFFFFu, before);
+        all = __reduce_add_sync(0xFFFFFFFFu, all);
+        __syncthreads();  // red[] of phase 1 has been read
+        if (lane == 0) {
+            red[warp] = before;
+            red2[warp] = all;
         }
         __syncthreads();
-        if (vt == 0) rec_mark(a, 6);
-        sort_hist_tile(a.keys, V, 0, 0xFFu, a.hist, nb, vt);
-        if (vt == 0) rec_mark(a, 7);
-    }
-    grid.sync();
-    rec_mark(a, 2);
-    if (one_cta_pools) {
-        if (cta == G - 1) {  // overlaps the first histogram scan (CTA 0) unless the grid is one CTA
-            for (uint32_t p = tid; p < P; p += 256) pool_math(a, p);
+        before = all = 0;
+        for (int w = 0; w < 8; ++w) {
+            before += red[w];
+            all += red2[w];
+        }
+        uint32_t run = total + before;
+        for (uint32_t w0 = 0; w0 < words; w0 += 256u) {  // 256 mask words (8192 rows) per step, in order
+            const uint32_t w = w0 + tid;
+            const uint32_t m = w < words ? mask[w] : 0u;
+            const uint32_t c = (uint32_t)__popc(m), inc = warp_incl_scan(c, lane);
             __syncthreads();
-            cta_exclusive_scan((const uint32_t *)a.current, (uint32_t *)a.member_off, P);
-            cta_exclusive_scan(a.kvict, (uint32_t *)a.victim_off, P);
-            cta_exclusive_scan((const uint32_t *)a.create_count, (uint32_t *)a.create_off, P);
-            if (a.want_ordinals) {
-                cta_exclusive_scan(a.span_words, a.word_off, P);
-                if (tid == 0) a.counters[4] = a.word_off[P];
+            if (lane == 31) red[warp] = inc;
+            __syncthreads();
+            uint32_t woff = 0, step = 0;
+            for (int k = 0; k < 8; ++k) {
+                woff += k < (int)warp ? red[k] : 0u;
+                step += red[k];
             }
+            uint32_t pos = run + woff + inc - c;
+            uint32_t bits = m;
+            while (bits) {
+                const uint32_t b = (uint32_t)__ffs(bits) - 1u;
+                bits &= bits - 1u;
+                // word w = (tile w / 8, warp w % 8): rows lo + (w/8)*256 + (w%8)*32 + b
+                const uint32_t v = lo + (w >> 3) * 256u + (w & 7u) * 32u + b;
+                const uint32_t p = (uint32_t)a.pool_of[v];
+                a.cand_keys[pos] = p;
+                a.cand_vals[pos] = v;
+                ++pos;
+                const uint32_t k = a.kvict[p], sn = __ldcg(&a.seen[p]);
+                const uint32_t rem = k > sn ? k - sn : 0u;
+                // every candidate of the pool stores the same value; whoever replaces the last
+                // non-zero one takes the pool off the list of pools still short
+                if (atomicExch(&a.remaining[p], rem) > 0u && rem == 0u) atomicSub(&a.counters[2], 1u);
+            }
+            run += step;
         }
-    } else {
-        for (uint32_t p = gtid; p < P; p += gsz) pool_math(a, p);
+        total += all;
         grid.sync();
-        coop_exclusive_scan(grid, (const uint32_t *)a.current, (uint32_t *)a.member_off, P, a.scan_sums,
-                            (uint32_t *)a.member_off + P);
-        coop_exclusive_scan(grid, a.kvict, (uint32_t *)a.victim_off, P, a.scan_sums, (uint32_t *)a.victim_off + P);
-        coop_exclusive_scan(grid, (const uint32_t *)a.create_count, (uint32_t *)a.create_off, P, a.scan_sums,
-                            (uint32_t *)a.create_off + P);
-        if (a.want_ordinals) coop_exclusive_scan(grid, a.span_words, a.word_off, P, a.scan_sums, a.counters + 4);
+        if (__ldcg(&a.counters[2]) == 0u) break;  // no pool is short of victims: the rest of the table cannot matter
     }
-    uint32_t *sk = a.keys, *sv = a.vals, *dk = a.keys_alt, *dv = a.vals_alt;
-    if (V > 0) {
-        for (int shift = 0; shift < a.bits; shift += 8) {
-            const int w = a.bits - shift < 8 ? a.bits - shift : 8;
-            const uint32_t mask = (1u << w) - 1u;
-            if (shift > 0) {
-                for (uint32_t vt = cta; vt < nb; vt += G) sort_hist_tile(sk, V, shift, mask, a.hist, nb, vt);
-                grid.sync();
-            }
-            if (nb <= kLocalScanMaxTiles) {  // every CTA scans the small histogram itself: no scan phase, no barrier
-                for (uint32_t vt = cta; vt < nb; vt += G) sort_scatter_tile(sk, sv, dk, dv, V, shift, mask, a.hist, nb, vt, true);
-            } else {
-                coop_exclusive_scan(grid, a.hist, a.hist_scan, nb * 256u, a.scan_sums, nullptr);
-                for (uint32_t vt = cta; vt < nb; vt += G) sort_scatter_tile(sk, sv, dk, dv, V, shift, mask, a.hist_scan, nb, vt);
-            }
-            grid.sync();
-            uint32_t *t;
-            t = sk; sk = dk; dk = t;
-            t = sv; sv = dv; dv = t;
-        }
-    } else {
-        grid.sync();  // the offsets written by the last CTA become visible to everyone
-    }
-    // (the host knows where the sorted pairs ended up: in keys/vals after an even number of passes)
-    rec_mark(a, 3);
-    for (uint32_t i = gtid; i < V; i += gsz) {  // victims (README.md:214) and used-ordinal bits
-        uint32_t p = sk[i];
-        if (p >= P) continue;
-        uint32_t r = i - (uint32_t)a.member_off[p];
-        if (r < a.kvict[p]) a.victim_vm[(uint32_t)a.victim_off[p] + r] = sv[i];
-        if (a.want_ordinals && a.vm_ordinal) {
-            uint32_t cc = (uint32_t)a.create_count[p];
-            if (cc) {
-                uint32_t o = a.vm_ordinal[sv[i]];
-                if (o < (uint32_t)a.current[p] + cc) atomicOr(&a.bitmap[a.word_off[p] + (o >> 5)], 1u << (o & 31u));
-            }
-        }
-    }
-    if (!a.want_ordinals) return;
-    grid.sync();
-    rec_mark(a, 4);
-    for (uint32_t p = gtid >> 5; p < P; p += gsz >> 5)  // one warp per pool
-        ordinal_emit_pool(p, a.current, a.create_count, a.word_off, a.bitmap, a.create_off, a.create_ordinal);
-    rec_mark(a, 5);
+    if (cta == 0 && tid == 0) a.counters[3] = total;
 }
+
+// ------------------------------------------------------------------ host side
 
 static int rec_upload(k8sgpu_ctx *ctx, const k8sgpu_pool_table *pools, const k8sgpu_vm_table *vms,
                       uint32_t n_owner_ids) {
@@ -380,226 +583,324 @@ static int rec_upload(k8sgpu_ctx *ctx, const k8sgpu_pool_table *pools, const k8s
     if (pools->p && (!pools->desired || !pools->owner_id)) return fail(ctx, K8SGPU_E_ARG, "reconcile: NULL pool column");
     if (vms->v && (!vms->owner_id || !vms->flags)) return fail(ctx, K8SGPU_E_ARG, "reconcile: NULL VM column");
     const size_t P = pools->p, V = vms->v;
+    // Spec.Replicas carries +kubebuilder:validation:Minimum=0 (README.md:94).  Checked here, before
+    // anything is launched: every list offset below is derived from it.
+    uint64_t sum_desired = 0;
+    for (size_t p = 0; p < P; ++p) {
+        if (pools->desired[p] < 0)
+            return fail(ctx, K8SGPU_E_ARG, "reconcile: negative desired replicas (pool row %zu: %d)", p, pools->desired[p]);
+        sum_desired += (uint64_t)pools->desired[p];
+    }
+    if (sum_desired > 0x7FFFFFFFull) return fail(ctx, K8SGPU_E_ARG, "reconcile: sum of desired replicas exceeds 2^31");
     st.p = pools->p;
     st.v = vms->v;
     st.n_owner_ids = n_owner_ids;
     st.has_ordinal = vms->ordinal != nullptr;
-    K8S_CUDA(ctx, st.desired.reserve(P * 4 + 16));
-    K8S_CUDA(ctx, st.pool_owner.reserve(P * 4 + 16));
-    K8S_CUDA(ctx, st.vm_owner.reserve(V * 4 + 16));
-    K8S_CUDA(ctx, st.vm_flags.reserve(V * 4 + 16));
-    if (P) {
-        K8S_CUDA(ctx, cudaMemcpyAsync(st.desired.p, pools->desired, P * 4, cudaMemcpyHostToDevice, s));
-        K8S_CUDA(ctx, cudaMemcpyAsync(st.pool_owner.p, pools->owner_id, P * 4, cudaMemcpyHostToDevice, s));
-    }
-    if (V) {
-        K8S_CUDA(ctx, cudaMemcpyAsync(st.vm_owner.p, vms->owner_id, V * 4, cudaMemcpyHostToDevice, s));
-        K8S_CUDA(ctx, cudaMemcpyAsync(st.vm_flags.p, vms->flags, V * 4, cudaMemcpyHostToDevice, s));
-    }
-    ctx->stats.h2d_bytes += (2 * P + 2 * V) * 4;
-    if (st.has_ordinal) {
-        K8S_CUDA(ctx, st.vm_ordinal.reserve(V * 4 + 16));
-        if (V) K8S_CUDA(ctx, cudaMemcpyAsync(st.vm_ordinal.p, vms->ordinal, V * 4, cudaMemcpyHostToDevice, s));
-        ctx->stats.h2d_bytes += V * 4;
-    }
+    st.create_cap = sum_desired;
+    rec_in_layout(P, V, st.in_off);
+    rec_out_layout(P, V, sum_desired, st.out_off);
+    K8S_CUDA(ctx, st.in_slab.reserve(st.in_off[kInTotal] * 4 + 64));
+    K8S_CUDA(ctx, st.out_slab.reserve(st.out_off[kOutTotal] * 4 + 64));
+    uint32_t *in = st.in_slab.as<uint32_t>();
+    CopyList cl;
+    cl.add(in + st.in_off[kInVmOwner], vms->owner_id, V * 4);
+    cl.add(in + st.in_off[kInVmFlags], vms->flags, V * 4);
+    if (st.has_ordinal) cl.add(in + st.in_off[kInVmOrdinal], vms->ordinal, V * 4);
+    cl.add(in + st.in_off[kInDesired], pools->desired, P * 4);
+    cl.add(in + st.in_off[kInPoolOwner], pools->owner_id, P * 4);
+    K8S_CUDA(ctx, cl.issue(cudaMemcpyHostToDevice, s));
+    ctx->stats.h2d_bytes += cl.total;
     // upper bound of the ordinal bitmap: sum over pools of ceil((cur + cc)/32) <= (V + sum desired)/32 + P
-    uint64_t sum_desired = 0;
-    for (size_t p = 0; p < P; ++p) sum_desired += pools->desired[p] > 0 ? (uint64_t)pools->desired[p] : 0u;
-    if (sum_desired > 0x7FFFFFFFull) return fail(ctx, K8SGPU_E_ARG, "reconcile: sum of desired replicas exceeds 2^31");
     const size_t bitmap_words = (V + sum_desired) / 32 + P + 1;
     K8S_CUDA(ctx, st.lut.reserve(((size_t)n_owner_ids + 1) * 4));
-    K8S_CUDA(ctx, st.pool_of.reserve(V * 4 + 16));
-    K8S_CUDA(ctx, st.current.reserve(P * 4 + 16));
-    K8S_CUDA(ctx, st.delta.reserve(P * 4 + 16));
-    K8S_CUDA(ctx, st.create_count.reserve(P * 4 + 16));
-    K8S_CUDA(ctx, st.kvict.reserve(P * 4 + 16));
-    K8S_CUDA(ctx, st.victim_off.reserve((P + 1) * 4 + 16));
-    K8S_CUDA(ctx, st.member_off.reserve((P + 2) * 4 + 16));
-    K8S_CUDA(ctx, st.create_off.reserve((P + 1) * 4 + 16));
-    K8S_CUDA(ctx, st.span_off.reserve((2 * P + 2) * 4 + 16));
-    K8S_CUDA(ctx, st.sort_keys.reserve(V * 4 + 16));
-    K8S_CUDA(ctx, st.sort_vals.reserve(V * 4 + 16));
-    K8S_CUDA(ctx, st.victim_vm.reserve(V * 4 + 16));
-    K8S_CUDA(ctx, st.create_ordinal.reserve((size_t)sum_desired * 4 + 16));
+    K8S_CUDA(ctx, st.pool_tmp.reserve((6 * P + 8) * 4));
     K8S_CUDA(ctx, st.bitmap.reserve(bitmap_words * 4));
     K8S_CUDA(ctx, st.counters.reserve(64 * 4));
+    // owner id -> pool row: part of the uploaded state (every run of these tables uses it)
+    K8S_CUDA(ctx, cudaMemsetAsync(st.counters.p, 0, 64 * 4, s));
+    K8S_CUDA(ctx, cudaMemsetAsync(st.lut.p, 0xFF, ((size_t)n_owner_ids + 1) * 4, s));
+    if (P)
+        K8S_LAUNCH(ctx, pool_lut_kernel, ceil_div((uint32_t)P, 256), 256, 0, s,
+                   reinterpret_cast<const int32_t *>(in + st.in_off[kInDesired]), in + st.in_off[kInPoolOwner], (uint32_t)P,
+                   n_owner_ids, st.lut.as<int32_t>(), st.counters.as<uint32_t>());
     st.uploaded = true;
     return K8SGPU_OK;
 }
 
-static int rec_finish(k8sgpu_ctx *ctx, cudaStream_t s);
+struct RecPtrs {
+    const uint32_t *vm_owner, *vm_flags, *vm_ordinal, *pool_owner;
+    const int32_t *desired;
+    int32_t *pool_of, *current, *ready, *delta, *create_count, *victim_off, *member_off, *create_off;
+    uint32_t *victim_vm, *member_vm, *create_ordinal;
+    uint32_t *kvict, *span_words, *word_off, *remaining, *seen, *cand_off;
+};
+static RecPtrs rec_ptrs(const ReconcileState &st) {
+    RecPtrs r;
+    const uint32_t *in = st.in_slab.as<uint32_t>();
+    uint32_t *out = st.out_slab.as<uint32_t>();
+    r.vm_owner = in + st.in_off[kInVmOwner];
+    r.vm_flags = in + st.in_off[kInVmFlags];
+    r.vm_ordinal = st.has_ordinal ? in + st.in_off[kInVmOrdinal] : nullptr;
+    r.desired = reinterpret_cast<const int32_t *>(in + st.in_off[kInDesired]);
+    r.pool_owner = in + st.in_off[kInPoolOwner];
+    r.pool_of = reinterpret_cast<int32_t *>(out + st.out_off[kOutPoolOf]);
+    r.current = reinterpret_cast<int32_t *>(out + st.out_off[kOutCurrent]);
+    r.ready = reinterpret_cast<int32_t *>(out + st.out_off[kOutReady]);
+    r.delta = reinterpret_cast<int32_t *>(out + st.out_off[kOutDelta]);
+    r.create_count = reinterpret_cast<int32_t *>(out + st.out_off[kOutCreateCount]);
+    r.victim_off = reinterpret_cast<int32_t *>(out + st.out_off[kOutVictimOff]);
+    r.member_off = reinterpret_cast<int32_t *>(out + st.out_off[kOutMemberOff]);
+    r.create_off = reinterpret_cast<int32_t *>(out + st.out_off[kOutCreateOff]);
+    r.victim_vm = out + st.out_off[kOutVictimVm];
+    r.member_vm = out + st.out_off[kOutMemberVm];
+    r.create_ordinal = out + st.out_off[kOutCreateOrdinal];
+    const size_t P = st.p;
+    uint32_t *t = st.pool_tmp.as<uint32_t>();
+    r.kvict = t;
+    r.span_words = t + P;
+    r.word_off = t + 2 * P;          // P + 1
+    r.remaining = t + 3 * P + 1;
+    r.seen = t + 4 * P + 1;
+    r.cand_off = t + 5 * P + 1;      // P + 1
+    return r;
+}
 
-static int rec_run_coop(k8sgpu_ctx *ctx, cudaStream_t s) {
+static int rec_check_flags(k8sgpu_ctx *ctx, uint32_t err) {
+    if (err & kErrNegDesired) return fail(ctx, K8SGPU_E_ARG, "reconcile: negative desired replicas");
+    if (err & kErrDupOwner) return fail(ctx, K8SGPU_E_ARG, "reconcile: two pools share an owner id");
+    return K8SGPU_OK;
+}
+
+// Path 0: the whole pass as one cooperative launch.
+static int rec_run_small(k8sgpu_ctx *ctx, cudaStream_t s) {
     ReconcileState &st = ctx->rec;
     const uint32_t P = st.p, V = st.v;
-    uint32_t *cnts = st.counters.as<uint32_t>();
-    if (st.coop_blocks_per_sm == 0) {
-        int per_sm = 0;
-        K8S_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, reconcile_coop_kernel, 256, 0));
-        st.coop_blocks_per_sm = per_sm > 0 ? per_sm : -1;
+    const RecPtrs q = rec_ptrs(st);
+    const size_t smem = (size_t)kSmallWarps * P * 4;
+    if (!st.small_attr_set) {  // more than 48 KB of dynamic shared memory needs the opt-in
+        K8S_CUDA(ctx, cudaFuncSetAttribute(reconcile_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)(kSmallWarps * kSmallMaxPools * 4)));
+        st.small_attr_set = true;
     }
-    if (st.coop_blocks_per_sm < 0) return fail(ctx, K8SGPU_E_CUDA, "cooperative reconcile kernel cannot be resident");
-    const uint32_t nb = ceil_div(V ? V : 1u, kSortTile);
-    K8S_CUDA(ctx, st.sort.keys_alt.reserve((size_t)V * 4 + 16));
-    K8S_CUDA(ctx, st.sort.vals_alt.reserve((size_t)V * 4 + 16));
-    K8S_CUDA(ctx, st.sort.hist.reserve(((size_t)nb * 256 * 2 + 256) * 4));
-    K8S_CUDA(ctx, st.sort.scan_tmp.reserve(((size_t)nb * 256 / kScanTile + (size_t)P / kScanTile + 128) * 4));
-    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
-    K8S_CUDA(ctx, cudaMemsetAsync(cnts, 0, 64 * 4, s));
-    K8S_CUDA(ctx, cudaMemsetAsync(st.lut.p, 0xFF, ((size_t)st.n_owner_ids + 1) * 4, s));
-    if (st.want_ordinals) K8S_CUDA(ctx, cudaMemsetAsync(st.bitmap.p, 0, st.bitmap.cap, s));
-    RecArgs a;
-    a.desired = st.desired.as<int32_t>();
-    a.pool_owner = st.pool_owner.as<uint32_t>();
-    a.vm_owner = st.vm_owner.as<uint32_t>();
-    a.vm_flags = st.vm_flags.as<uint32_t>();
-    a.vm_ordinal = st.has_ordinal ? st.vm_ordinal.as<uint32_t>() : nullptr;
-    a.lut = st.lut.as<int32_t>();
-    a.pool_of = st.pool_of.as<int32_t>();
-    a.current = st.current.as<int32_t>();
-    a.delta = st.delta.as<int32_t>();
-    a.create_count = st.create_count.as<int32_t>();
-    a.member_off = st.member_off.as<int32_t>();
-    a.victim_off = st.victim_off.as<int32_t>();
-    a.create_off = st.create_off.as<int32_t>();
-    a.keys = st.sort_keys.as<uint32_t>();
-    a.vals = st.sort_vals.as<uint32_t>();
-    a.keys_alt = st.sort.keys_alt.as<uint32_t>();
-    a.vals_alt = st.sort.vals_alt.as<uint32_t>();
-    a.hist = st.sort.hist.as<uint32_t>();
-    a.hist_scan = a.hist + (size_t)nb * 256;
-    a.scan_sums = st.sort.scan_tmp.as<uint32_t>();
-    a.kvict = st.kvict.as<uint32_t>();
-    a.span_words = st.span_off.as<uint32_t>();
-    a.word_off = a.span_words + P + 1;
-    a.victim_vm = st.victim_vm.as<uint32_t>();
+    if (st.small_occ == 0 || st.small_occ_smem != smem) {
+        int occ = 0;
+        K8S_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, reconcile_small_kernel, kSmallWarps * 32, smem));
+        st.small_occ = occ > 0 ? occ : -1;
+        st.small_occ_smem = smem;
+    }
+    const int per_sm = st.small_occ;
+    if (per_sm < 1) return fail(ctx, K8SGPU_E_CUDA, "cooperative reconcile kernel cannot be resident (P=%u)", P);
+    // CTAs: about 1024 rows each while the pass is latency bound (one per SM at config 2: measured
+    // best, the grid barriers stay cheap), up to four per SM once there is bandwidth to fill.
+    uint32_t cap = (uint32_t)ctx->sm_count * (uint32_t)(per_sm < 4 ? per_sm : 4);
+    uint32_t grid = ceil_div(V ? V : 1u, 1024u);
+    if (grid > cap) grid = cap;
+    if (ctx->tune.rec_grid >= 1 && (uint32_t)ctx->tune.rec_grid <= (uint32_t)ctx->sm_count * (uint32_t)per_sm)
+        grid = (uint32_t)ctx->tune.rec_grid;
+    K8S_CUDA(ctx, st.tot.reserve(((size_t)P * grid + 4) * 4));
+    RecSmallArgs a;
+    a.vm_owner = q.vm_owner; a.vm_flags = q.vm_flags; a.vm_ordinal = q.vm_ordinal;
+    a.desired = q.desired; a.lut = st.lut.as<int32_t>();
+    a.pool_of = q.pool_of; a.current = q.current; a.ready = q.ready; a.delta = q.delta;
+    a.create_count = q.create_count; a.victim_off = q.victim_off; a.member_off = q.member_off;
+    a.create_off = q.create_off; a.victim_vm = q.victim_vm; a.member_vm = q.member_vm;
+    a.create_ordinal = q.create_ordinal;
+    a.tot = st.tot.as<uint32_t>();
+    a.kvict = q.kvict; a.span_words = q.span_words; a.word_off = q.word_off;
     a.bitmap = st.bitmap.as<uint32_t>();
-    a.create_ordinal = st.create_ordinal.as<uint32_t>();
-    a.counters = cnts;
-    a.P = P;
-    a.V = V;
-    a.n_owner_ids = st.n_owner_ids;
-    a.bits = key_bits(P);
+    a.counters = st.counters.as<uint32_t>();
+    a.mailbox = ctx->d_mailbox + kRecMailbox;
+    a.P = P; a.V = V; a.n_owner_ids = st.n_owner_ids;
+    a.rows_per_warp = ceil_div(ceil_div(V ? V : 1u, grid * kSmallWarps), 32u) * 32u;
+    a.bitmap_words = (uint32_t)(((size_t)V + st.create_cap) / 32 + P + 1);
+    a.seq = ++ctx->mail_seq;
+    a.want_members = st.want_members ? 1 : 0;
     a.want_ordinals = st.want_ordinals ? 1 : 0;
-    const int passes = V ? (a.bits + 7) / 8 : 0;
-    st.sorted_vals = (passes & 1) ? a.vals_alt : a.vals;
-    // CTAs: enough to spread the tiles (+1 for the pool offsets), few enough that the grid barriers
-    // stay cheap -- at most one per SM while the pass is latency bound (measured at config 2:
-    // 98-148 CTAs 57-58 us, 196 CTAs 62 us), two per SM beyond that.
-    uint32_t want = ceil_div(V ? V : 1u, 1024u) + 1u, pw = ceil_div(P + 1, 256u);
-    if (pw > want) want = pw;
-    const uint32_t per_sm = (V <= (256u << 10) || st.coop_blocks_per_sm < 2) ? 1u : 2u;
-    uint32_t cap = (uint32_t)ctx->sm_count * per_sm;
-    uint32_t grid = want > cap ? cap : want;
-    if (const char *e = getenv("K8SGPU_REC_GRID")) {  // developer knob: CTAs in the cooperative grid
-        uint32_t g = (uint32_t)atoi(e);
-        if (g >= 1 && g <= (uint32_t)ctx->sm_count * (uint32_t)st.coop_blocks_per_sm) grid = g;
-    }
-    static const bool want_prof = getenv("K8SGPU_REC_PROF") != nullptr;
-    a.prof = want_prof ? reinterpret_cast<unsigned long long *>(cnts + 16) : nullptr;  // counters[16..28)
+    a.prof = ctx->tune.rec_prof ? reinterpret_cast<unsigned long long *>(a.counters + 16) : nullptr;
+    st.last_path = 0;
+    st.last_grid = grid;
+    st.members_src = q.member_vm;
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
     void *args[] = {&a};
-    K8S_CUDA(ctx, cudaLaunchCooperativeKernel((void *)reconcile_coop_kernel, dim3(grid), dim3(256), args, 0, s));
+    K8S_CUDA(ctx, cudaLaunchCooperativeKernel((void *)reconcile_small_kernel, dim3(grid), dim3(kSmallWarps * 32), args,
+                                              smem, s));
     ctx->stats.kernel_launches++;
-    int rc = rec_finish(ctx, s);
-    if (want_prof && rc == K8SGPU_OK) {  // developer aid: phase boundaries (CTA 0's clock), microseconds
-        unsigned long long t[8];
-        K8S_CUDA(ctx, cudaMemcpy(t, cnts + 16, sizeof t, cudaMemcpyDeviceToHost));
-        fprintf(stderr, "[reconcile coop CTA 0, tile 0] match %.1f hist %.1f barrier %.1f us\n", (t[6] - t[1]) / 1e3,
-                (t[7] - t[6]) / 1e3, (t[2] - t[7]) / 1e3);
-        fprintf(stderr, "[reconcile coop P=%u V=%u grid=%u] lut %.1f match+hist %.1f pools+sort %.1f gather %.1f "
-                        "ordinals %.1f kernel %.1f us, events %.1f us\n",
-                P, V, grid, (t[1] - t[0]) / 1e3, (t[2] - t[1]) / 1e3, (t[3] - t[2]) / 1e3, (t[4] - t[3]) / 1e3,
-                (t[5] - t[4]) / 1e3, (t[5] - t[0]) / 1e3, ctx->stats.device_ms * 1e3);
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_end, s));
+    // the list lengths arrive in mapped host memory half way through the kernel
+    volatile uint32_t *mb = ctx->h_pinned + 32 + kRecMailbox;
+    int rc = wait_mailbox(ctx, mb, a.seq, s, "reconcile");
+    if (rc) return rc;
+    rc = rec_check_flags(ctx, mb[1]);
+    if (rc) return rc;
+    st.n_victims = mb[2];
+    st.n_members = mb[3];
+    st.n_creates = mb[4];
+    if (ctx->tune.rec_prof) {  // developer aid: phase boundaries (CTA 0's clock), microseconds
+        unsigned long long t[5];
+        K8S_CUDA(ctx, cudaMemcpyAsync(t, a.counters + 16, sizeof t, cudaMemcpyDeviceToHost, s));
+        K8S_CUDA(ctx, cudaStreamSynchronize(s));
+        fprintf(stderr, "[reconcile one-launch P=%u V=%u grid=%u] filter+count %.1f pools %.1f rank %.1f names %.1f "
+                        "kernel %.1f us\n",
+                P, V, grid, (t[1] - t[0]) / 1e3, (t[2] - t[1]) / 1e3, (t[3] - t[2]) / 1e3,
+                st.want_ordinals ? (t[4] - t[3]) / 1e3 : 0.0, (t[st.want_ordinals ? 4 : 3] - t[0]) / 1e3);
     }
-    return rc;
+    return K8SGPU_OK;
+}
+
+// Paths 1 and 2: chains of kernels for tables with many pools.
+static int rec_run_large(k8sgpu_ctx *ctx, cudaStream_t s, bool full_sort) {
+    ReconcileState &st = ctx->rec;
+    const uint32_t P = st.p, V = st.v;
+    const RecPtrs q = rec_ptrs(st);
+    uint32_t *cnts = st.counters.as<uint32_t>();
+    K8S_CUDA(ctx, st.sort_keys.reserve((size_t)V * 4 + 16));
+    K8S_CUDA(ctx, st.sort_vals.reserve((size_t)V * 4 + 16));
+    uint32_t *keys = st.sort_keys.as<uint32_t>(), *vals = st.sort_vals.as<uint32_t>();
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
+    K8S_CUDA(ctx, cudaMemsetAsync(cnts + 1, 0, 7 * 4, s));  // [0] keeps the upload-time error flags
+    if (P) K8S_CUDA(ctx, cudaMemsetAsync(q.current, 0, (size_t)P * 4, s));
+    if (V) {
+        const int vec = ((((uintptr_t)q.vm_owner | (uintptr_t)q.vm_flags | (uintptr_t)q.pool_of) & 15u) == 0) ? 1 : 0;
+        K8S_LAUNCH(ctx, match_count_kernel, ceil_div(ceil_div(V, 4), 256), 256, 0, s, q.vm_owner, q.vm_flags, V,
+                   st.n_owner_ids, st.lut.as<int32_t>(), q.pool_of, q.current, vec);
+    }
+    if (P) {
+        K8S_LAUNCH(ctx, pool_kernel, ceil_div(P, 256), 256, 0, s, q.desired, P, q.current, q.ready, q.delta,
+                   q.create_count, q.kvict, q.span_words, q.remaining, q.seen, cnts);
+        int rc = exclusive_scan_u32(ctx, s, q.kvict, (uint32_t *)q.victim_off, P, st.scan_tmp, (uint32_t *)q.victim_off + P);
+        if (rc) return rc;
+        rc = exclusive_scan_u32(ctx, s, (const uint32_t *)q.create_count, (uint32_t *)q.create_off, P, st.scan_tmp,
+                                (uint32_t *)q.create_off + P);
+        if (rc) return rc;
+        rc = exclusive_scan_u32(ctx, s, (const uint32_t *)q.current, (uint32_t *)q.member_off, P, st.scan_tmp,
+                                (uint32_t *)q.member_off + P);
+        if (rc) return rc;
+    } else {
+        K8S_CUDA(ctx, cudaMemsetAsync(q.victim_off, 0, 4, s));
+        K8S_CUDA(ctx, cudaMemsetAsync(q.create_off, 0, 4, s));
+        K8S_CUDA(ctx, cudaMemsetAsync(q.member_off, 0, 4, s));
+    }
+    st.last_segments = st.last_candidates = 0;
+    if (V && P && full_sort) {
+        // rows grouped by pool, in list order: Status.VMs of every pool, and the victims at the
+        // head of each run
+        st.last_path = 2;
+        K8S_LAUNCH(ctx, keys_from_pool_kernel, ceil_div(V, 256), 256, 0, s, q.pool_of, V, P, keys, vals);
+        int rc = sort_pairs(ctx, s, keys, vals, V, key_bits(P), st.sort);
+        if (rc) return rc;
+        K8S_LAUNCH(ctx, victim_gather_kernel, ceil_div(V, 256), 256, 0, s, keys, vals, V, P,
+                   (const uint32_t *)q.member_off, q.kvict, q.victim_off, q.victim_vm);
+        st.members_src = vals;
+    } else if (V && P) {
+        st.last_path = 1;
+        if (st.prune_occ == 0) {
+            int per_sm = 0;
+            K8S_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, prune_kernel, 256, 0));
+            st.prune_occ = per_sm > 0 ? per_sm : -1;
+        }
+        if (st.prune_occ < 0) return fail(ctx, K8SGPU_E_CUDA, "cooperative pruning kernel cannot be resident");
+        uint32_t grid = (uint32_t)ctx->sm_count * (uint32_t)(st.prune_occ < 2 ? st.prune_occ : 2);
+        if (grid > ceil_div(V, 256u)) grid = ceil_div(V, 256u);
+        if (ctx->tune.rec_grid >= 1 && (uint32_t)ctx->tune.rec_grid <= (uint32_t)ctx->sm_count * (uint32_t)st.prune_occ)
+            grid = (uint32_t)ctx->tune.rec_grid;
+        // Segments: few enough that the two grid barriers per segment stay small beside the rows
+        // walked, many enough that the pass can stop early and that a pool overshoots its victim
+        // count by little; a CTA's share of a segment must fit the shared-memory mask.
+        uint32_t segs = V / (grid * 16384u);
+        segs = segs < 4u ? 4u : (segs > 32u ? 32u : segs);
+        if (ctx->tune.rec_segments >= 1) segs = (uint32_t)ctx->tune.rec_segments;
+        uint32_t rows_per_cta = ceil_div(ceil_div(V, segs), grid);
+        rows_per_cta = ceil_div(rows_per_cta, 256u) * 256u;
+        if (rows_per_cta > kPruneMaxRowsPerCta) {
+            rows_per_cta = kPruneMaxRowsPerCta;
+            segs = ceil_div(V, rows_per_cta * grid);  // V < 2^31, grid >= 1: fits
+        } else {
+            segs = ceil_div(V, rows_per_cta * grid);
+        }
+        K8S_CUDA(ctx, st.cta_cnt.reserve((size_t)grid * 4 + 16));
+        PruneArgs a;
+        a.pool_of = q.pool_of;
+        a.kvict = q.kvict;
+        a.remaining = q.remaining;
+        a.seen = q.seen;
+        a.cta_cnt = st.cta_cnt.as<uint32_t>();
+        a.cand_keys = keys;
+        a.cand_vals = vals;
+        a.counters = cnts;
+        a.V = V;
+        a.segments = segs;
+        a.rows_per_cta = rows_per_cta;
+        void *args[] = {&a};
+        K8S_CUDA(ctx, cudaLaunchCooperativeKernel((void *)prune_kernel, dim3(grid), dim3(256), args, 0, s));
+        ctx->stats.kernel_launches++;
+        K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned + 8, cnts + 3, 4, cudaMemcpyDeviceToHost, s));
+        K8S_CUDA(ctx, cudaStreamSynchronize(s));  // the sort's launch sizes depend on the candidate count
+        const uint32_t n_cand = ctx->h_pinned[8];
+        st.last_grid = grid;
+        st.last_segments = segs;
+        st.last_candidates = n_cand;
+        int rc = sort_pairs(ctx, s, keys, vals, n_cand, key_bits(P), st.sort);
+        if (rc) return rc;
+        rc = exclusive_scan_u32(ctx, s, q.seen, q.cand_off, P, st.scan_tmp, q.cand_off + P);
+        if (rc) return rc;
+        if (n_cand)
+            K8S_LAUNCH(ctx, victim_gather_kernel, ceil_div(n_cand, 256), 256, 0, s, keys, vals, n_cand, P, q.cand_off,
+                       q.kvict, q.victim_off, q.victim_vm);
+        st.members_src = nullptr;
+    } else {
+        st.last_path = full_sort ? 2 : 1;
+        st.members_src = vals;  // (no managed rows: nothing is read from it)
+    }
+    if (st.want_ordinals && P) {
+        int rc = exclusive_scan_u32(ctx, s, q.span_words, q.word_off, P, st.scan_tmp, nullptr);
+        if (rc) return rc;
+        K8S_CUDA(ctx, cudaMemsetAsync(st.bitmap.p, 0, (((size_t)V + st.create_cap) / 32 + P + 1) * 4, s));
+        if (st.has_ordinal && V)
+            K8S_LAUNCH(ctx, ordinal_mark_kernel, ceil_div(V, 256), 256, 0, s, q.pool_of, V, q.vm_ordinal, q.current,
+                       q.create_count, q.word_off, st.bitmap.as<uint32_t>());
+        K8S_LAUNCH(ctx, ordinal_emit_kernel, ceil_div(P, 8), 256, 0, s, P, q.current, q.create_count, q.word_off,
+                   st.bitmap.as<uint32_t>(), q.create_off, q.create_ordinal);
+    }
+    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_end, s));
+    // totals + error flag: one small copy each (this path is for large tables; latency is not the issue)
+    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, cnts, 4, cudaMemcpyDeviceToHost, s));
+    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned + 1, q.victim_off + P, 4, cudaMemcpyDeviceToHost, s));
+    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned + 2, q.member_off + P, 4, cudaMemcpyDeviceToHost, s));
+    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned + 3, q.create_off + P, 4, cudaMemcpyDeviceToHost, s));
+    K8S_CUDA(ctx, cudaStreamSynchronize(s));
+    int rc = rec_check_flags(ctx, ctx->h_pinned[0]);
+    if (rc) return rc;
+    st.n_victims = ctx->h_pinned[1];
+    st.n_members = ctx->h_pinned[2];
+    st.n_creates = ctx->h_pinned[3];
+    return K8SGPU_OK;
 }
 
 static int rec_run(k8sgpu_ctx *ctx, int want_members, int want_ordinals) {
     ReconcileState &st = ctx->rec;
     cudaStream_t s = ctx->stream;
     if (!st.uploaded) return fail(ctx, K8SGPU_E_ARG, "reconcile: no tables uploaded");
-    const uint32_t P = st.p, V = st.v;
     st.want_members = want_members != 0;
     st.want_ordinals = want_ordinals != 0;
-    uint32_t *cnts = st.counters.as<uint32_t>();
-    st.sorted_vals = st.sort_vals.as<uint32_t>();
-    // One cooperative launch for the whole pass while it is latency bound (config 2 is); the chain
-    // of kernels below once the tables are big enough to be bandwidth bound.  K8SGPU_REC_COOP=0/1
-    // forces either.
-    bool coop = V <= (4u << 20);
-    if (const char *e = getenv("K8SGPU_REC_COOP")) coop = atoi(e) != 0;
-    if (coop) return rec_run_coop(ctx, s);
-    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
-    K8S_CUDA(ctx, cudaMemsetAsync(cnts, 0, 64 * 4, s));
-    K8S_CUDA(ctx, cudaMemsetAsync(st.lut.p, 0xFF, ((size_t)st.n_owner_ids + 1) * 4, s));
-    if (P)
-        K8S_LAUNCH(ctx, pool_lut_kernel, ceil_div(P, 256), 256, 0, s, st.desired.as<int32_t>(),
-                   st.pool_owner.as<uint32_t>(), P, st.n_owner_ids, st.lut.as<int32_t>(), cnts);
-    uint32_t *keys = st.sort_keys.as<uint32_t>(), *vals = st.sort_vals.as<uint32_t>();
-    if (V) {
-        K8S_LAUNCH(ctx, match_kernel, ceil_div(ceil_div(V, 4), 256), 256, 0, s, st.vm_owner.as<uint32_t>(),
-                   st.vm_flags.as<uint32_t>(), V, st.n_owner_ids, st.lut.as<int32_t>(), P, st.pool_of.as<int32_t>(),
-                   keys, vals);
-        int rc = sort_pairs(ctx, s, keys, vals, V, key_bits(P), st.sort);
-        if (rc) return rc;
-    }
-    int32_t *member_off = st.member_off.as<int32_t>();
-    K8S_LAUNCH(ctx, segment_bounds_kernel, ceil_div(P + 1, 256), 256, 0, s, keys, V, P, member_off);
-    uint32_t *kvict = st.kvict.as<uint32_t>();
-    uint32_t *span_words = st.span_off.as<uint32_t>(), *word_off = span_words + P + 1;
-    int32_t *victim_off = st.victim_off.as<int32_t>(), *create_off = st.create_off.as<int32_t>();
-    if (P) {
-        K8S_LAUNCH(ctx, pool_kernel, ceil_div(P, 256), 256, 0, s, st.desired.as<int32_t>(), member_off, P,
-                   st.current.as<int32_t>(), st.delta.as<int32_t>(), st.create_count.as<int32_t>(), kvict, span_words);
-        int rc = exclusive_scan_u32(ctx, s, kvict, (uint32_t *)victim_off, P, st.scan_tmp, (uint32_t *)victim_off + P);
-        if (rc) return rc;
-        rc = exclusive_scan_u32(ctx, s, (const uint32_t *)st.create_count.p, (uint32_t *)create_off, P, st.scan_tmp,
-                                (uint32_t *)create_off + P);
-        if (rc) return rc;
-    } else {
-        K8S_CUDA(ctx, cudaMemsetAsync(victim_off, 0, 4, s));
-        K8S_CUDA(ctx, cudaMemsetAsync(create_off, 0, 4, s));
-    }
-    if (V && P)
-        K8S_LAUNCH(ctx, victim_gather_kernel, ceil_div(V, 256), 256, 0, s, keys, vals, V, P, member_off, kvict,
-                   victim_off, st.victim_vm.as<uint32_t>());
-    if (st.want_ordinals && P) {
-        int rc = exclusive_scan_u32(ctx, s, span_words, word_off, P, st.scan_tmp, cnts + 4);
-        if (rc) return rc;
-        K8S_CUDA(ctx, cudaMemsetAsync(st.bitmap.p, 0, st.bitmap.cap, s));
-        if (st.has_ordinal && V)
-            K8S_LAUNCH(ctx, ordinal_mark_kernel, ceil_div(V, 256), 256, 0, s, keys, vals, V, P,
-                       st.vm_ordinal.as<uint32_t>(), st.current.as<int32_t>(), st.create_count.as<int32_t>(),
-                       word_off, st.bitmap.as<uint32_t>());
-        K8S_LAUNCH(ctx, ordinal_emit_kernel, ceil_div(P, 8), 256, 0, s, P, st.current.as<int32_t>(),
-                   st.create_count.as<int32_t>(), word_off, st.bitmap.as<uint32_t>(), create_off,
-                   st.create_ordinal.as<uint32_t>());
-    }
-    return rec_finish(ctx, s);
+    st.ran = false;
+    // Few pools: one launch.  Many pools: the pruned ranking, or the full stable sort when the
+    // caller wants every pool's member list (Status.VMs).  k8sgpu_set_tuning("rec_path") forces one.
+    int path = st.p <= kSmallMaxPools ? 0 : (st.want_members ? 2 : 1);
+    if (ctx->tune.rec_path >= 0 && ctx->tune.rec_path <= 2) path = ctx->tune.rec_path;
+    if (path == 0 && st.p > kSmallMaxPools) path = st.want_members ? 2 : 1;
+    if (path == 1 && st.want_members) path = 2;
+    int rc = path == 0 ? rec_run_small(ctx, s) : rec_run_large(ctx, s, path == 2);
+    if (rc) return rc;
+    st.ran = true;
+    return K8SGPU_OK;
 }
 
-static int rec_finish(k8sgpu_ctx *ctx, cudaStream_t s) {
-    ReconcileState &st = ctx->rec;
-    const uint32_t P = st.p;
-    uint32_t *cnts = st.counters.as<uint32_t>();
-    int32_t *victim_off = st.victim_off.as<int32_t>(), *create_off = st.create_off.as<int32_t>();
-    int32_t *member_off = st.member_off.as<int32_t>();
-    K8S_CUDA(ctx, cudaEventRecord(ctx->ev_end, s));
-    // totals + error flag
-    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, cnts, 4, cudaMemcpyDeviceToHost, s));
-    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned + 1, victim_off + P, 4, cudaMemcpyDeviceToHost, s));
-    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned + 2, member_off + P, 4, cudaMemcpyDeviceToHost, s));
-    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned + 3, create_off + P, 4, cudaMemcpyDeviceToHost, s));
-    K8S_CUDA(ctx, cudaStreamSynchronize(s));
-    if (ctx->h_pinned[0] & kErrNegDesired) return fail(ctx, K8SGPU_E_ARG, "reconcile: negative desired replicas");
-    if (ctx->h_pinned[0] & kErrDupOwner) return fail(ctx, K8SGPU_E_ARG, "reconcile: two pools share an owner id");
-    st.n_victims = ctx->h_pinned[1];
-    st.n_members = ctx->h_pinned[2];
-    st.n_creates = ctx->h_pinned[3];
+// Fills stats.device_ms (needs the run's kernels to have finished).
+static int rec_time(k8sgpu_ctx *ctx) {
     float ms = 0.f;
+    K8S_CUDA(ctx, cudaEventSynchronize(ctx->ev_end));
     K8S_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
     ctx->stats.device_ms = ms;
-    st.ran = true;
     return K8SGPU_OK;
 }
 
@@ -612,39 +913,53 @@ static int rec_download(k8sgpu_ctx *ctx, k8sgpu_reconcile_out *out) {
     if ((V && !out->pool_of) || (P && (!out->current || !out->delta || !out->ready || !out->create_count)) ||
         !out->victim_off || (st.n_victims && !out->victim_vm))
         return fail(ctx, K8SGPU_E_ARG, "reconcile: NULL output column");
-    if (out->create_off && out->create_ordinal && st.want_ordinals && st.n_creates > out->create_capacity)
+    const bool members = out->member_off && out->member_vm && st.want_members;
+    const bool ordinals = out->create_off && out->create_ordinal && st.want_ordinals;
+    if (ordinals && st.n_creates > out->create_capacity)
         return fail(ctx, K8SGPU_E_CAPACITY, "reconcile: create_ordinal needs %u elements, caller gave %llu",
                     st.n_creates, (unsigned long long)out->create_capacity);
-    uint64_t bytes = 0;
-#define D2H(dst, src, n)                                                                         \
-    if ((n) > 0) {                                                                               \
-        K8S_CUDA(ctx, cudaMemcpyAsync((dst), (src), (size_t)(n)*4, cudaMemcpyDeviceToHost, s)); \
-        bytes += (uint64_t)(n)*4;                                                                \
-    }
-    D2H(out->pool_of, st.pool_of.p, V);
-    D2H(out->current, st.current.p, P);
-    D2H(out->ready, st.current.p, P);  // README.md:225: ReadyReplicas = currentCount
-    D2H(out->delta, st.delta.p, P);
-    D2H(out->create_count, st.create_count.p, P);
-    D2H(out->victim_off, st.victim_off.p, P + 1);
-    D2H(out->victim_vm, st.victim_vm.p, st.n_victims);
-    if (out->member_off && out->member_vm && st.want_members) {
-        D2H(out->member_off, st.member_off.p, P + 1);
-        D2H(out->member_vm, st.sorted_vals, st.n_members);
-    }
-    if (out->create_off && out->create_ordinal && st.want_ordinals) {
-        D2H(out->create_off, st.create_off.p, P + 1);
-        D2H(out->create_ordinal, st.create_ordinal.p, st.n_creates);
-    }
-#undef D2H
-    ctx->stats.d2h_bytes += bytes;
+    if (members && !st.members_src) return fail(ctx, K8SGPU_E_ARG, "reconcile: member lists were not produced by the last run");
+    const RecPtrs q = rec_ptrs(st);
+    CopyList cl;  // in the order of the device block: adjacent host buffers merge into one copy
+    cl.add(out->pool_of, q.pool_of, V * 4);
+    cl.add(out->current, q.current, P * 4);
+    cl.add(out->ready, q.ready, P * 4);  // README.md:225: ReadyReplicas = currentCount
+    cl.add(out->delta, q.delta, P * 4);
+    cl.add(out->create_count, q.create_count, P * 4);
+    cl.add(out->victim_off, q.victim_off, (P + 1) * 4);
+    if (members) cl.add(out->member_off, q.member_off, (P + 1) * 4);
+    if (ordinals) cl.add(out->create_off, q.create_off, (P + 1) * 4);
+    cl.add(out->victim_vm, q.victim_vm, (size_t)st.n_victims * 4);
+    if (members) cl.add(out->member_vm, st.members_src, (size_t)st.n_members * 4);
+    if (ordinals) cl.add(out->create_ordinal, q.create_ordinal, (size_t)st.n_creates * 4);
+    K8S_CUDA(ctx, cl.issue(cudaMemcpyDeviceToHost, s));
+    ctx->stats.d2h_bytes += cl.total;
     K8S_CUDA(ctx, cudaStreamSynchronize(s));
-    return K8SGPU_OK;
+    return rec_time(ctx);
 }
 
 }  // namespace k8sgpu
 
 using namespace k8sgpu;
+
+extern "C" int k8sgpu_reconcile_out_size(uint32_t p, uint32_t v, uint64_t create_capacity, k8sgpu_reconcile_layout *out) {
+    if (!out) return K8SGPU_E_ARG;
+    uint64_t off[12];
+    rec_out_layout(p, v, create_capacity, off);
+    out->pool_of = off[kOutPoolOf];
+    out->current = off[kOutCurrent];
+    out->ready = off[kOutReady];
+    out->delta = off[kOutDelta];
+    out->create_count = off[kOutCreateCount];
+    out->victim_off = off[kOutVictimOff];
+    out->member_off = off[kOutMemberOff];
+    out->create_off = off[kOutCreateOff];
+    out->victim_vm = off[kOutVictimVm];
+    out->member_vm = off[kOutMemberVm];
+    out->create_ordinal = off[kOutCreateOrdinal];
+    out->total = off[kOutTotal];
+    return K8SGPU_OK;
+}
 
 extern "C" int k8sgpu_reconcile_upload(k8sgpu_ctx *ctx, const k8sgpu_pool_table *pools, const k8sgpu_vm_table *vms,
                                        uint32_t n_owner_ids) {
@@ -652,14 +967,19 @@ extern "C" int k8sgpu_reconcile_upload(k8sgpu_ctx *ctx, const k8sgpu_pool_table 
     reset_call_stats(ctx);
     int rc = rec_upload(ctx, pools, vms, n_owner_ids);
     if (rc) return rc;
+    K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned, ctx->rec.counters.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
     K8S_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return K8SGPU_OK;
+    rc = rec_check_flags(ctx, ctx->h_pinned[0]);
+    if (rc) ctx->rec.uploaded = false;
+    return rc;
 }
 
 extern "C" int k8sgpu_reconcile_run(k8sgpu_ctx *ctx, int want_members, int want_ordinals) {
     K8S_ENTER(ctx);
     reset_call_stats(ctx);
-    return rec_run(ctx, want_members, want_ordinals);
+    int rc = rec_run(ctx, want_members, want_ordinals);
+    if (rc) return rc;
+    return rec_time(ctx);
 }
 
 extern "C" int k8sgpu_reconcile_download(k8sgpu_ctx *ctx, k8sgpu_reconcile_out *out) {

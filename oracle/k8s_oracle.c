@@ -74,14 +74,14 @@ typedef struct {
     const uint32_t *fg, *fc, *fm;
     const orc_pod_table *pods;
     const uint32_t *active;
-    uint32_t lo, hi, flags;
+    uint32_t n_active, flags, chunk;
     int32_t *best;
 } score_job;
 
-static void *score_worker(void *arg) {
-    score_job *j = (score_job *)arg;
+/* best[i] for active positions [lo, hi): every node, in ascending order, strict '>' */
+static void score_range(const score_job *j, uint32_t lo, uint32_t hi) {
     const uint32_t N = j->nodes->n;
-    for (uint32_t i = j->lo; i < j->hi; ++i) {
+    for (uint32_t i = lo; i < hi; ++i) {
         uint32_t p = j->active[i];
         uint32_t rot = orc_rot(p, N, j->flags);
         uint64_t bk = 0;
@@ -95,31 +95,89 @@ static void *score_worker(void *arg) {
         }
         j->best[i] = bn;
     }
+}
+
+/* A persistent pool of worker threads (created on first use, kept for the life of the process):
+ * a round hands out chunks of the active list through one shared counter, so a scoring pass costs
+ * two condition-variable hand-shakes instead of nthreads pthread_create/join pairs, and threads
+ * that draw cheap pods (early filter exits) simply take more chunks.  Which thread scores a pod
+ * cannot change best[i]: every entry is a function of the tables alone. */
+static struct {
+    pthread_mutex_t mu;
+    pthread_cond_t work, done;
+    pthread_t *tid;
+    int nworkers;      /* threads created so far                                  */
+    int want;          /* workers [0, want) take part in the current job          */
+    int pending;       /* workers that have not finished the current job yet      */
+    uint64_t gen;      /* job generation: bumped once per posted job              */
+    const score_job *job;
+    uint32_t next;     /* next unclaimed active position (atomic)                 */
+} g_pool = {PTHREAD_MUTEX_INITIALIZER, PTHREAD_COND_INITIALIZER, PTHREAD_COND_INITIALIZER, NULL, 0, 0, 0, 0, NULL, 0};
+
+static void pool_drain(const score_job *j) {
+    for (;;) {
+        uint32_t lo = __atomic_fetch_add(&g_pool.next, j->chunk, __ATOMIC_RELAXED);
+        if (lo >= j->n_active) return;
+        uint32_t hi = lo + j->chunk;
+        score_range(j, lo, hi < j->n_active ? hi : j->n_active);
+    }
+}
+
+static void *pool_worker(void *arg) {
+    const int me = (int)(intptr_t)arg;
+    uint64_t seen = 0;
+    pthread_mutex_lock(&g_pool.mu);
+    for (;;) {
+        while (g_pool.gen == seen) pthread_cond_wait(&g_pool.work, &g_pool.mu);
+        seen = g_pool.gen;
+        if (me >= g_pool.want) continue;  /* not part of this job */
+        const score_job *j = g_pool.job;
+        pthread_mutex_unlock(&g_pool.mu);
+        pool_drain(j);
+        pthread_mutex_lock(&g_pool.mu);
+        if (--g_pool.pending == 0) pthread_cond_signal(&g_pool.done);
+    }
     return NULL;
 }
 
 void orc_score_round(const orc_node_table *nodes, const uint32_t *free_gpu, const uint32_t *free_mcpu,
                      const uint32_t *free_mib, const orc_pod_table *pods, const uint32_t *active,
                      uint32_t n_active, uint32_t policy_flags, int nthreads, int32_t *best) {
+    score_job j;
+    j.nodes = nodes; j.fg = free_gpu; j.fc = free_mcpu; j.fm = free_mib;
+    j.pods = pods; j.active = active; j.n_active = n_active; j.flags = policy_flags; j.best = best;
     if (nthreads < 1) nthreads = 1;
     if ((uint32_t)nthreads > n_active) nthreads = n_active ? (int)n_active : 1;
-    score_job *jobs = (score_job *)calloc((size_t)nthreads, sizeof(score_job));
-    pthread_t *tid = (pthread_t *)calloc((size_t)nthreads, sizeof(pthread_t));
-    for (int t = 0; t < nthreads; ++t) {
-        score_job *j = &jobs[t];
-        j->nodes = nodes; j->fg = free_gpu; j->fc = free_mcpu; j->fm = free_mib;
-        j->pods = pods; j->active = active; j->flags = policy_flags; j->best = best;
-        j->lo = (uint32_t)((uint64_t)n_active * (uint64_t)t / (uint64_t)nthreads);
-        j->hi = (uint32_t)((uint64_t)n_active * (uint64_t)(t + 1) / (uint64_t)nthreads);
-    }
     if (nthreads == 1) {
-        score_worker(&jobs[0]);
-    } else {
-        for (int t = 0; t < nthreads; ++t) pthread_create(&tid[t], NULL, score_worker, &jobs[t]);
-        for (int t = 0; t < nthreads; ++t) pthread_join(tid[t], NULL);
+        score_range(&j, 0, n_active);
+        return;
     }
-    free(jobs);
-    free(tid);
+    /* ~16 chunks per thread, at most 256 pods each: fine enough to balance, coarse enough that the
+     * shared counter is touched once per ~10^6 evals at config-3 sizes */
+    uint32_t chunk = n_active / ((uint32_t)nthreads * 16u);
+    j.chunk = chunk < 1 ? 1 : (chunk > 256 ? 256 : chunk);
+    pthread_mutex_lock(&g_pool.mu);
+    const int helpers = nthreads - 1;  /* the calling thread works too */
+    if (g_pool.nworkers < helpers) {
+        g_pool.tid = (pthread_t *)realloc(g_pool.tid, (size_t)helpers * sizeof(pthread_t));
+        while (g_pool.nworkers < helpers) {
+            if (pthread_create(&g_pool.tid[g_pool.nworkers], NULL, pool_worker, (void *)(intptr_t)g_pool.nworkers) != 0)
+                break;  /* fewer threads than asked for: the job still completes */
+            pthread_detach(g_pool.tid[g_pool.nworkers]);
+            g_pool.nworkers++;
+        }
+    }
+    g_pool.want = helpers < g_pool.nworkers ? helpers : g_pool.nworkers;
+    g_pool.pending = g_pool.want;
+    g_pool.job = &j;
+    __atomic_store_n(&g_pool.next, 0u, __ATOMIC_RELAXED);
+    g_pool.gen++;
+    pthread_cond_broadcast(&g_pool.work);
+    pthread_mutex_unlock(&g_pool.mu);
+    pool_drain(&j);
+    pthread_mutex_lock(&g_pool.mu);
+    while (g_pool.pending > 0) pthread_cond_wait(&g_pool.done, &g_pool.mu);
+    pthread_mutex_unlock(&g_pool.mu);
 }
 
 /* prefix sums over ALL proposers of a node in global pod order. */

@@ -62,13 +62,12 @@ def case_place(rng, ctx):
     n, m = pick_size(rng, 3000), pick_size(rng, 12000)
     nodes, pods = random_nodes(rng, n), random_pods(rng, m)
     flags = int(rng.random() < 0.2)
-    env = dict(K8SGPU_RES=str(rng.integers(0, 5)), K8SGPU_PPT=str(rng.choice([1, 2, 4])),
-               K8SGPU_COOP=str(rng.integers(0, 2)))
+    env = dict(res=int(rng.integers(0, 5)), ppt=int(rng.choice([1, 2, 4])), coop=int(rng.integers(0, 2)))
     if rng.random() < 0.5:
-        env["K8SGPU_SPLITS"] = str(rng.integers(1, 9))
+        env["splits"] = int(rng.integers(1, 9))
     if rng.random() < 0.5:  # few CTAs in the single-launch admission: every CTA loops over several tiles
-        env["K8SGPU_COOP_GRID"] = str(rng.choice([1, 2, 3, 5, 17, 64]))
-    os.environ.update(env)
+        env["coop_grid"] = int(rng.choice([1, 2, 3, 5, 17, 64]))
+    ctx.set_tuning(**env)
     try:
         if rng.random() < 0.3:
             gang = rng.integers(0, max(m // 5, 1), m).astype(np.uint32)
@@ -84,16 +83,20 @@ def case_place(rng, ctx):
             ok = same(got, want, ("assign", "free_gpu", "free_mcpu", "free_mib"))
         ok = ok and (got["rounds"], got["evals"], got["placed"]) == (want["rounds"], want["evals"], want["placed"])
     finally:
-        for k in ("K8SGPU_RES", "K8SGPU_PPT", "K8SGPU_COOP", "K8SGPU_SPLITS", "K8SGPU_COOP_GRID"):
-            os.environ.pop(k, None)
-    return ok, f"place n={n} m={m} flags={flags} env={env}"
+        ctx.reset_tuning()
+    return ok, f"place n={n} m={m} flags={flags} tuning={env}"
 
 
 def case_reconcile(rng, ctx):
     P, V = pick_size(rng, 4000), pick_size(rng, 150_000)
-    os.environ["K8SGPU_REC_COOP"] = str(rng.integers(0, 2))
+    # path 0 = one launch (few pools), 1 = pruned ranking (victims only), 2 = full stable sort
+    members = bool(rng.random() < 0.6)
+    env = dict(rec_path=int(rng.integers(0, 3)))
     if rng.random() < 0.5:
-        os.environ["K8SGPU_REC_GRID"] = str(rng.choice([1, 2, 3, 5, 17, 64]))
+        env["rec_grid"] = int(rng.choice([1, 2, 3, 5, 17, 64]))
+    if rng.random() < 0.5:
+        env["rec_segments"] = int(rng.choice([1, 2, 3, 7, 40]))
+    ctx.set_tuning(**env)
     try:
         n_ids = P + int(rng.integers(0, 50))
         powner = rng.permutation(n_ids)[:P].astype(np.uint32)
@@ -107,12 +110,11 @@ def case_reconcile(rng, ctx):
         ords[rng.random(V) < 0.1] = NONE
         desired = rng.integers(0, max(2 * V // max(P, 1), 3), P).astype(np.int32)
         args = (desired, powner, vowner, vflags, n_ids, ords if rng.random() < 0.8 else None)
-        got, want = ctx.reconcile_batch(*args), orc.reconcile_batch(*args, nthreads=NCPU)
-        ok = all(np.array_equal(got[k], want[k]) for k in want)
+        got, want = ctx.reconcile_batch(*args, members=members), orc.reconcile_batch(*args, nthreads=NCPU)
+        ok = all(np.array_equal(got[k], want[k]) for k in want if members or not k.startswith("member_"))
     finally:
-        os.environ.pop("K8SGPU_REC_COOP", None)
-        os.environ.pop("K8SGPU_REC_GRID", None)
-    return ok, f"reconcile P={P} V={V}"
+        ctx.reset_tuning()
+    return ok, f"reconcile P={P} V={V} members={members} tuning={env}"
 
 
 def main():

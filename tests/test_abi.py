@@ -34,7 +34,7 @@ def test_library_exports_every_declared_symbol(capi):
     lib = ctypes.CDLL(capi.LIB_PATH)
     for name in declared_symbols():
         assert hasattr(lib, name), name
-    assert lib.k8sgpu_abi_version() == 1
+    assert lib.k8sgpu_abi_version() == 2
 
 
 def test_struct_layouts_match_header(capi):

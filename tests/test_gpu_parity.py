@@ -29,6 +29,14 @@ def ctx():
     c.close()
 
 
+@pytest.fixture(autouse=True)
+def _default_tuning(request):
+    """Kernel-variant knobs set by a test (ctx.set_tuning) never leak into the next one."""
+    yield
+    if "ctx" in request.fixturenames:
+        request.getfixturevalue("ctx").reset_tuning()
+
+
 @pytest.fixture(scope="module")
 def capi():
     import k8sgpu_b200  # noqa: F401
@@ -71,12 +79,12 @@ def test_sort_pairs_is_stable(ctx, n, bits):
                                             ("2", "7", "2"), ("4", "2", "4"), ("4", "1", "4"), ("1", "2", "0"),
                                             ("2", "3", "1"), ("1", "5", "3")])
 @pytest.mark.parametrize("flags", [0, 1])
-def test_score_once_matches_oracle(ctx, orc, synth, ppt, splits, res, flags, monkeypatch):
+def test_score_once_matches_oracle(ctx, orc, synth, ppt, splits, res, flags):
     """Every kernel variant (pods per thread, node splits, eval_pair RES 0-4) is bit-identical."""
     if ppt:
-        monkeypatch.setenv("K8SGPU_PPT", ppt)
-        monkeypatch.setenv("K8SGPU_SPLITS", splits)
-        monkeypatch.setenv("K8SGPU_RES", res)
+        ctx.set_tuning(ppt=int(ppt))
+        ctx.set_tuning(splits=int(splits))
+        ctx.set_tuning(res=int(res))
     nodes, pods = synth.gen_nodes(1500, config_id=5), synth.gen_pods(3333, config_id=5)
     ctx.place_upload(nodes, pods)
     got = ctx.score_once(flags)
@@ -97,10 +105,10 @@ def test_score_once_identical_ties(ctx, orc, synth):
 
 @pytest.mark.parametrize("n", [1, 7, 8, 9, 255, 256, 257, 511, 513, 1031])
 @pytest.mark.parametrize("splits", [None, "1", "5"])
-def test_rotation_tiebreak_at_chunk_and_tile_edges(ctx, orc, synth, n, splits, monkeypatch):
+def test_rotation_tiebreak_at_chunk_and_tile_edges(ctx, orc, synth, n, splits):
     # identical nodes: only rot(p) decides, and rot(p) lands on every chunk/tile boundary case
     if splits:
-        monkeypatch.setenv("K8SGPU_SPLITS", splits)
+        ctx.set_tuning(splits=int(splits))
     nodes, pods = synth.gen_identical(n, 700)
     ctx.place_upload(nodes, pods)
     free = (nodes["free_gpu"], nodes["free_mcpu"], nodes["free_mib"])
@@ -170,22 +178,22 @@ def test_place_long_active_list(ctx, orc, synth, n, m):
 
 
 @pytest.mark.parametrize("grid", ["1", "3", "7"])
-def test_place_few_ctas_many_tiles(ctx, orc, synth, grid, monkeypatch):
+def test_place_few_ctas_many_tiles(ctx, orc, synth, grid):
     """30 sort tiles / 240 segment blocks handled by 1, 3 or 7 CTAs: every per-CTA loop of the
     single-launch admission runs many iterations (shared scratch is reused across them)."""
-    monkeypatch.setenv("K8SGPU_COOP_GRID", grid)
+    ctx.set_tuning(coop_grid=int(grid))
     nodes, pods = synth.gen_nodes(500, config_id=5), synth.gen_pods(60_000, config_id=5)
     same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
 
 
 @pytest.mark.parametrize("grid", [None, "1", "3", "40"])
 @pytest.mark.parametrize("name", ["c3_small", "ties_rot_zero", "c5_all_h100"])
-def test_place_single_launch_admission(ctx, name, grid, monkeypatch):
+def test_place_single_launch_admission(ctx, name, grid):
     """K8SGPU_COOP=1: the cooperative one-launch admission path gives the golden result too --
     also with so few CTAs that each one loops over several tiles in every phase."""
-    monkeypatch.setenv("K8SGPU_COOP", "1")
+    ctx.set_tuning(coop=int("1"))
     if grid:
-        monkeypatch.setenv("K8SGPU_COOP_GRID", grid)
+        ctx.set_tuning(coop_grid=int(grid))
     nodes, pods, flags = mg.place_inputs(name)
     g = np.load(os.path.join(HERE, "golden", f"place_{name}.npz"))
     got = ctx.place(nodes, pods, flags=flags)
@@ -362,9 +370,9 @@ def same_reconcile(got, want):
 
 @pytest.mark.parametrize("grid", [None, "1", "3"])
 @pytest.mark.parametrize("name", list(mg.RECONCILE_CASES))
-def test_reconcile_matches_golden(ctx, synth, name, grid, monkeypatch):
+def test_reconcile_matches_golden(ctx, synth, name, grid):
     if grid:  # few CTAs in the one-launch pass: every CTA loops over several tiles
-        monkeypatch.setenv("K8SGPU_REC_GRID", grid)
+        ctx.set_tuning(rec_grid=int(grid))
     c = mg.RECONCILE_CASES[name]
     t = synth.gen_reconcile(c["p"], c["v"], c["config_id"])
     got = ctx.reconcile_batch(t["desired"], t["pool_owner_id"], t["vm_owner_id"], t["vm_flags"], t["n_owner_ids"],
@@ -374,12 +382,69 @@ def test_reconcile_matches_golden(ctx, synth, name, grid, monkeypatch):
         assert np.array_equal(got[k], g[k]), k
 
 
-@pytest.mark.parametrize("p,v", [(1000, 100_000), (1, 1000), (7, 3), (5000, 1_000_003), (40_000, 400_000)])
+@pytest.mark.parametrize("p,v", [(1000, 100_000), (1, 1000), (7, 3), (5000, 1_000_003), (6144, 70_000),
+                                 (6145, 70_000), (40_000, 400_000)])
 def test_reconcile_matches_oracle(ctx, orc, synth, p, v):
-    # (1000, 100000) is BASELINE.json config 2 at full size
+    # (1000, 100000) is BASELINE.json config 2 at full size; 6144 / 6145 pools straddle the limit of
+    # the one-launch path (automatic path selection on both sides of it)
     t = synth.gen_reconcile(p, v)
     args = (t["desired"], t["pool_owner_id"], t["vm_owner_id"], t["vm_flags"], t["n_owner_ids"], t["vm_ordinal"])
     same_reconcile(ctx.reconcile_batch(*args), orc.reconcile_batch(*args, nthreads=NCPU))
+
+
+@pytest.mark.parametrize("path,members", [(0, True), (0, False), (1, False), (2, True), (2, False)])
+@pytest.mark.parametrize("p,v,segments,grid", [(1000, 100_000, None, None), (300, 77_777, 3, 5), (3000, 250_001, 9, 17),
+                                               (17, 4097, 1, 1), (2, 100_000, 40, 64), (5000, 300, None, None)])
+def test_reconcile_every_path(ctx, orc, synth, path, members, p, v, segments, grid):
+    """The three ways of ranking rows inside their pool -- one cooperative launch, pruned candidate
+    sort, full stable sort -- give the oracle's bytes, with and without member lists, with few and
+    many CTAs / row segments (every per-CTA loop runs several tiles; early exit of the pruning pass)."""
+    t = synth.gen_reconcile(p, v)
+    args = (t["desired"], t["pool_owner_id"], t["vm_owner_id"], t["vm_flags"], t["n_owner_ids"], t["vm_ordinal"])
+    ctx.set_tuning(rec_path=path, rec_segments=segments, rec_grid=grid)
+    got, want = ctx.reconcile_batch(*args, members=members), orc.reconcile_batch(*args, nthreads=NCPU)
+    for k in want:
+        if members or not k.startswith("member_"):
+            assert np.array_equal(got[k], want[k]), k
+
+
+@pytest.mark.parametrize("path", [0, 1, 2])
+def test_reconcile_scale_to_zero_and_one_giant_pool(ctx, orc, path):
+    """K11 in batch form: desired 0 everywhere (every managed row is a victim, in list order), and
+    one pool that owns nearly every row (the longest possible rank chain)."""
+    rng = np.random.default_rng(11)
+    V, P = 120_000, 40
+    vowner = rng.integers(0, P + 5, V).astype(np.uint32)
+    vflags = (rng.random(V) < 0.95).astype(np.uint32)
+    ctx.set_tuning(rec_path=path, rec_segments=5)
+    for desired, owner in ((np.zeros(P, np.int32), vowner), (np.full(P, 3, np.int32), np.where(rng.random(V) < 0.97, 7, vowner).astype(np.uint32))):
+        args = (desired, np.arange(P, dtype=np.uint32), owner, vflags, P + 5, None)
+        got, want = ctx.reconcile_batch(*args, members=path != 1), orc.reconcile_batch(*args, nthreads=NCPU)
+        for k in want:
+            if path != 1 or not k.startswith("member_"):
+                assert np.array_equal(got[k], want[k]), k
+
+
+def test_reconcile_single_block_outputs(ctx, capi, orc, synth):
+    """Outputs laid out in one caller block as k8sgpu_reconcile_out_size says (the layout the
+    library keeps in HBM, so the copies merge): same bytes as separately allocated arrays."""
+    t = synth.gen_reconcile(1000, 100_000)
+    args = (t["desired"], t["pool_owner_id"], t["vm_owner_id"], t["vm_flags"], t["n_owner_ids"], t["vm_ordinal"])
+    P, V, cap = 1000, 100_000, int(t["desired"].sum()) + 1
+    lay = capi.reconcile_out_size(P, V, cap)
+    assert lay["pool_of"] == 0 and lay["current"] == V and lay["total"] == 3 * V + 7 * P + 3 + cap
+    block = np.full(lay["total"], 0xDEADBEEF, np.uint32)
+    sizes = {"pool_of": V, "current": P, "ready": P, "delta": P, "create_count": P, "victim_off": P + 1,
+             "member_off": P + 1, "create_off": P + 1, "victim_vm": V, "member_vm": V, "create_ordinal": cap}
+    order = iter(["pool_of", "current", "delta", "ready", "create_count", "victim_off", "victim_vm", "member_off",
+                  "member_vm", "create_off", "create_ordinal"])  # the order Context._rec_out asks for buffers in
+
+    def alloc(n, dt):
+        k = next(order)
+        return block[lay[k]: lay[k] + sizes[k]].view(dt)
+
+    got = ctx.reconcile_batch(*args, alloc=alloc, create_capacity=cap - 1)
+    same_reconcile(got, orc.reconcile_batch(*args, nthreads=NCPU))
 
 
 def test_reconcile_hand_vector_and_config1(ctx):
@@ -407,6 +472,11 @@ def test_reconcile_errors_and_empty(ctx, capi):
     assert e.value.code == capi.E_ARG
     with pytest.raises(capi.K8sGpuError):
         ctx.reconcile_batch([-1], [0], [0], [1], 8)
+    with pytest.raises(capi.K8sGpuError) as e:  # far outside any buffer if it were ever used as a count
+        ctx.reconcile_batch([-1_000_000, 0, -(2 ** 31)], [0, 1, 2], [1] * 10, [1] * 10, 8, list(range(10)))
+    assert e.value.code == capi.E_ARG and "negative" in str(e.value)
+    ok = ctx.reconcile_batch([0, 12], [0, 1], [1] * 10, [1] * 10, 8, list(range(10)))  # the context still works
+    assert ok["delta"].tolist() == [0, 2] and ok["create_ordinal"].tolist() == [10, 11]
     out = ctx.reconcile_batch([2, 0], [0, 1], [], [], 4)
     assert out["delta"].tolist() == [2, 0] and out["victim_off"].tolist() == [0, 0, 0]
     assert out["create_ordinal"].tolist() == [0, 1]
