@@ -121,6 +121,13 @@ def gen_workload(name):
     return synth.gen_nodes(w["n"], w["config_id"]), synth.gen_pods(w["m"], w["config_id"])
 
 
+# The CPU arm times a BOUNDED SAMPLE of the workload: every round of the first `frac` of the pods
+# against the whole node table.  One rule for both the --impl reference arm and the in-line
+# cpu_baseline (so that one config has one CPU number), sized for >= ~2 s of work on 32 host
+# threads, so that handing the chunks to the oracle's thread pool is noise.
+CPU_SAMPLE_FRAC = {"c3": 0.5, "c4": 0.02, "c5": 0.05, "tiny": 1.0}
+
+
 def cpu_port(nodes, pods, frac, threads):
     """The CPU oracle (a port: the reference has no runnable code) on the first `frac` of the pods,
     every round, all host threads.  Returns (evals_per_s, evals, seconds, sample text)."""
@@ -143,10 +150,9 @@ def reference_arm(args, rank, world):
     wl = args.workload or ("c3" if args.gpus == 1 else "c4")
     nodes, pods = gen_workload(wl)
     threads = os.cpu_count() or 1
-    # size the per-step sample so that steps+warmup end within a few minutes
-    frac = {"c3": 0.10, "c4": 0.0004, "c5": 0.004, "tiny": 1.0}[wl]
-    for _ in range(args.warmup):
-        cpu_port(nodes, pods, frac / 4, threads)
+    frac = CPU_SAMPLE_FRAC[wl]
+    for _ in range(min(args.warmup, 2)):  # the thread pool exists and the tables are in cache after one
+        cpu_port(nodes, pods, frac, threads)
     ev, secs, sample = 0, 0.0, ""
     for _ in range(args.steps):
         _, e, dt, sample = cpu_port(nodes, pods, frac, threads)
@@ -160,11 +166,51 @@ def reference_arm(args, rank, world):
         "data": "synthetic",
         "config": {"workload": WORKLOADS[wl]["desc"], "nodes": WORKLOADS[wl]["n"], "pods": WORKLOADS[wl]["m"],
                    "note": "reference is Markdown only; CPU oracle port timed on host cores"},
-        "cpu_baseline": {"value": v, "unit": "evals/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "evals/s", "cores": threads, "kind": "port", "sample": sample,
+                         "sample_frac": frac, "seconds_per_step": secs / args.steps},
         "e2e": {"value": v, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def pinned_block(torch, n_elems):
+    return torch.empty(max(int(n_elems), 1), dtype=torch.int32).pin_memory().numpy().view(np.uint32)
+
+
+def slab(torch, cols, order):
+    """One pinned block with the columns back to back (the layout the device keeps): the library
+    then moves a table with one copy instead of eight."""
+    n = len(cols[order[0]])
+    blk = pinned_block(torch, len(order) * n)
+    out = {}
+    for c, k in enumerate(order):
+        out[k] = blk[c * n:(c + 1) * n]
+        out[k][:] = cols[k]
+    return out
+
+
+def time_resident(ctx, steps, flush, barrier, dist, torch):
+    """`steps` whole placements from tables resident in HBM; device time per step (CUDA events
+    recorded by the library on the stream its kernels run on), max over ranks."""
+    tot = dict(ms=0.0, evals=0, score_ms=0.0, score_evals=0, score_launches=0, launches=0)
+    st = None
+    for _ in range(steps):
+        flush.zero_()  # evict the tables from L2 between timed steps (untimed)
+        barrier()
+        st = ctx.place_run()
+        ms = st["device_ms"]
+        if dist is not None:  # max over ranks, measured on the device
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        tot["ms"] += ms
+        tot["evals"] += st["evals"]
+        tot["score_ms"] += st["score_ms"]
+        tot["score_evals"] += st["score_evals"]
+        tot["score_launches"] += st["score_launches"]
+        tot["launches"] += st["kernel_launches"]
+    return tot, st
 
 
 def main():
@@ -177,6 +223,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-reconcile", action="store_true")
     ap.add_argument("--no-scaling-base", action="store_true")
+    ap.add_argument("--exchange", default=None, choices=["allgather", "peer"],
+                    help="N>1: how a round's proposals travel (default: NCCL all-gather)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -194,21 +242,28 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: there is no CPU path for --impl ours")
     import k8sgpu_b200  # noqa: F401
-    from k8sgpu_b200 import capi, placement
+    from k8sgpu_b200 import capi
+    from k8sgpu_b200.digest import place_digest
 
     torch.cuda.set_device(local_rank)
     dist = None
+    ctx = capi.Context(local_rank)
     if world > 1:
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # torch.distributed is the plumbing (id broadcast, barriers, max over ranks); the placement's
+        # own collectives run on the library's NCCL communicator, inside k8sgpu_place_run.
+        box = [capi.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        ctx.comm_init_rank(rank, world, box[0])
+        if args.exchange:
+            ctx.set_tuning(exchange=1 if args.exchange == "peer" else 0)
     wl = args.workload or ("c3" if world == 1 else "c4")
     nodes, pods = gen_workload(wl)
     N, M = len(nodes["flags"]), len(pods["req_gpu"])
 
-    ctx = capi.Context(local_rank)
-    placer = placement.ShardedPlacer(ctx, dist, rank, world)
-    placer.upload(nodes, pods)
+    ctx.place_upload(nodes, pods)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     def barrier():
@@ -217,152 +272,130 @@ def main():
         torch.cuda.synchronize()
 
     for _ in range(args.warmup):
-        placer.run()
+        ctx.place_run()
     sampler = ClockSampler(local_rank, period=0.01).start() if rank == 0 else None
-    tot_ms = tot_score_ms = 0.0
-    tot_evals = tot_score_evals = launches = score_launches = 0
     barrier()
     wall0 = time.perf_counter()
-    for _ in range(args.steps):
-        flush.zero_()  # evict the tables from L2 between timed steps (untimed)
-        barrier()
-        st = placer.run()
-        ms = st["step_ms"]  # CUDA events on the stream the kernels run on
-        if dist is not None:  # max over ranks, measured on the device
-            t = torch.tensor([ms], device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        tot_ms += ms
-        tot_evals += st["evals"]
-        tot_score_ms += st["score_ms"]
-        tot_score_evals += st["score_evals"]
-        score_launches += st["score_launches"]
-        launches += st["kernel_launches"]
+    tot, st = time_resident(ctx, args.steps, flush, barrier, dist, torch)
     barrier()
     wall = time.perf_counter() - wall0
     clocks = sampler.stop() if sampler else None
-    rounds = st["rounds"]
-    placed = st["placed"]
+    rounds, placed = st["rounds"], st["placed"]
+    result = ctx.place_download()  # untimed: what was computed, as a digest (equal at every N)
+    sha = place_digest(result)
 
-    # end to end through the drop-in call: pinned host tables -> H2D -> rounds -> D2H of results
-    e2e = None
-    if world == 1:
-        def slab(cols, order, dtype=np.uint32):
-            """One pinned block with the columns back to back (the layout the device keeps): the library
-            then moves a table with one copy instead of eight."""
-            n = len(cols[order[0]])
-            blk = torch.empty(len(order) * max(n, 1), dtype=torch.int32).pin_memory().numpy().view(dtype)
-            out = {}
-            for c, k in enumerate(order):
-                out[k] = blk[c * n:(c + 1) * n]
-                out[k][:] = cols[k]
-            return out
+    # end to end through the drop-in call: pinned host tables -> H2D -> rounds -> D2H of results,
+    # one k8sgpu_place per step (collective across the ranks at N > 1)
+    hn = slab(torch, nodes, ("free_gpu", "free_mcpu", "free_mib", "cap_gpu", "sku_id", "zone_id", "taint_mask", "flags"))
+    hp = slab(torch, pods, ("req_gpu", "req_mcpu", "req_mib", "sku_mask", "zone_mask", "tol_mask", "pref_zone", "priority"))
+    ho = slab(torch, {k: np.zeros(N, np.uint32) for k in ("free_gpu", "free_mcpu", "free_mib")},
+              ("free_gpu", "free_mcpu", "free_mib"))
+    ho["assign"] = pinned_block(torch, M).view(np.int32)[:M]
+    ctx.place(hn, hp, out=ho)
+    barrier()
+    t0 = time.perf_counter()
+    e_evals = 0
+    for _ in range(args.steps):
+        r = ctx.place(hn, hp, out=ho)
+        e_evals += r["evals"]
+    e_dt = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([e_dt], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e_dt = float(t.item())
+    e2e = {"value": e_evals / e_dt, "unit": "evals/s", "h2d_bytes_per_step": int(r["h2d_bytes"]) * world,
+           "d2h_bytes_per_step": int(r["d2h_bytes"]) * world, "ms_per_step": 1e3 * e_dt / args.steps,
+           "result_sha256": place_digest(ho)}
+    if world > 1:
+        e2e["note"] = "every rank uploads the replicated tables and downloads the full result"
+    launches_e2e = int(r["kernel_launches"])
 
-        hn = slab(nodes, ("free_gpu", "free_mcpu", "free_mib", "cap_gpu", "sku_id", "zone_id", "taint_mask", "flags"))
-        hp = slab(pods, ("req_gpu", "req_mcpu", "req_mib", "sku_mask", "zone_mask", "tol_mask", "pref_zone", "priority"))
-        n_, m_ = len(nodes["flags"]), len(pods["req_gpu"])
-        ho = slab({k: np.zeros(n_, np.uint32) for k in ("free_gpu", "free_mcpu", "free_mib")},
-                  ("free_gpu", "free_mcpu", "free_mib"))
-        ho["assign"] = torch.empty(max(m_, 1), dtype=torch.int32).pin_memory().numpy()[:m_]
-        ctx.place(hn, hp, out=ho)
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        e_evals = 0
-        for _ in range(args.steps):
-            r = ctx.place(hn, hp, out=ho)
-            e_evals += r["evals"]
-        e_dt = time.perf_counter() - t0
-        e2e = {"value": e_evals / e_dt, "unit": "evals/s", "h2d_bytes_per_step": int(r["h2d_bytes"]),
-               "d2h_bytes_per_step": int(r["d2h_bytes"]), "ms_per_step": 1e3 * e_dt / args.steps}
-        launches_e2e = int(r["kernel_launches"])
-    else:
-        pin = lambda d: {k: torch.from_numpy(v).pin_memory().numpy() for k, v in d.items()}
-        hn, hp = pin(nodes), pin(pods)
-        placer.upload(hn, hp)
-        placer.run()
+    # N > 1 runs config 4; the like-for-like base of its scaling efficiency is config 4 on ONE GPU:
+    # rank 0 times it on its own GPU after the sharded run (the other ranks wait at the barrier).
+    same_base = None
+    if world > 1 and not args.no_scaling_base:
+        if rank == 0:
+            with capi.Context(local_rank) as solo:
+                solo.place_upload(nodes, pods)
+                solo.place_run()
+                b_tot, b_st = time_resident(solo, max(args.steps, 5), flush, torch.cuda.synchronize, None, torch)
+                same_base = {"workload": WORKLOADS[wl]["desc"], "n_gpus": 1, "value": b_tot["evals"] / (b_tot["ms"] * 1e-3),
+                             "unit": "evals/s", "ms_per_step": b_tot["ms"] / max(args.steps, 5), "steps": max(args.steps, 5),
+                             "rounds": b_st["rounds"], "result_sha256": place_digest(solo.place_download())}
         barrier()
-        t0 = time.perf_counter()
-        e_evals = 0
-        for _ in range(args.steps):
-            placer.upload(hn, hp)
-            h2d = ctx.stats()["h2d_bytes"]
-            r = placer.run()
-            placer.download()
-            d2h = ctx.stats()["d2h_bytes"]
-            e_evals += r["evals"]
-        barrier()
-        e_dt = torch.tensor([time.perf_counter() - t0], device="cuda")
-        dist.all_reduce(e_dt, op=dist.ReduceOp.MAX)
-        e_dt = float(e_dt.item())
-        e2e = {"value": e_evals / e_dt, "unit": "evals/s", "h2d_bytes_per_step": int(h2d) * world,
-               "d2h_bytes_per_step": int(d2h) * world, "ms_per_step": 1e3 * e_dt / args.steps,
-               "note": "every rank uploads the replicated tables and downloads the full result"}
-        launches_e2e = None
 
     if rank != 0:
+        ctx.close()
         if dist is not None:
             dist.destroy_process_group()
         return
 
     peak, peak_src = peaks()
-    achieved = tot_score_evals * NODE_REC_BYTES / (tot_score_ms * 1e-3) / 1e9 if tot_score_ms > 0 else 0.0
+    tot_ms, tot_evals, tot_score_ms, tot_score_evals = tot["ms"], tot["evals"], tot["score_ms"], tot["score_evals"]
+    score_launches, launches = tot["score_launches"], tot["launches"]
+    contract_gbs = tot_score_evals * NODE_REC_BYTES / (tot_score_ms * 1e-3) / 1e9 if tot_score_ms > 0 else 0.0
     traffic = ncu_traffic()
+    ipe = float((traffic or {}).get("warp_instructions_per_warp_eval", 15.67))  # ncu: inst_executed / warp-evals
     if traffic and traffic.get("workload", "c3") != wl:
         traffic = None  # the committed ncu capture is of another workload's launch
-    # second roofline, the one that actually binds: INT ALU pipe, 16 lanes/clk/SMSP on 592 SMSPs
-    # SASS of score_kernel<2,4> (the default): 4 LOP3 + SHF + 2 ISETP per eval on the ALU pipe; 6 IMAD on
-    # the FMA pipe and one LDS.128 (two pods share each node record) -- 14 issue slots per eval, so the
-    # issue rate (32 lanes/clk/SMSP / 14) gives the same ceiling as the ALU pipe (16 lanes/clk/SMSP / 7).
-    alu_ops_per_eval = 7
+    # What binds the scoring kernel is instruction issue (one warp instruction per clock per SM
+    # sub-partition, 592 of them), not HBM: node records are re-used from shared memory by every
+    # pod of a CTA.  Ceiling = issue rate / the instructions ncu counted per pod-node eval.
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965
-    alu_peak = 148 * 4 * 16 * sm_mhz * 1e6 / alu_ops_per_eval  # evals/s if the ALU pipe never idled
-    alu_achieved = tot_score_evals / (tot_score_ms * 1e-3) if tot_score_ms > 0 else 0.0
+    issue_peak = 148 * 4 * 32 * sm_mhz * 1e6 / ipe
+    score_rate = tot_score_evals / (tot_score_ms * 1e-3) if tot_score_ms > 0 else 0.0
     line = {
         "metric": "pod_node_score_evals_per_sec", "value": tot_evals / (tot_ms * 1e-3), "unit": "evals/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None,  # total work per workload is fixed
         "dtype": "u32", "data": "synthetic",
         "config": {"workload": WORKLOADS[wl]["desc"], "nodes": N, "pods": M, "rounds": rounds, "placed": placed,
-                   "evals_per_step": tot_evals // args.steps, "parallelism": f"pods sharded x{world}, nodes replicated", "exchange": placer.exchange,
-                   "l2": "flushed between timed steps (256 MB write)", "wall_s_timed_region": wall},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic["dram_bytes_per_launch"] if traffic else None, "peak_source": peak_src,
-                     "kernel": "score_kernel", "algorithmic_bytes_per_eval": NODE_REC_BYTES,
+                   "evals_per_step": tot_evals // args.steps, "result_sha256": sha,
+                   "parallelism": f"pods sharded x{world}, nodes replicated",
+                   "exchange": "none" if world == 1 else ("peer stores + 1-word ncclAllReduce" if args.exchange == "peer"
+                                                          else "ncclAllGather of the proposals, in the library"),
+                   "l2": "flushed between timed steps (256 MB write)", "wall_s_timed_region": wall,
+                   "launches_per_e2e_step": launches_e2e},
+        "roofline": {"bound": "instruction issue (INT32), not hbm: see roofline_contract", "achieved": score_rate,
+                     "peak": issue_peak, "unit": "evals/s", "frac": score_rate / issue_peak,
+                     "traffic": traffic["dram_bytes_per_launch"] if traffic else None,
+                     "kernel": "score_kernel", "instructions_per_eval": ipe,
+                     "peak_source": "592 SM sub-partitions x 32 lanes x SM clock under load / warp instructions per "
+                                    "warp-eval measured by ncu (profiles/score_kernel_traffic.json)",
                      "evals_per_launch": tot_score_evals // max(score_launches, 1),
                      "avg_launch_ms": tot_score_ms / max(score_launches, 1),
-                     "share_of_step": tot_score_ms / tot_ms if tot_ms else None,
-                     "note": "node records are re-read from shared memory/L2, not DRAM: frac > 1 is on-chip reuse "
-                             "(DESIGN.md 'roofline')"},
-        "roofline_alu": {"bound": "int32 ALU pipe", "achieved": alu_achieved, "peak": alu_peak, "unit": "evals/s",
-                         "frac": alu_achieved / alu_peak, "alu_ops_per_eval": alu_ops_per_eval,
-                         "issue_slots_per_eval": 14,
-                         "note": "peak = 592 SMSPs x 16 lanes/clk x sm clock / ALU instructions per eval "
-                                 "(= the issue-slot ceiling, 32 lanes/clk / 14 instructions)"},
+                     "share_of_step": tot_score_ms / tot_ms if tot_ms else None},
+        "roofline_contract": {"bound": "hbm", "achieved": contract_gbs, "peak": peak, "unit": "GB/s",
+                              "ratio": contract_gbs / peak, "algorithmic_bytes_per_eval": NODE_REC_BYTES,
+                              "peak_source": peak_src,
+                              "note": "SURVEY 8(d) contract figure: 32 B (one node record) per eval against the HBM copy "
+                                      "peak.  The records come from shared memory / L2, not DRAM (compare `traffic`), "
+                                      "so this ratio exceeds 1 and is NOT a roofline fraction"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
-    if launches_e2e is not None:
-        line["config"]["launches_per_e2e_step"] = launches_e2e
+    if same_base is not None:
+        eff = line["value"] / (world * same_base["value"])
+        e_eff = e2e["value"] / (world * same_base["value"])
+        line["scaling_base"] = dict(same_base, same_workload_efficiency=eff, same_workload_efficiency_e2e=e_eff,
+                                    digest_equal=same_base["result_sha256"] == sha)
     if world == 1 and wl == "c3" and not args.no_scaling_base:
         # N>1 runs config 4 (BASELINE.json), so the like-for-like 1-GPU base of the scaling
-        # series is config 4 on one GPU: measure it here too (2 steps, ~0.5 s each).
+        # series is config 4 on one GPU: measure it here too.
         n4, p4 = gen_workload("c4")
-        placer.upload(n4, p4)
-        placer.run()
-        b_ms = b_ev = 0.0
-        for _ in range(2):
-            flush.zero_()
-            torch.cuda.synchronize()
-            st4 = placer.run()
-            b_ms += st4["step_ms"]
-            b_ev += st4["evals"]
-        line["scaling_base"] = {"workload": WORKLOADS["c4"]["desc"], "n_gpus": 1, "value": b_ev / (b_ms * 1e-3),
-                                "unit": "evals/s", "ms_per_step": b_ms / 2, "rounds": st4["rounds"],
+        ctx.place_upload(n4, p4)
+        ctx.place_run()
+        b_tot, st4 = time_resident(ctx, 5, flush, torch.cuda.synchronize, None, torch)
+        line["scaling_base"] = {"workload": WORKLOADS["c4"]["desc"], "n_gpus": 1, "value": b_tot["evals"] / (b_tot["ms"] * 1e-3),
+                                "unit": "evals/s", "ms_per_step": b_tot["ms"] / 5, "steps": 5, "rounds": st4["rounds"],
+                                "result_sha256": place_digest(ctx.place_download()),
                                 "note": "divide the --gpus N>1 values by N times this for same-workload scaling efficiency"}
 
     if not args.no_reconcile and world == 1:
         from k8sgpu_b200 import synth
+        from k8sgpu_b200.digest import reconcile_digest
 
         t = synth.gen_reconcile(C2["p"], C2["v"])
+        P, V = C2["p"], C2["v"]
         rargs = (t["desired"], t["pool_owner_id"], t["vm_owner_id"], t["vm_flags"], t["n_owner_ids"], t["vm_ordinal"])
         ctx.reconcile_upload(*rargs)
         for _ in range(args.warmup):
@@ -372,27 +405,42 @@ def main():
             flush.zero_()
             torch.cuda.synchronize()
             rms += ctx.reconcile_run()["device_ms"]
-        # end to end: pinned host tables in, host results out, one k8sgpu_reconcile_batch call per step
-        pin1 = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
-        pargs = tuple(pin1(a) if isinstance(a, np.ndarray) else a for a in rargs)
-        bufs, nxt = [], [0]  # pinned output buffers, allocated on the first call and reused by every later one
+        # end to end: pinned host tables in, host results out, one k8sgpu_reconcile_batch call per step.
+        # Inputs in one pinned block in the order the library keeps them (one H2D copy), outputs in one
+        # pinned block laid out as k8sgpu_reconcile_out_size says (adjacent copies merge).
+        inb = pinned_block(torch, 3 * V + 2 * P)
+        pin_in = []
+        for i, a in enumerate((t["vm_owner_id"], t["vm_flags"], t["vm_ordinal"])):
+            inb[i * V:(i + 1) * V] = a
+            pin_in.append(inb[i * V:(i + 1) * V])
+        inb[3 * V:3 * V + P] = t["desired"].view(np.uint32)
+        inb[3 * V + P:3 * V + 2 * P] = t["pool_owner_id"]
+        pargs = (inb[3 * V:3 * V + P].view(np.int32), inb[3 * V + P:3 * V + 2 * P], pin_in[0], pin_in[1],
+                 t["n_owner_ids"], pin_in[2])
+        cap = int(t["desired"].sum()) + 1
+        lay = capi.reconcile_out_size(P, V, cap)
+        outb = pinned_block(torch, lay["total"])
+        sizes = {"pool_of": V, "current": P, "ready": P, "delta": P, "create_count": P, "victim_off": P + 1,
+                 "member_off": P + 1, "create_off": P + 1, "victim_vm": V, "member_vm": V, "create_ordinal": cap}
+        order = ["pool_of", "current", "delta", "ready", "create_count", "victim_off", "victim_vm", "member_off",
+                 "member_vm", "create_off", "create_ordinal"]  # the order Context._rec_out asks for buffers in
+        nxt = [0]
 
         def alloc(n, dt):
-            i = nxt[0]
+            k = order[nxt[0]]
             nxt[0] += 1
-            if i == len(bufs):
-                bufs.append(torch.empty(max(n, 1), dtype=torch.int32).pin_memory().numpy().view(dt)[:n])
-            return bufs[i]
+            return outb[lay[k]: lay[k] + sizes[k]].view(dt)
 
         def call():
             nxt[0] = 0
-            return ctx.reconcile_batch(*pargs, alloc=alloc, trim=False)
+            return ctx.reconcile_batch(*pargs, alloc=alloc, create_capacity=cap - 1, trim=False)
 
         call()
         t0 = time.perf_counter()
         for _ in range(args.steps):
             rr = call()
         rdt = time.perf_counter() - t0
+        rsha = reconcile_digest(capi.Context._rec_trim({k: np.array(v) for k, v in rr.items() if isinstance(v, np.ndarray)}, P))
         alg = 12 * C2["v"] + 16 * C2["p"]
         line["reconcile"] = {
             "workload": f"config2: {C2['p']} pools x {C2['v']} VMs", "decisions_per_s": C2["p"] * args.steps / (rms * 1e-3),
@@ -400,7 +448,7 @@ def main():
             "e2e_decisions_per_s": C2["p"] * args.steps / rdt, "e2e_ms_per_step": 1e3 * rdt / args.steps,
             "h2d_bytes_per_step": int(rr["h2d_bytes"]), "d2h_bytes_per_step": int(rr["d2h_bytes"]),
             "launches_per_step": int(rr["kernel_launches"]), "algorithmic_bytes": alg,
-            "achieved_gbs": alg * args.steps / (rms * 1e-3) / 1e9,
+            "achieved_gbs": alg * args.steps / (rms * 1e-3) / 1e9, "result_sha256": rsha,
             "note": "1.2 MB of work: launch-latency bound at this size; see profiles/ for the scaled sweep",
         }
         if not args.no_cpu_baseline:
@@ -426,11 +474,13 @@ def main():
 
     if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
-        frac = {"c3": 0.25, "c4": 0.001, "c5": 0.01, "tiny": 1.0}[wl]
+        frac = CPU_SAMPLE_FRAC[wl]
+        cpu_port(nodes, pods, min(frac, 0.05), threads)  # thread pool up, tables in cache
         v, ev, dt, sample = cpu_port(nodes, pods, frac, threads)
         line["cpu_baseline"] = {"value": v, "unit": "evals/s", "cores": threads, "kind": "port", "sample": sample,
-                                "seconds": dt}
+                                "sample_frac": frac, "seconds": dt}
     print(json.dumps(line), flush=True)
+    ctx.close()
     if dist is not None:
         dist.destroy_process_group()
 

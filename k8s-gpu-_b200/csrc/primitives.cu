@@ -18,8 +18,9 @@ __global__ void __launch_bounds__(kScanThreads) scan_reduce_kernel(const uint32_
     if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
 }
 
-__global__ void __launch_bounds__(kScanThreads) scan_down_kernel(const uint32_t *__restrict__ in,
-                                                                 uint32_t *__restrict__ out, uint32_t n,
+// (in and out may be the same buffer -- the allocation-free entry point documents in-place use --
+// so neither is __restrict__: every thread loads its eight elements before it stores them.)
+__global__ void __launch_bounds__(kScanThreads) scan_down_kernel(const uint32_t *in, uint32_t *out, uint32_t n,
                                                                  const uint32_t *__restrict__ block_offs) {
     block_scan_tile(in, out, blockIdx.x * kScanTile, n, block_offs[blockIdx.x], true);
 }

@@ -27,6 +27,20 @@ type AzureVmPoolReconciler struct {
 
 func ownerTag(p *computev1alpha1.AzureVmPool) string { return p.Namespace + "-" + p.Name } // README.md:238
 
+// getAzureVMClient is step 2 of Reconcile (README.md:181): build the Azure VM client from the
+// Secret named by spec.azureCredentialSecret (keys AZURE_CLIENT_ID, AZURE_CLIENT_SECRET,
+// AZURE_TENANT_ID, AZURE_SUBSCRIPTION_ID, README.md:108).  There is no network here, so the fake
+// ARM client stands in; it can be told to fail, which is the path README.md:183-185 handles.
+func (r *AzureVmPoolReconciler) getAzureVMClient(ctx context.Context, pool *computev1alpha1.AzureVmPool) (*fakearm.Client, error) {
+	if r.ARM == nil {
+		return nil, fmt.Errorf("no Azure client for secret %q", pool.Spec.AzureCredentialSecret)
+	}
+	if err := r.ARM.ClientError(); err != nil {
+		return nil, err
+	}
+	return r.ARM, nil
+}
+
 func managedBy(vm fakearm.VM, owner string) bool {
 	return vm.Tags[fakearm.ManagedByKey] == fakearm.ManagedByValue && vm.Tags[fakearm.OwnerKey] == owner
 }
@@ -89,7 +103,12 @@ func (r *AzureVmPoolReconciler) Reconcile(ctx context.Context, req ctrl.Request)
 	if err := r.Get(ctx, req.NamespacedName, &pool); err != nil {
 		return ctrl.Result{}, client.IgnoreNotFound(err)
 	}
-	vmClient := r.ARM
+	// 2. Azure client; an error here requeues after 30 s (README.md:181-185)
+	vmClient, err := r.getAzureVMClient(ctx, &pool)
+	if err != nil {
+		logger.Error(err, "unable to create Azure VM client")
+		return ctrl.Result{RequeueAfter: 30 * time.Second}, err
+	}
 	existingVMs, err := r.listManagedVMs(ctx, vmClient, &pool)
 	if err != nil {
 		logger.Error(err, "listing managed VMs failed")
@@ -136,6 +155,10 @@ func (r *AzureVmPoolReconciler) ReconcileAll(ctx context.Context, reqs []ctrl.Re
 		var p computev1alpha1.AzureVmPool
 		if err := r.Get(ctx, req.NamespacedName, &p); err != nil {
 			errs[i] = client.IgnoreNotFound(err)
+			continue
+		}
+		if _, err := r.getAzureVMClient(ctx, &p); err != nil { // step 2 (README.md:181-185)
+			results[i], errs[i] = ctrl.Result{RequeueAfter: 30 * time.Second}, err
 			continue
 		}
 		pools = append(pools, live{i, p})

@@ -26,9 +26,21 @@ const (
 )
 
 type Client struct {
-	groups map[string][]VM
-	failAt [4]int
-	Calls  [4]int
+	groups     map[string][]VM
+	failAt     [4]int
+	Calls      [4]int
+	clientFail bool // getAzureVMClient fails while set (README.md:183-185: requeue after 30 s)
+}
+
+// FailClient arms or disarms the failure of step 2 (building the Azure client from the Secret).
+func (c *Client) FailClient(on bool) { c.clientFail = on }
+
+// ClientError is what getAzureVMClient returns for this fake: nil, or the armed failure.
+func (c *Client) ClientError() error {
+	if c.clientFail {
+		return errors.New("fake ARM: cannot build the Azure VM client")
+	}
+	return nil
 }
 
 func New() *Client { return &Client{groups: map[string][]VM{}} }

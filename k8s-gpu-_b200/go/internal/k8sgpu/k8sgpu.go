@@ -26,12 +26,23 @@ type Decisions struct {
 	VictimVM, MemberVM, CreateOrdinal          []uint32
 }
 
-func New(device int) (*Ctx, error) {
-	dev := C.int(device)
+// New opens one GPU, or several as one placement group (a controller process that owns the
+// node's eight B200s passes all eight: k8sgpu_place then shards the pods of every round across
+// them inside the library, over NCCL, and returns the same bytes as one GPU would).
+func New(devices ...int) (*Ctx, error) {
+	if len(devices) == 0 {
+		devices = []int{0}
+	}
+	devs := make([]C.int, len(devices))
+	for i, d := range devices {
+		devs[i] = C.int(d)
+	}
 	var h *C.k8sgpu_ctx
-	if rc := C.k8sgpu_create(&dev, 1, &h); rc != C.K8SGPU_OK {
+	errbuf := (*C.char)(C.calloc(512, 1)) // per-call buffer: safe when goroutines create contexts concurrently
+	defer C.free(unsafe.Pointer(errbuf))
+	if rc := C.k8sgpu_create_ex(&devs[0], C.int(len(devs)), &h, errbuf, 512); rc != C.K8SGPU_OK {
 		// no GPU is an error: the library has no CPU path
-		return nil, fmt.Errorf("k8sgpu_create: %d: %s", int(rc), C.GoString(C.k8sgpu_last_error(nil)))
+		return nil, fmt.Errorf("k8sgpu_create: %d: %s", int(rc), C.GoString(errbuf))
 	}
 	return &Ctx{h}, nil
 }

@@ -82,6 +82,18 @@ const char *khost_status_condition(khost_world *w, const char *ns, const char *n
     return w->scratch.c_str();
 }
 
+// every condition of the pool's status, "Type=Status:Reason" joined by ';'
+const char *khost_status_conditions(khost_world *w, const char *ns, const char *name) {
+    auto *p = w->api.Get(ns, name);
+    if (!p) return nullptr;
+    w->scratch.clear();
+    for (const auto &c : p->Status.Conditions) {
+        if (!w->scratch.empty()) w->scratch += ";";
+        w->scratch += c.Type + "=" + c.Status + ":" + c.Reason;
+    }
+    return w->scratch.c_str();
+}
+
 // the reference's entry point for one pool (host only)
 int khost_reconcile(khost_world *w, const char *ns, const char *name, int64_t *requeue_s, int *err) {
     auto [res, e] = w->rec.Reconcile(ctrl::Request{ns, name});
@@ -185,6 +197,13 @@ const char *khost_snap_name(khost_snap *s, int table, uint32_t row) {
     const std::vector<std::string> *v = table == 0 ? &s->rec.pool_key : table == 1 ? &s->rec.vm_name
                                         : table == 2 ? &s->nodes.name : &s->pods.name;
     return row < v->size() ? (*v)[row].c_str() : nullptr;
+}
+// i-th pool left out of the reconcile tables because its owner tag is already claimed:
+// "<dropped ns/name>|<ns/name of the pool that keeps the tag>", nullptr past the end
+const char *khost_snap_conflict(khost_snap *s, uint32_t i) {
+    if (i >= s->rec.conflicts.size()) return nullptr;
+    s->err = s->rec.conflicts[i].first + "|" + s->rec.conflicts[i].second;  // (err doubles as the string scratch)
+    return s->err.c_str();
 }
 const char *khost_snap_pool_field(khost_snap *s, uint32_t i, const char *field) {
     const auto &pools = s->b.Pools();

@@ -74,18 +74,60 @@ Error AzureVmPoolReconciler::deleteVM(const AzureVmPool &pool, const std::string
     return Error{};
 }
 
-static void fill_status(AzureVmPool *pool, int32_t currentCount, const std::vector<std::string> &names) {
+const char *ErrKindName(ErrKind k) {
+    switch (k) {
+        case ErrKind::Client: return "ClientFailed";
+        case ErrKind::List: return "ListFailed";
+        case ErrKind::Create: return "CreateFailed";
+        case ErrKind::Delete: return "DeleteFailed";
+        case ErrKind::Status: return "StatusUpdateFailed";
+        case ErrKind::Gpu: return "GpuFailed";
+        case ErrKind::Conflict: return "OwnerTagConflict";
+        default: return "None";
+    }
+}
+
+// Step 5's status (README.md:225-226) with the four condition types README.md:310 proposes:
+// Ready, Provisioning, Deleting, Failed -- in that order, all four always present.
+static void fill_status(AzureVmPool *pool, int32_t currentCount, const std::vector<std::string> &names, ErrKind prev) {
     pool->Status.ReadyReplicas = currentCount;  // README.md:225: the PRE-action count
     pool->Status.VMs = names;                   // README.md:124-125, :226 (elided in the reference)
-    computev1alpha1::Condition c;
-    c.Type = "Ready";  // README.md:310 names Provisioning / Ready / Deleting / Failed
     const int32_t desired = pool->Spec.Replicas;
-    c.Status = currentCount == desired ? "True" : "False";
-    c.Reason = currentCount == desired ? "Reconciled" : (currentCount < desired ? "Provisioning" : "Deleting");
-    pool->Status.Conditions = {c};
+    auto cond = [](const char *type, bool on, const char *reason) {
+        computev1alpha1::Condition c;
+        c.Type = type;
+        c.Status = on ? "True" : "False";
+        c.Reason = reason;
+        return c;
+    };
+    pool->Status.Conditions = {
+        cond("Ready", currentCount == desired,
+             currentCount == desired ? "Reconciled" : (currentCount < desired ? "Provisioning" : "Deleting")),
+        cond("Provisioning", currentCount < desired, currentCount < desired ? "ScalingUp" : "NotScalingUp"),
+        cond("Deleting", currentCount > desired, currentCount > desired ? "ScalingDown" : "NotScalingDown"),
+        // the pass before this one ended in an error (and so wrote no status, README.md:207,219)
+        cond("Failed", prev != ErrKind::None, prev != ErrKind::None ? ErrKindName(prev) : "NoError"),
+    };
+}
+
+ErrKind AzureVmPoolReconciler::lastFailure(const ctrl::Request &req) const {
+    auto it = last_failure_.find(std::make_pair(req.Namespace, req.Name));
+    return it == last_failure_.end() ? ErrKind::None : it->second;
+}
+
+void AzureVmPoolReconciler::remember(const ctrl::Request &req, const Error &e, bool pool_exists) {
+    auto key = std::make_pair(req.Namespace, req.Name);
+    if (e && pool_exists) last_failure_[key] = e.kind;
+    else last_failure_.erase(key);
 }
 
 std::pair<ctrl::Result, Error> AzureVmPoolReconciler::Reconcile(const ctrl::Request &req) {
+    auto out = reconcileOnce(req, lastFailure(req));
+    remember(req, out.second, api_->Get(req.Namespace, req.Name) != nullptr);
+    return out;
+}
+
+std::pair<ctrl::Result, Error> AzureVmPoolReconciler::reconcileOnce(const ctrl::Request &req, ErrKind prev) {
     // 1. r.Get; NotFound is swallowed (README.md:174-177)
     AzureVmPool *found = api_->Get(req.Namespace, req.Name);
     if (!found) return {ctrl::Result{}, Error{}};
@@ -117,7 +159,7 @@ std::pair<ctrl::Result, Error> AzureVmPoolReconciler::Reconcile(const ctrl::Requ
     // 5. status (README.md:225-230)
     std::vector<std::string> names;
     for (const VM &vm : existingVMs) names.push_back(vm.Name);
-    fill_status(&azureVmPool, currentCount, names);
+    fill_status(&azureVmPool, currentCount, names, prev);
     if (!api_->StatusUpdate(azureVmPool)) return {ctrl::Result{}, Error{ErrKind::Status, "status update failed"}};
 
     return {ctrl::Result{seconds(60)}, Error{}};  // :234
@@ -134,20 +176,25 @@ std::vector<BatchOutcome> BatchReconciler::ReconcileAll(const std::vector<ctrl::
     };
     std::vector<Live> live;
     std::map<std::pair<std::string, std::string>, size_t> seen;  // (ns,name) -> index in live, or npos
+    std::map<std::pair<std::string, std::string>, size_t> first_req;  // (ns,name) -> first request naming it
     std::vector<long> alias(reqs.size(), -1);                    // request -> live index
+    std::vector<long> same_as(reqs.size(), -1);                  // request -> earlier request with the same outcome
     constexpr size_t npos = static_cast<size_t>(-1);
 
     // steps 1 and 2 per request
     for (size_t r = 0; r < reqs.size(); ++r) {
         auto key = std::make_pair(reqs[r].Namespace, reqs[r].Name);
         auto it = seen.find(key);
-        if (it != seen.end()) {
-            if (it->second != npos) alias[r] = static_cast<long>(it->second);  // same pool again: one pass, same outcome
+        if (it != seen.end()) {  // same pool again: one pass, same outcome (whatever it was)
+            if (it->second != npos) alias[r] = static_cast<long>(it->second);
+            else same_as[r] = static_cast<long>(first_req[key]);
             continue;
         }
+        first_req[key] = r;
         AzureVmPool *found = api_->Get(reqs[r].Namespace, reqs[r].Name);
         if (!found) {  // README.md:176
             seen[key] = npos;
+            remember(reqs[r], Error{}, false);
             continue;
         }
         auto [vmClient, cerr] = getAzureVMClient(*found);
@@ -155,6 +202,7 @@ std::vector<BatchOutcome> BatchReconciler::ReconcileAll(const std::vector<ctrl::
         if (cerr) {  // README.md:184
             out[r] = BatchOutcome{ctrl::Result{seconds(30)}, cerr};
             seen[key] = npos;
+            remember(reqs[r], cerr, true);
             continue;
         }
         seen[key] = live.size();
@@ -181,10 +229,18 @@ std::vector<BatchOutcome> BatchReconciler::ReconcileAll(const std::vector<ctrl::
     std::map<std::pair<std::string, std::string>, uint32_t> owner_id;  // (rg, owner tag) -> pool row
     std::vector<int32_t> desired;
     std::vector<uint32_t> pool_owner;
+    std::vector<long> conflicts_with(live.size(), -1);
     for (size_t i = 0; i < live.size(); ++i) {
         if (live[i].rg_failed) continue;
         auto key = std::make_pair(live[i].pool.Spec.ResourceGroupName, OwnerTag(live[i].pool));
-        if (owner_id.count(key)) continue;  // two CRs cannot share namespace/name; defensive
+        auto dup = owner_id.find(key);
+        if (dup != owner_id.end()) {
+            // "<namespace>-<name>" (README.md:238) is not injective: team-a/pool and team/a-pool share
+            // the tag "team-a-pool", so both would claim the same VMs.  The first keeps the tag; this
+            // pool gets an explicit error instead of a table row (its VMs cannot be told apart).
+            conflicts_with[i] = static_cast<long>(pool_of_live[dup->second]);
+            continue;
+        }
         owner_id[key] = static_cast<uint32_t>(pool_of_live.size());
         pool_owner.push_back(static_cast<uint32_t>(pool_of_live.size()));
         desired.push_back(live[i].pool.Spec.Replicas);
@@ -243,6 +299,13 @@ std::vector<BatchOutcome> BatchReconciler::ReconcileAll(const std::vector<ctrl::
             live_out[i] = BatchOutcome{ctrl::Result{seconds(20)}, Error{ErrKind::List, "ARM list failed"}};
             continue;
         }
+        if (conflicts_with[i] >= 0) {
+            const AzureVmPool &o = live[static_cast<size_t>(conflicts_with[i])].pool;
+            live_out[i] = BatchOutcome{ctrl::Result{seconds(30)},
+                                       Error{ErrKind::Conflict, "owner tag '" + OwnerTag(l.pool) + "' is already claimed by pool " +
+                                                                    o.Metadata.Namespace + "/" + o.Metadata.Name}};
+            continue;
+        }
         if (rc != K8SGPU_OK) {  // no CPU path: report, requeue like a client failure
             live_out[i] = BatchOutcome{ctrl::Result{seconds(30)}, Error{ErrKind::Gpu, k8sgpu_last_error(gpu_)}};
             continue;
@@ -259,15 +322,18 @@ std::vector<BatchOutcome> BatchReconciler::ReconcileAll(const std::vector<ctrl::
         }
         std::vector<std::string> names;
         for (int32_t j = member_off[p]; j < member_off[p + 1]; ++j) names.push_back(vm_row[member_vm[static_cast<size_t>(j)]]->Name);
-        fill_status(&l.pool, ready[p], names);  // :225
+        fill_status(&l.pool, ready[p], names, lastFailure(reqs[l.req]));  // :225
         if (!api_->StatusUpdate(l.pool)) {
             live_out[i] = BatchOutcome{ctrl::Result{}, Error{ErrKind::Status, "status update failed"}};  // :229
             continue;
         }
         live_out[i] = BatchOutcome{ctrl::Result{seconds(60)}, Error{}};  // :234
     }
-    for (size_t r = 0; r < reqs.size(); ++r)
+    for (size_t i = 0; i < live.size(); ++i) remember(reqs[live[i].req], live_out[i].err, true);
+    for (size_t r = 0; r < reqs.size(); ++r) {
         if (alias[r] >= 0) out[r] = live_out[static_cast<size_t>(alias[r])];
+        else if (same_as[r] >= 0) out[r] = out[static_cast<size_t>(same_as[r])];  // e.g. the client failure of the first one
+    }
     return out;
 }
 

@@ -11,6 +11,7 @@
 // status writes of README.md:203-230 per pool, in the same order and with the same early returns.
 #pragma once
 #include <chrono>
+#include <map>
 #include <optional>
 #include <string>
 #include <utility>
@@ -30,7 +31,8 @@ struct Request {
 };
 }  // namespace ctrl
 
-enum class ErrKind { None = 0, Client = 1, List = 2, Create = 3, Delete = 4, Status = 5, Gpu = 6 };
+enum class ErrKind { None = 0, Client = 1, List = 2, Create = 3, Delete = 4, Status = 5, Gpu = 6, Conflict = 7 };
+const char *ErrKindName(ErrKind k);  // "ClientFailed", "ListFailed", ... (condition reasons)
 struct Error {
     ErrKind kind = ErrKind::None;
     std::string msg;
@@ -59,8 +61,17 @@ class AzureVmPoolReconciler {
     static std::optional<uint32_t> OrdinalOf(const std::string &vm_name, const std::string &pool_name);
 
   protected:
+    // Steps 1-5 for one pool; prev = how this pool's previous pass ended (for the Failed condition).
+    std::pair<ctrl::Result, Error> reconcileOnce(const ctrl::Request &req, ErrKind prev);
+    // The four condition types README.md:310 names.  A pass that fails returns before the status
+    // write (README.md:207,219), so Failed=True can only be written by the NEXT pass that gets as
+    // far as step 5: the reconciler remembers how each pool's last pass ended.
+    ErrKind lastFailure(const ctrl::Request &req) const;
+    void remember(const ctrl::Request &req, const Error &e, bool pool_exists);
+
     FakeApiServer *api_;
     FakeArmClient *arm_;
+    std::map<std::pair<std::string, std::string>, ErrKind> last_failure_;
 };
 
 // Per-pool outcome of one batch pass, in request order.

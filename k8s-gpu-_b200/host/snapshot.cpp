@@ -560,7 +560,11 @@ ReconcileTables SnapshotBuilder::BuildReconcileTables() const {
     std::map<std::pair<std::string, std::string>, uint32_t> row;  // (resource group, owner tag) -> pool row
     for (const auto &p : pools_) {
         auto key = std::make_pair(p.Spec.ResourceGroupName, AzureVmPoolReconciler::OwnerTag(p));
-        if (row.count(key)) continue;
+        auto dup = row.find(key);
+        if (dup != row.end()) {  // same owner tag as an earlier pool: its VMs cannot be told apart
+            t.conflicts.emplace_back(p.Metadata.Namespace + "/" + p.Metadata.Name, t.pool_key[dup->second]);
+            continue;
+        }
         row[key] = static_cast<uint32_t>(t.desired.size());
         t.pool_owner.push_back(static_cast<uint32_t>(t.desired.size()));
         t.desired.push_back(p.Spec.Replicas);

@@ -62,6 +62,10 @@ struct ReconcileTables {  // k8sgpu_pool_table + k8sgpu_vm_table, owned
     uint32_t n_owner_ids = 0;
     std::vector<std::string> pool_key;  // "<namespace>/<name>" per pool row
     std::vector<std::string> vm_name;   // per VM row
+    // Pools left out of the table because another pool of the same resource group already claims
+    // their owner tag ("<namespace>-<name>", README.md:238, is not injective): "<ns>/<name>" of the
+    // dropped pool and of the pool that keeps the tag.  Never silently: callers must report these.
+    std::vector<std::pair<std::string, std::string>> conflicts;
 };
 
 struct NodeTable {  // k8sgpu_node_table, owned (one node per VM)

@@ -8,7 +8,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libk8sgpu_host.so")
-ERR = {"None": 0, "Client": 1, "List": 2, "Create": 3, "Delete": 4, "Status": 5, "Gpu": 6}
+ERR = {"None": 0, "Client": 1, "List": 2, "Create": 3, "Delete": 4, "Status": 5, "Gpu": 6, "Conflict": 7}
 FAIL = {"client": 0, "list": 1, "create": 2, "delete": 3, "status": 4}
 _lib = None
 
@@ -38,6 +38,8 @@ def load():
         L.khost_status_vm.restype = cp
         L.khost_status_condition.argtypes = [vp, cp, cp]
         L.khost_status_condition.restype = cp
+        L.khost_status_conditions.argtypes = [vp, cp, cp]
+        L.khost_status_conditions.restype = cp
         L.khost_reconcile.argtypes = [vp, cp, cp, C.POINTER(C.c_int64), C.POINTER(C.c_int)]
         L.khost_reconcile_batch.argtypes = [vp, C.c_int, C.c_int, C.POINTER(cp), C.POINTER(cp),
                                             C.POINTER(C.c_int64), C.POINTER(C.c_int)]
@@ -91,6 +93,19 @@ class World:
     def condition(self, ns, name):
         c = self._L.khost_status_condition(self._h, ns.encode(), name.encode())
         return c.decode() if c else None
+
+    def conditions(self, ns, name):
+        """Every condition of the pool's status: {"Ready": ("True", "Reconciled"), ...}."""
+        c = self._L.khost_status_conditions(self._h, ns.encode(), name.encode())
+        if not c:
+            return None
+        out = {}
+        for item in c.decode().split(";"):
+            if item:
+                t, rest = item.split("=", 1)
+                st, reason = rest.split(":", 1)
+                out[t] = (st, reason)
+        return out
 
     def reconcile(self, ns, name):
         """AzureVmPoolReconciler.Reconcile for one pool -> (requeue_after_seconds, error kind)."""
@@ -148,6 +163,8 @@ class Snapshot:
         L.khost_snap_name.restype = cp
         L.khost_snap_pool_field.argtypes = [vp, C.c_uint32, cp]
         L.khost_snap_pool_field.restype = cp
+        L.khost_snap_conflict.argtypes = [vp, C.c_uint32]
+        L.khost_snap_conflict.restype = cp
         self._h = L.khost_snap_new()
 
     def __del__(self):
@@ -169,6 +186,16 @@ class Snapshot:
     def pool_field(self, i, field):
         v = self._L.khost_snap_pool_field(self._h, i, field.encode())
         return None if v is None else v.decode()
+
+    def conflicts(self):
+        """Pools left out of the reconcile tables (after build()): [(dropped "ns/name", kept "ns/name")]."""
+        out, i = [], 0
+        while True:
+            v = self._L.khost_snap_conflict(self._h, i)
+            if v is None:
+                return out
+            out.append(tuple(v.decode().split("|", 1)))
+            i += 1
 
     def _col(self, table, col, n, dtype=None):
         np = self.np

@@ -100,6 +100,34 @@ def test_error_paths_match_reference_requeue_delays(hm, orc):
     assert step_both(hm, orc, w, o, name) == (0, 5)
 
 
+def test_four_condition_types(hm, orc):
+    """README.md:310 names Provisioning / Ready / Deleting / Failed.  All four are written on every
+    status update; Failed=True appears on the first pass AFTER a failed one, because the failing
+    pass returns before the status write (README.md:207,219) -- K8 and K9 are unchanged by this."""
+    name, owner = "p", f"{NS}-p"
+    w, o = both_worlds(hm, orc, [(name, 3)], [(f"p-{i}", OP, owner) for i in range(3)])
+    assert step_both(hm, orc, w, o, name) == (60, 0)
+    assert w.conditions(NS, name) == {"Ready": ("True", "Reconciled"), "Provisioning": ("False", "NotScalingUp"),
+                                      "Deleting": ("False", "NotScalingDown"), "Failed": ("False", "NoError")}
+    w.put_pool(NS, name, 6); o[0].set_replicas(NS, name, 6)
+    w.fail("create", 2); o[1].fail_create_at(2)
+    assert step_both(hm, orc, w, o, name) == (40, 3)                      # K8: status NOT written
+    assert w.conditions(NS, name)["Failed"] == ("False", "NoError")       # ... so it still says what it said
+    assert step_both(hm, orc, w, o, name) == (60, 0)                      # next pass gets to step 5
+    c = w.conditions(NS, name)
+    assert c["Failed"] == ("True", "CreateFailed") and c["Provisioning"] == ("True", "ScalingUp")
+    assert c["Ready"] == ("False", "Provisioning")                         # ReadyReplicas is the pre-action count (4)
+    assert step_both(hm, orc, w, o, name) == (60, 0)
+    c = w.conditions(NS, name)
+    assert c["Failed"] == ("False", "NoError") and c["Ready"] == ("True", "Reconciled")
+    w.put_pool(NS, name, 1); o[0].set_replicas(NS, name, 1)
+    w.fail("delete", 3); o[1].fail_delete_at(3)
+    assert step_both(hm, orc, w, o, name) == (40, 4)                      # K9
+    assert step_both(hm, orc, w, o, name) == (60, 0)
+    c = w.conditions(NS, name)
+    assert c["Failed"] == ("True", "DeleteFailed") and c["Deleting"] == ("True", "ScalingDown")
+
+
 def test_k10_k11_foreign_vms_and_scale_to_zero(hm, orc):
     name, owner = "p", f"{NS}-p"
     vms = [("other-0", OP, "default-other"), ("p-0", OP, owner), ("bare", None, owner), ("impostor", "someone", owner),
@@ -150,7 +178,7 @@ def random_world(rng, hm, n_pools, n_vms, two_groups):
 
 def snapshot(w, pools):
     return ({rg: w.vm_names(rg) for rg in ("rgA", "rgB")},
-            {name: (w.ready_replicas(NS, name), w.status_vms(NS, name), w.condition(NS, name)) for name, _, _ in pools},
+            {name: (w.ready_replicas(NS, name), w.status_vms(NS, name), w.conditions(NS, name)) for name, _, _ in pools},
             w.status_writes)
 
 
@@ -176,6 +204,28 @@ def test_batch_reconciler_equals_sequential(hm, seed):
     want = [seq.reconcile(ns, nm) for ns, nm in keys]
     assert bat.reconcile_batch(keys) == want
     assert snapshot(bat, pools) == snapshot(seq, pools)
+
+
+@pytest.mark.gpu
+def test_batch_owner_tag_collision_and_repeated_requests(hm):
+    """"<namespace>-<name>" is not injective: team-a/pool and team/a-pool both own the tag
+    "team-a-pool".  The batch pass gives the second pool an explicit Conflict outcome (no table row,
+    no out-of-range row index) and still reconciles the first.  A pool named twice in one pass gets
+    the same outcome both times -- also when that outcome is the 30 s client failure."""
+    w = hm.World()
+    w.put_pool("team-a", "pool", 2)
+    w.put_pool("team", "a-pool", 5)
+    w.put_pool(NS, "solo", 1)
+    for i in range(3):
+        w.add_vm(f"pool-{i}", managed_by=OP, owner="team-a-pool")
+    out = w.reconcile_batch([("team-a", "pool"), ("team", "a-pool"), (NS, "solo"), ("team", "a-pool")])
+    assert out[0] == (60, 0) and out[2] == (60, 0)
+    assert out[1] == (30, hm.ERR["Conflict"]) and out[3] == out[1]
+    assert w.vm_names() == ["pool-1", "pool-2", "solo-0"]  # first victim in list order; solo scaled up
+    w2 = hm.World()
+    w2.put_pool(NS, "p", 1)
+    w2.fail("client")
+    assert w2.reconcile_batch([(NS, "p"), (NS, "p"), (NS, "gone")]) == [(30, 1), (30, 1), (0, 0)]
 
 
 def test_batch_reconciler_needs_a_gpu(hm):

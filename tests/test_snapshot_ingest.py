@@ -215,3 +215,17 @@ def test_ingested_snapshot_through_the_gpu(built, orc):
         # the 8-GPU pod can only land on the H100 VM in eastus-2; the 1-GPU pods take T4 nodes (best fit)
         assert b["node_names"][gp["assign"][2]] == "h100-pool-1"
         assert all(b["nodes"]["cap_gpu"][gp["assign"][i]] == 1 for i in (0, 1, 3))
+
+
+def test_owner_tag_conflict_is_reported(hm):
+    """team-a/pool and team/a-pool share the owner tag "team-a-pool" (README.md:238 builds it as
+    "<namespace>-<name>"): the second is left out of the tables and listed in conflicts()."""
+    mk = lambda ns, name: (f"apiVersion: compute.my.domain/v1alpha1\nkind: AzureVmPool\nmetadata:\n  name: {name}\n"
+                           f"  namespace: {ns}\nspec:\n  replicas: 1\n  resourceGroupName: rg1\n  location: eastus\n"
+                           f"  vmSize: Standard_NC4as_T4_v3\n")
+    s = hm.Snapshot()
+    s.add_pools_yaml(mk("team-a", "pool") + "---\n" + mk("team", "a-pool") + "---\n" + mk("team", "other"))
+    s.add_vms_json("[]")
+    b = s.build()
+    assert b["pool_keys"] == ["team-a/pool", "team/other"]
+    assert s.conflicts() == [("team/a-pool", "team-a/pool")]

@@ -47,6 +47,36 @@ def test_two_calls_in_a_row_match_the_allocating_entry_point(capi):
             want, want_total = ctx.exclusive_scan(a)  # the existing, allocating entry point
             assert np.array_equal(got, want)          # integer work: bit exact
             assert got_total == want_total == int(a.sum(dtype=np.uint64) & 0xFFFFFFFF)
+            ref = np.cumsum(a, dtype=np.uint64)       # and both against numpy itself
+            assert got[0] == 0 and np.array_equal(got[1:], (ref[:-1] & 0xFFFFFFFF).astype(np.uint32))
+
+
+def test_largest_size_against_numpy_and_no_allocation(capi):
+    """n = 2^24 exactly: the one size that fills the built-in scratch to its last word (8192 block
+    sums), where an off-by-one would run past the array.  Checked against numpy.cumsum directly,
+    and the device's free memory is the same before and after the calls: nothing was allocated."""
+    import torch
+
+    n = capi.SCAN_NOALLOC_MAX_N
+    rng = np.random.default_rng(7)
+    with capi.Context(0) as ctx:
+        a = rng.integers(0, 200, n, dtype=np.uint32)
+        d_in = torch.from_numpy(a.view(np.int32)).cuda()
+        d_out = torch.empty_like(d_in)
+        d_tot = torch.zeros(1, dtype=torch.int32, device="cuda")
+        stream = torch.cuda.current_stream().cuda_stream
+        ctx.exclusive_scan_noalloc(d_in.data_ptr(), 16, d_out.data_ptr(), d_tot.data_ptr(), stream)  # set-up call
+        torch.cuda.synchronize()
+        free_before, _ = torch.cuda.mem_get_info()
+        for m in (n, n - 1, n - 2047):  # full, one short of full, last block nearly empty
+            ctx.exclusive_scan_noalloc(d_in.data_ptr(), m, d_out.data_ptr(), d_tot.data_ptr(), stream)
+            torch.cuda.synchronize()
+            want = np.cumsum(a[:m], dtype=np.uint64)
+            got = d_out[:m].cpu().numpy().view(np.uint32)
+            assert got[0] == 0 and np.array_equal(got[1:], (want[:-1] & 0xFFFFFFFF).astype(np.uint32))
+            assert int(d_tot.cpu().numpy().view(np.uint32)[0]) == int(want[-1] & 0xFFFFFFFF)
+        free_after, _ = torch.cuda.mem_get_info()
+        assert free_after == free_before
 
 
 def test_small_inputs_in_place_and_empty(capi):
