@@ -224,7 +224,7 @@ def main():
     ap.add_argument("--no-reconcile", action="store_true")
     ap.add_argument("--no-scaling-base", action="store_true")
     ap.add_argument("--exchange", default=None, choices=["allgather", "peer"],
-                    help="N>1: how a round's proposals travel (default: NCCL all-gather)")
+                    help="N>1: force how a round's proposals travel (default: chosen per round by list length)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -352,8 +352,10 @@ def main():
         "config": {"workload": WORKLOADS[wl]["desc"], "nodes": N, "pods": M, "rounds": rounds, "placed": placed,
                    "evals_per_step": tot_evals // args.steps, "result_sha256": sha,
                    "parallelism": f"pods sharded x{world}, nodes replicated",
-                   "exchange": "none" if world == 1 else ("peer stores + 1-word ncclAllReduce" if args.exchange == "peer"
-                                                          else "ncclAllGather of the proposals, in the library"),
+                   "exchange": "none" if world == 1 else {"peer": "peer stores + 1-word ncclAllReduce (forced)",
+                                                          "allgather": "ncclAllGather of the proposals (forced)",
+                                                          None: "per round, in the library: ncclAllGather above 2^18 "
+                                                                "proposals, peer stores + 1-word ncclAllReduce below"}[args.exchange],
                    "l2": "flushed between timed steps (256 MB write)", "wall_s_timed_region": wall,
                    "launches_per_e2e_step": launches_e2e},
         "roofline": {"bound": "instruction issue (INT32), not hbm: see roofline_contract", "achieved": score_rate,

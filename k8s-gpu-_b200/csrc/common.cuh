@@ -133,7 +133,7 @@ struct Tuning {
     int rec_segments = -1;  // row segments of the pruned ranking pass
     int coop_prof = 0, rec_prof = 0;  // print phase times (stderr)
     int shard_admit = -1;   // multi-GPU: 1 = admission sharded by node range, 0 = replicated
-    int exchange = -1;      // multi-GPU: 0 = NCCL all-gather, 1 = peer stores
+    int exchange = -1;      // multi-GPU: 0 = NCCL all-gather, 1 = peer stores, -1 = per round by list length
 };
 
 }  // namespace k8sgpu
@@ -167,7 +167,7 @@ struct k8sgpu_ctx {
     k8sgpu::DevBuf xsmall;    // barrier word, IPC handles
     uint32_t xchg_m = 0;      // proposals per half of xchg
     int32_t *xpeer[16] = {};  // every rank's xchg as seen from this GPU (peer-store exchange)
-    bool xpeer_ready = false, xpeer_ipc = false;
+    bool xpeer_ready = false, xpeer_ipc = false, xpeer_failed = false;
 };
 
 namespace k8sgpu {

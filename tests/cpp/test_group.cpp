@@ -128,9 +128,10 @@ int main(int argc, char **argv) {
     for (auto sz : sizes) {
         const Tables t = make(sz.n, sz.m, 1000 + sz.n);
         for (int gangs = 0; gangs < 2; ++gangs)
-            for (int variant = 0; variant < 4; ++variant) {
-                // variant: 0 all-gather + one-launch admission, 1 peer stores, 2 all-gather + kernel chain, 3 rot = 0
-                k8sgpu_set_tuning(grp, "exchange", variant == 1 ? 1 : 0);
+            for (int variant = 0; variant < 5; ++variant) {
+                // variant: 0 all-gather + one-launch admission, 1 peer stores, 2 all-gather + kernel chain,
+                // 3 rot = 0 (all-gather), 4 automatic exchange (chosen per round by the list length)
+                k8sgpu_set_tuning(grp, "exchange", variant == 1 ? 1 : variant == 4 ? -1 : 0);
                 k8sgpu_set_tuning(grp, "coop", variant == 2 ? 0 : -1);
                 const uint32_t flags = variant == 3 ? K8SGPU_POLICY_ROT_ZERO : 0;
                 Result a, b;
