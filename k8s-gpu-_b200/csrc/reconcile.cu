@@ -479,28 +479,39 @@ constexpr uint32_t kPruneMaxRowsPerCta = 65536;  // 2048 mask words
 
 __global__ void __launch_bounds__(256) prune_kernel(PruneArgs a) {
     cg::grid_group grid = cg::this_grid();
-    __shared__ uint32_t mask[kPruneMaxRowsPerCta / 32];
+    __shared__ uint32_t mask[kPruneMaxRowsPerCta / 32];  // candidate bits: word t*8+w = rows lo + t*256 + w*32 ..
+    __shared__ uint32_t wpre[kPruneMaxRowsPerCta / 32];  // candidates of this CTA before that word
     __shared__ uint32_t red[8], red2[8];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5, cta = blockIdx.x, G = gridDim.x;
-    const uint32_t words = a.rows_per_cta / 32u;
+    const uint32_t lt = (1u << lane) - 1u;
+    const uint32_t tiles = a.rows_per_cta / 256u, words = tiles * 8u;
     const uint64_t seg_rows = (uint64_t)a.rows_per_cta * G;
+    constexpr uint32_t U = 8;  // tiles of 256 rows whose loads are issued together
     uint32_t total = 0;  // candidates of all earlier segments (every CTA computes the same number)
     for (uint32_t s = 0; s < a.segments; ++s) {
         const uint64_t lo64 = (uint64_t)s * seg_rows + (uint64_t)cta * a.rows_per_cta;
         const uint32_t lo = lo64 < a.V ? (uint32_t)lo64 : a.V;
         const uint32_t hi = (uint64_t)lo + a.rows_per_cta < a.V ? lo + a.rows_per_cta : a.V;
         uint32_t mine = 0;
-        for (uint32_t t = 0; t * 256u < a.rows_per_cta; ++t) {
-            const uint32_t v = lo + t * 256u + tid;
-            bool cand = false;
-            int32_t p = -1;
-            if (v < hi) p = a.pool_of[v];
-            if (p >= 0) cand = __ldcg(&a.remaining[p]) > 0u;
-            if (cand) atomicAdd(&a.seen[p], 1u);
-            const uint32_t m = __ballot_sync(0xFFFFFFFFu, cand);
-            if (lane == 0) {
-                mask[t * 8u + warp] = m;
-                mine += (uint32_t)__popc(m);
+        for (uint32_t t0 = 0; t0 < tiles; t0 += U) {
+            int32_t p[U];
+            uint32_t rem[U];
+#pragma unroll
+            for (uint32_t u = 0; u < U; ++u) {
+                const uint32_t v = lo + (t0 + u) * 256u + tid;
+                p[u] = (t0 + u < tiles && v < hi) ? __ldg(&a.pool_of[v]) : -1;
+            }
+#pragma unroll
+            for (uint32_t u = 0; u < U; ++u) rem[u] = p[u] >= 0 ? __ldcg(&a.remaining[p[u]]) : 0u;
+#pragma unroll
+            for (uint32_t u = 0; u < U; ++u) {
+                const bool cand = rem[u] > 0u;
+                if (cand) atomicAdd(&a.seen[p[u]], 1u);
+                const uint32_t m = __ballot_sync(0xFFFFFFFFu, cand);
+                if (lane == 0 && t0 + u < tiles) {
+                    mask[(t0 + u) * 8u + warp] = m;
+                    mine += (uint32_t)__popc(m);
+                }
             }
         }
         if (lane == 0) red[warp] = mine;
@@ -520,48 +531,68 @@ __global__ void __launch_bounds__(256) prune_kernel(PruneArgs a) {
         }
         before = __reduce_add_sync(0xFFFFFFFFu, before);
         all = __reduce_add_sync(0xFFFFFFFFu, all);
-        __syncthreads();  // red[] of phase 1 has been read
+        // exclusive prefix of the per-word candidate counts: thread i owns words [8i, 8i+8)
+        uint32_t wc[8], wsum = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < 8; ++k) {
+            const uint32_t w = tid * 8u + k;
+            wc[k] = w < words ? (uint32_t)__popc(mask[w]) : 0u;
+            wsum += wc[k];
+        }
+        const uint32_t winc = warp_incl_scan(wsum, (int)lane);
         if (lane == 0) {
             red[warp] = before;
             red2[warp] = all;
         }
+        __shared__ uint32_t wtot[8];
+        if (lane == 31) wtot[warp] = winc;
         __syncthreads();
         before = all = 0;
-        for (int w = 0; w < 8; ++w) {
-            before += red[w];
-            all += red2[w];
+        uint32_t woff = 0;
+        for (uint32_t k = 0; k < 8; ++k) {
+            before += red[k];
+            all += red2[k];
+            woff += k < warp ? wtot[k] : 0u;
         }
-        uint32_t run = total + before;
-        for (uint32_t w0 = 0; w0 < words; w0 += 256u) {  // 256 mask words (8192 rows) per step, in order
-            const uint32_t w = w0 + tid;
-            const uint32_t m = w < words ? mask[w] : 0u;
-            const uint32_t c = (uint32_t)__popc(m), inc = warp_incl_scan(c, lane);
-            __syncthreads();
-            if (lane == 31) red[warp] = inc;
-            __syncthreads();
-            uint32_t woff = 0, step = 0;
-            for (int k = 0; k < 8; ++k) {
-                woff += k < (int)warp ? red[k] : 0u;
-                step += red[k];
+        {
+            uint32_t run = woff + winc - wsum;
+#pragma unroll
+            for (uint32_t k = 0; k < 8; ++k) {
+                const uint32_t w = tid * 8u + k;
+                if (w < words) wpre[w] = run;
+                run += wc[k];
             }
-            uint32_t pos = run + woff + inc - c;
-            uint32_t bits = m;
-            while (bits) {
-                const uint32_t b = (uint32_t)__ffs(bits) - 1u;
-                bits &= bits - 1u;
-                // word w = (tile w / 8, warp w % 8): rows lo + (w/8)*256 + (w%8)*32 + b
-                const uint32_t v = lo + (w >> 3) * 256u + (w & 7u) * 32u + b;
-                const uint32_t p = (uint32_t)a.pool_of[v];
-                a.cand_keys[pos] = p;
-                a.cand_vals[pos] = v;
-                ++pos;
-                const uint32_t k = a.kvict[p], sn = __ldcg(&a.seen[p]);
-                const uint32_t rem = k > sn ? k - sn : 0u;
+        }
+        __syncthreads();
+        const uint32_t base = total + before;
+        constexpr uint32_t U2 = 4;
+        for (uint32_t t0 = 0; t0 < tiles; t0 += U2) {
+            bool is[U2];
+            uint32_t v[U2], pos[U2], p[U2], k[U2], sn[U2];
+#pragma unroll
+            for (uint32_t u = 0; u < U2; ++u) {
+                const uint32_t w = (t0 + u) * 8u + warp;
+                const uint32_t m = t0 + u < tiles ? mask[w] : 0u;
+                is[u] = (m >> lane) & 1u;
+                v[u] = lo + (t0 + u) * 256u + tid;
+                pos[u] = is[u] ? base + wpre[w] + (uint32_t)__popc(m & lt) : 0u;
+                p[u] = is[u] ? (uint32_t)__ldg(&a.pool_of[v[u]]) : 0u;
+            }
+#pragma unroll
+            for (uint32_t u = 0; u < U2; ++u) {
+                k[u] = is[u] ? __ldg(&a.kvict[p[u]]) : 0u;
+                sn[u] = is[u] ? __ldcg(&a.seen[p[u]]) : 0u;
+            }
+#pragma unroll
+            for (uint32_t u = 0; u < U2; ++u) {
+                if (!is[u]) continue;
+                a.cand_keys[pos[u]] = p[u];
+                a.cand_vals[pos[u]] = v[u];
+                const uint32_t rem = k[u] > sn[u] ? k[u] - sn[u] : 0u;
                 // every candidate of the pool stores the same value; whoever replaces the last
                 // non-zero one takes the pool off the list of pools still short
-                if (atomicExch(&a.remaining[p], rem) > 0u && rem == 0u) atomicSub(&a.counters[2], 1u);
+                if (atomicExch(&a.remaining[p[u]], rem) > 0u && rem == 0u) atomicSub(&a.counters[2], 1u);
             }
-            run += step;
         }
         total += all;
         grid.sync();
@@ -799,7 +830,7 @@ static int rec_run_large(k8sgpu_ctx *ctx, cudaStream_t s, bool full_sort) {
             st.prune_occ = per_sm > 0 ? per_sm : -1;
         }
         if (st.prune_occ < 0) return fail(ctx, K8SGPU_E_CUDA, "cooperative pruning kernel cannot be resident");
-        uint32_t grid = (uint32_t)ctx->sm_count * (uint32_t)(st.prune_occ < 2 ? st.prune_occ : 2);
+        uint32_t grid = (uint32_t)ctx->sm_count * (uint32_t)(st.prune_occ < 4 ? st.prune_occ : 4);
         if (grid > ceil_div(V, 256u)) grid = ceil_div(V, 256u);
         if (ctx->tune.rec_grid >= 1 && (uint32_t)ctx->tune.rec_grid <= (uint32_t)ctx->sm_count * (uint32_t)st.prune_occ)
             grid = (uint32_t)ctx->tune.rec_grid;
