@@ -66,6 +66,11 @@ struct PlaceState {
     DevBuf podq;       // m x 32 B packed pod records (built at begin)
     DevBuf assign;     // m i32
     DevBuf active[2];  // m u32 each
+    DevBuf order[2];   // m u32: active positions sorted by pod class = the scoring kernel's thread -> pod map
+    DevBuf inv[2];     // m u32: inverse of order (position -> slot), for proposals that arrive by slot
+    DevBuf pod_cls;    // m u8: eval_pair class of each pod
+    bool want_order = false;   // this run sorts its scoring order by class (the in-library loops do)
+    bool order_valid = false;  // order[cur] / inv[cur] describe active[cur]
     DevBuf best_key;   // m u64, indexed by active position
     DevBuf best;       // m i32, indexed by active position
     DevBuf sort_keys, sort_vals;  // m u32
@@ -103,7 +108,7 @@ struct ReconcileState {
     uint64_t in_off[6] = {}, out_off[12] = {};  // element offsets of the sections (out_off[11] = total)
     uint64_t create_cap = 0;                     // elements reserved for create_ordinal (sum of desired)
     DevBuf lut;       // owner id -> pool row, built at upload
-    DevBuf pool_tmp;  // kvict[P] | span_words[P] | word_off[P+1] | remaining[P] | seen[P] | cand_off[P+1]
+    DevBuf pool_tmp;  // kvict[P] | span_words[P] | word_off[P+1] | need[P] | cand_cnt[P] | cand_off[P+1] | bits[P/32+1]
     DevBuf tot;       // small path: per-CTA member counts, pool major [P][G]
     DevBuf bitmap;    // used-ordinal bits of the pools that scale up
     DevBuf sort_keys, sort_vals;  // general path: (pool, row) pairs
@@ -116,7 +121,7 @@ struct ReconcileState {
     int small_occ = 0;                      // occupancy of the one-launch kernel at small_occ_smem bytes (0 = not queried)
     size_t small_occ_smem = 0;
     bool small_attr_set = false;
-    int prune_occ = 0;
+    bool prune_attr_set = false;
     uint32_t last_path = 0, last_grid = 0, last_segments = 0, last_candidates = 0;  // what the last run used
 };
 
@@ -133,6 +138,8 @@ struct Tuning {
     int rec_segments = -1;  // row segments of the pruned ranking pass
     int coop_prof = 0, rec_prof = 0;  // print phase times (stderr)
     int shard_admit = -1;   // multi-GPU: 1 = admission sharded by node range, 0 = replicated
+    int order = -1;         // 0: do not sort the scoring order by pod class
+    int force_cls = -1;     // timing experiments only: eval_pair class for every warp (results are wrong)
     int exchange = -1;      // multi-GPU: 0 = NCCL all-gather, 1 = peer stores, -1 = per round by list length
 };
 

@@ -347,6 +347,7 @@ int group_place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, const k8sgpu_g
         K8S_DEV(ctx, c);
         if (c != ctx) reset_call_stats(c);
         if (gangs) rc = gang_setup(c, gangs, c->stream);
+        c->place.want_order = true;  // slots of the class-sorted scoring order are what the ranks share out
         if (!rc) rc = round_begin(c, policy, c->stream);
         if (rc) return lift(ctx, c, rc);
     }

@@ -47,32 +47,58 @@ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
 
 // ------------------------------------------------------------------ table preparation
 
-__global__ void pod_prep_kernel(const uint32_t *__restrict__ cols, uint32_t m, uint32_t n_nodes, uint32_t policy,
-                                int mul_masks, PodQ *__restrict__ podq, int32_t *__restrict__ assign,
-                                uint32_t *__restrict__ active, uint32_t *__restrict__ err) {
+// Also: the pod's eval_pair class (bit 0: restricts SKUs or zones, bit 1: prefers a zone) in
+// pod_cls[p], and -- when the run sorts its scoring order by class -- flags0[p] = 1 + class and the
+// per-class counts of this block's 256 pods in chunk_tot[block] (see class_partition_tile).
+__global__ void __launch_bounds__(256) pod_prep_kernel(const uint32_t *__restrict__ cols, uint32_t m, uint32_t n_nodes,
+                                                       uint32_t policy, int mul_masks, PodQ *__restrict__ podq,
+                                                       int32_t *__restrict__ assign, uint32_t *__restrict__ active,
+                                                       uint32_t *__restrict__ err, uint8_t *__restrict__ pod_cls,
+                                                       uint32_t *__restrict__ flags0,
+                                                       unsigned long long *__restrict__ chunk_tot) {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= m) return;
-    PodQ q;
-    q.req_gpu = cols[0 * (size_t)m + p];
-    q.req_mcpu = cols[1 * (size_t)m + p];
-    q.req_mib = cols[2 * (size_t)m + p];
-    q.nsku = ~cols[3 * (size_t)m + p];
-    q.nzone = __brev(~cols[4 * (size_t)m + p]);  // bit-reversed, like NodeQ::zone_bit
-    if (mul_masks) {  // eval_pair RES = 4: each mask is mirrored against its node-side one-hot word
-        q.nsku = __brev(q.nsku);
-        q.nzone = __brev(q.nzone);
+    uint32_t cls = 4;  // 4 = no pod here
+    if (p < m) {
+        PodQ q;
+        q.req_gpu = cols[0 * (size_t)m + p];
+        q.req_mcpu = cols[1 * (size_t)m + p];
+        q.req_mib = cols[2 * (size_t)m + p];
+        q.nsku = ~cols[3 * (size_t)m + p];
+        q.nzone = __brev(~cols[4 * (size_t)m + p]);  // bit-reversed, like NodeQ::zone_bit
+        if (mul_masks) {  // eval_pair RES = 4: each mask is mirrored against its node-side one-hot word
+            q.nsku = __brev(q.nsku);
+            q.nzone = __brev(q.nzone);
+        }
+        q.ntol = ~cols[5 * (size_t)m + p];
+        uint32_t pz = cols[6 * (size_t)m + p];
+        q.pzb = pz < 32u ? (1u << pz) : 0u;
+        q.rot = ((policy & K8SGPU_POLICY_ROT_ZERO) || n_nodes == 0)
+                    ? 0u
+                    : (uint32_t)(mix64((uint64_t)p + 0x9E3779B97F4A7C15ull) % (uint64_t)n_nodes);
+        if ((q.req_gpu | q.req_mcpu | q.req_mib) & 0x80000000u) atomicOr(err, kErrPod);
+        if (pz >= 32u && pz != K8SGPU_NONE_U32) atomicOr(err, kErrPod);
+        podq[p] = q;
+        assign[p] = K8SGPU_ASSIGN_PENDING;
+        active[p] = p;
+        cls = ((q.nsku | q.nzone) ? 1u : 0u) | (q.pzb ? 2u : 0u);
+        pod_cls[p] = (uint8_t)cls;
+        if (flags0) flags0[p] = 1u + cls;
     }
-    q.ntol = ~cols[5 * (size_t)m + p];
-    uint32_t pz = cols[6 * (size_t)m + p];
-    q.pzb = pz < 32u ? (1u << pz) : 0u;
-    q.rot = ((policy & K8SGPU_POLICY_ROT_ZERO) || n_nodes == 0)
-                ? 0u
-                : (uint32_t)(mix64((uint64_t)p + 0x9E3779B97F4A7C15ull) % (uint64_t)n_nodes);
-    if ((q.req_gpu | q.req_mcpu | q.req_mib) & 0x80000000u) atomicOr(err, kErrPod);
-    if (pz >= 32u && pz != K8SGPU_NONE_U32) atomicOr(err, kErrPod);
-    podq[p] = q;
-    assign[p] = K8SGPU_ASSIGN_PENDING;
-    active[p] = p;
+    if (!chunk_tot) return;  // (block-uniform)
+    // (ballots + shared counters, not four __syncthreads_count in a row: back-to-back barrier
+    // reductions raised "illegal instruction" in the admission kernel on B200)
+    __shared__ uint32_t ccnt[4];
+    if (threadIdx.x < 4) ccnt[threadIdx.x] = 0;
+    __syncthreads();
+#pragma unroll
+    for (uint32_t k = 0; k < 4; ++k) {
+        const uint32_t mk = __ballot_sync(0xFFFFFFFFu, cls == k);
+        if ((threadIdx.x & 31u) == 0 && mk) atomicAdd(&ccnt[k], (uint32_t)__popc(mk));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+        chunk_tot[blockIdx.x] = (unsigned long long)ccnt[0] | ((unsigned long long)ccnt[1] << 16) |
+                                ((unsigned long long)ccnt[2] << 32) | ((unsigned long long)ccnt[3] << 48);
 }
 
 __device__ __forceinline__ NodeQ make_nodeq(const uint32_t *__restrict__ cols, const uint32_t *__restrict__ freec,
@@ -164,11 +190,73 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
 // RES = 3: as 2, and the zone-preference bit comes from two multiplies instead of a funnel shift:
 //          pzb * zone_bit = 2^(31 + pref - zone) has bit 31 set exactly when pref == zone, and
 //          mul.hi by 2^8 brings that bit to position 7.  7 ALU + 6 FMA-pipe ops per eval.
-template <int RES>
+// CLS (RES = 4 only) drops clauses that cannot matter for ANY pod of the calling warp -- the host
+// sorts each round's scoring order by pod class so that most warps are uniform:
+//   bit 0: some pod restricts SKUs or zones (else the two mask multiplies and their OR go: -3)
+//   bit 1: some pod prefers a zone         (else the funnel shift and the key LOP3 go:      -2)
+// A pod without the feature has an all-zero mask / one-hot word, for which the dropped instructions
+// compute the identity, so every CLS gives the same bits as CLS = 3 for the pods it is used on.
+template <int RES, int CLS = 3>
 __device__ __forceinline__ void eval_pair(const uint4 &a, const uint4 &b, uint32_t rg, uint32_t rc, uint32_t rm,
                                           uint32_t nsku, uint32_t nzone, uint32_t ntol, uint32_t pzb,
                                           uint32_t &best, uint32_t negone) {
-    if (RES == 0) {
+    if (RES == 4 && CLS == 0) {  // 9 instructions: 5 ALU + 4 FMA-pipe
+        asm("{\n\t"
+            ".reg .pred pf;\n\t"
+            ".reg .b32 m, d1, d2, d3;\n\t"
+            "mad.lo.s32 d1, %5, %8, %1;\n\t"
+            "mad.lo.s32 d2, %6, %8, %2;\n\t"
+            "mad.lo.s32 d3, %7, %8, %3;\n\t"
+            "and.b32 m, %4, %10;\n\t"
+            "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t"
+            "setp.eq.u32 pf, m, 0;\n\t"
+            "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
+            "setp.gt.and.u32 pf, %11, %0, pf;\n\t"
+            "@pf mad.lo.u32 %0, %11, %9, 0;\n\t"
+            "}"
+            : "+r"(best)
+            : "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.y), "r"(rg), "r"(rc), "r"(rm), "r"(negone), "r"(0u - negone),
+              "r"(ntol), "r"(b.z));
+    } else if (RES == 4 && CLS == 2) {  // 11: no mask multiplies
+        asm("{\n\t"
+            ".reg .pred pf;\n\t"
+            ".reg .b32 m, z, key, d1, d2, d3;\n\t"
+            "mad.lo.s32 d1, %5, %8, %1;\n\t"
+            "mad.lo.s32 d2, %6, %8, %2;\n\t"
+            "mad.lo.s32 d3, %7, %8, %3;\n\t"
+            "and.b32 m, %4, %10;\n\t"
+            "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t"
+            "setp.eq.u32 pf, m, 0;\n\t"
+            "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
+            "shf.r.wrap.b32 z, %12, %12, %13;\n\t"
+            "lop3.b32 key, z, 0x80, %11, 0xEA;\n\t"
+            "setp.gt.and.u32 pf, key, %0, pf;\n\t"
+            "@pf mad.lo.u32 %0, key, %9, 0;\n\t"
+            "}"
+            : "+r"(best)
+            : "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.y), "r"(rg), "r"(rc), "r"(rm), "r"(negone), "r"(0u - negone),
+              "r"(ntol), "r"(b.z), "r"(pzb), "r"(b.w));
+    } else if (RES == 4 && CLS == 1) {  // 12: no zone-preference bit
+        asm("{\n\t"
+            ".reg .pred pf;\n\t"
+            ".reg .b32 m, d1, d2, d3, d4, d5;\n\t"
+            "mad.lo.s32 d1, %5, %8, %1;\n\t"
+            "mad.lo.s32 d2, %6, %8, %2;\n\t"
+            "mad.lo.s32 d3, %7, %8, %3;\n\t"
+            "mul.lo.u32 d4, %12, %13;\n\t"
+            "mul.lo.u32 d5, %14, %15;\n\t"
+            "and.b32 m, %4, %10;\n\t"
+            "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t"
+            "setp.eq.u32 pf, m, 0;\n\t"
+            "lop3.b32 d1, d1, d4, d5, 0xFE;\n\t"
+            "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
+            "setp.gt.and.u32 pf, %11, %0, pf;\n\t"
+            "@pf mad.lo.u32 %0, %11, %9, 0;\n\t"
+            "}"
+            : "+r"(best)
+            : "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.y), "r"(rg), "r"(rc), "r"(rm), "r"(negone), "r"(0u - negone),
+              "r"(ntol), "r"(b.z), "r"(nsku), "r"(a.w), "r"(nzone), "r"(b.x));
+    } else if (RES == 0) {
         asm("{\n\t"
             ".reg .pred pf;\n\t"
             ".reg .b32 m, z, key;\n\t"
@@ -296,7 +384,8 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
                                                     uint32_t tiles_per_split, const PodQ *__restrict__ podq,
                                                     const uint32_t *__restrict__ active, uint32_t lo, uint32_t hi,
                                                     unsigned long long *__restrict__ best_key, uint32_t n_nodes,
-                                                    int use_atomic, uint32_t negone) {
+                                                    int use_atomic, uint32_t negone, int cls_force,
+                                                    const uint32_t *__restrict__ order) {
     // kStages-deep ring of node tiles.  full[b]: the TMA copy into buffer b has landed (one
     // arrival + its byte count); empty[b]: all 8 warps are done reading buffer b (one arrival per
     // warp).  No __syncthreads in the tile loop: a warp may run a tile ahead of its slowest sibling.
@@ -327,17 +416,28 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
     uint32_t best[PPT], bestn[PPT];
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
-        pos[j] = lo + (blockIdx.x * PPT + j) * 256u + tid;
+        // thread -> active position: straight, or through the round's class-sorted scoring order
+        const uint32_t slot = lo + (blockIdx.x * PPT + j) * 256u + tid;
+        pos[j] = slot < hi ? (order ? __ldg(&order[slot]) : slot) : 0xFFFFFFFFu;
         best[j] = 0;
         bestn[j] = 0;
-        if (pos[j] < hi) {
+        if (slot < hi) {
             const uint4 *q = reinterpret_cast<const uint4 *>(podq + active[pos[j]]);
             uint4 a = __ldg(q), b = __ldg(q + 1);
             rg[j] = a.x; rc[j] = a.y; rm[j] = a.z; nsku[j] = a.w;
             nzone[j] = b.x; ntol[j] = b.y; pzb[j] = b.z; rot[j] = b.w;
-        } else {  // idle lane: nothing is ever feasible
-            rg[j] = 0x7FFFFFFFu; rc[j] = rm[j] = 0; nsku[j] = nzone[j] = ntol[j] = 0xFFFFFFFFu; pzb[j] = 0; rot[j] = 0;
+        } else {  // idle lane: no node has 2^31 - 1 free GPUs, so nothing is ever feasible (and its class is 0)
+            rg[j] = 0x7FFFFFFFu; rc[j] = rm[j] = 0; nsku[j] = nzone[j] = 0; ntol[j] = 0xFFFFFFFFu; pzb[j] = 0; rot[j] = 0;
         }
+    }
+    // Class of this warp's pods (see eval_pair): which clauses can be left out of the inner loop.
+    uint32_t wcls = 3;
+    if (RES == 4) {
+        uint32_t mine = 0;
+#pragma unroll
+        for (int j = 0; j < PPT; ++j) mine |= ((nsku[j] | nzone[j]) ? 1u : 0u) | (pzb[j] ? 2u : 0u);
+        wcls = __reduce_or_sync(0xFFFFFFFFu, mine);
+        if (cls_force >= 0 && cls_force < 4) wcls = (uint32_t)cls_force;  // timing experiments only
     }
 
     for (uint32_t t = t0; t < t1; ++t) {
@@ -360,17 +460,24 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
 #pragma unroll
             for (int j = 0; j < PPT; ++j) gx |= (rrel[j] - g) < kGroup;
             if (!__any_sync(0xFFFFFFFFu, gx)) {  // common case: 64 evals per pod, no checks at all
-#pragma unroll 1
-                for (uint32_t kb = g; kb < g + kGroup; kb += 16) {
-#pragma unroll
-                    for (uint32_t i = 0; i < 16; ++i) {
-                        const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];
-#pragma unroll
-                        for (int j = 0; j < PPT; ++j)
-                            eval_pair<RES>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j],
-                                           negone);
-                    }
+#define K8S_GROUP(CLS)                                                                                           \
+    _Pragma("unroll 1") for (uint32_t kb = g; kb < g + kGroup; kb += 16) {                                       \
+        _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
+            const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];                                          \
+            _Pragma("unroll") for (int j = 0; j < PPT; ++j)                                                      \
+                eval_pair<RES, CLS>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j], negone); \
+        }                                                                                                        \
+    }
+                if (RES != 4 || wcls == 3) {
+                    K8S_GROUP(3)
+                } else if (wcls == 0) {
+                    K8S_GROUP(0)
+                } else if (wcls == 2) {
+                    K8S_GROUP(2)
+                } else {
+                    K8S_GROUP(1)
                 }
+#undef K8S_GROUP
             } else {
 #pragma unroll 1
                 for (uint32_t kb = g; kb < g + kGroup; kb += 8) {
@@ -432,7 +539,7 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
 
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
-        if (pos[j] >= hi) continue;
+        if (pos[j] == 0xFFFFFFFFu) continue;
         unsigned long long key64 = 0ull;
         if (best[j] != 0u) {
             // strip the index bits and undo a crossing decrement: the spec's upper key bits
@@ -448,40 +555,39 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
     }
 }
 
-__global__ void score_finalize_kernel(const unsigned long long *__restrict__ best_key, const PodQ *__restrict__ podq,
-                                      const uint32_t *__restrict__ active, uint32_t lo, uint32_t cnt,
-                                      uint32_t n_nodes, int32_t *__restrict__ out) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= cnt) return;
-    unsigned long long key = best_key[lo + i];
-    int32_t node = -1;
-    if (key != 0ull) {
-        uint32_t ridx = 0xFFFFFFFFu - (uint32_t)key;
-        uint32_t rot = podq[active[lo + i]].rot;
-        uint32_t n = ridx + rot;  // < 2N < 2^32
-        node = (int32_t)(n >= n_nodes ? n - n_nodes : n);
-    }
-    out[i] = node;
+// Proposals travel by SLOT (the index the scoring kernel's threads are numbered by): slot i of
+// [lo, lo + cnt) belongs to active position order[lo + i], or to position lo + i without an order.
+__device__ __forceinline__ int32_t decode_proposal(const unsigned long long *__restrict__ best_key,
+                                                   const PodQ *__restrict__ podq, const uint32_t *__restrict__ active,
+                                                   const uint32_t *__restrict__ order, uint32_t slot, uint32_t n_nodes) {
+    const uint32_t pos = order ? __ldg(&order[slot]) : slot;
+    const unsigned long long key = best_key[pos];
+    if (key == 0ull) return -1;
+    const uint32_t n = (0xFFFFFFFFu - (uint32_t)key) + podq[active[pos]].rot;  // < 2N < 2^32
+    return (int32_t)(n >= n_nodes ? n - n_nodes : n);
 }
 
-// Decode the packed best key of active positions [lo, lo+cnt) and store the proposal straight
-// into EVERY rank's exchange buffer (peer stores over NVLink; the own buffer is just another
-// pointer): the all-gather of the round is done by the kernel that produces the values.
+__global__ void score_finalize_kernel(const unsigned long long *__restrict__ best_key, const PodQ *__restrict__ podq,
+                                      const uint32_t *__restrict__ active, const uint32_t *__restrict__ order,
+                                      uint32_t lo, uint32_t cnt, uint32_t n_nodes, int32_t *__restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < cnt) out[i] = decode_proposal(best_key, podq, active, order, lo + i, n_nodes);
+}
+
+// Decode the packed best key of slots [lo, lo+cnt) and store the proposal straight into EVERY
+// rank's exchange buffer (peer stores over NVLink; the own buffer is just another pointer): the
+// all-gather of the round is done by the kernel that produces the values.
 struct PeerPtrs {
     int32_t *p[16];
     int world;
 };
 __global__ void score_finalize_p2p_kernel(const unsigned long long *__restrict__ best_key,
                                           const PodQ *__restrict__ podq, const uint32_t *__restrict__ active,
-                                          uint32_t lo, uint32_t cnt, uint32_t n_nodes, PeerPtrs peers) {
+                                          const uint32_t *__restrict__ order, uint32_t lo, uint32_t cnt,
+                                          uint32_t n_nodes, PeerPtrs peers) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= cnt) return;
-    unsigned long long key = best_key[lo + i];
-    int32_t node = -1;
-    if (key != 0ull) {
-        uint32_t n = (0xFFFFFFFFu - (uint32_t)key) + podq[active[lo + i]].rot;
-        node = (int32_t)(n >= n_nodes ? n - n_nodes : n);
-    }
+    const int32_t node = decode_proposal(best_key, podq, active, order, lo + i, n_nodes);
 #pragma unroll 1
     for (int r = 0; r < peers.world; ++r) peers.p[r][lo + i] = node;
 }
@@ -677,6 +783,112 @@ __global__ void count_placed_kernel(const int32_t *__restrict__ assign, uint32_t
     if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(out, cnt);
 }
 
+// ------------------------------------------------------------------ scoring order by pod class
+//
+// eval_pair leaves out the clauses no pod of a warp needs (its CLS parameter), which only pays if
+// warps are uniform.  So each round's scoring kernel walks the active list through `order`: the
+// active positions sorted by pod class (0..3), stable inside a class.  The order is built where
+// the next active list is built, from the same per-chunk counts: flags[i] = 0 (settled) or
+// 1 + class of the pod at active position i; chunk_tot[c] = pending pods of chunk c (256
+// positions) per class, four 16-bit fields.  One CTA handles one tile of 2048 positions: it sums the
+// chunk counts before its tile (and all of them, for the class bases), scans its own tile with one
+// 64-bit scan (the four class counts side by side), and writes
+//   next_active[q] = pod       q = stable position among the pending pods (pod order kept)
+//   order[o] = q, inv[q] = o   o = class base + rank inside the class
+// Admission order is untouched (next_active stays in pod order); only which THREAD scores which
+// pod changes.  Returns the number of pending pods up to and including this tile (all threads).
+__device__ __forceinline__ uint32_t class_partition_tile(uint32_t vt, uint32_t na, const uint32_t *flags,
+                                                         const uint32_t *active, const unsigned long long *chunk_tot,
+                                                         uint32_t *next_active, uint32_t *order, uint32_t *inv) {
+    __shared__ uint32_t psum[8][8];
+    __shared__ unsigned long long wtot64[8];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t nchunks = (na + 255u) / 256u, first = vt * (kScanTile / 256u);
+    uint32_t bef[4] = {0, 0, 0, 0}, tot[4] = {0, 0, 0, 0};
+    for (uint32_t c = tid; c < nchunks; c += 256u) {
+        const unsigned long long x = __ldcg(&chunk_tot[c]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t v = (uint32_t)(x >> (16 * k)) & 0xFFFFu;
+            tot[k] += v;
+            bef[k] += c < first ? v : 0u;
+        }
+    }
+    const uint32_t i0 = vt * kScanTile + tid * 8u;
+    uint32_t f[8], act[8];
+    unsigned long long mine = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const bool in = i0 + k < na;
+        f[k] = in ? flags[i0 + k] : 0u;
+        act[k] = in ? active[i0 + k] : 0u;
+        if (f[k]) mine += 1ull << (16u * (f[k] - 1u));
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        bef[k] = __reduce_add_sync(0xFFFFFFFFu, bef[k]);
+        tot[k] = __reduce_add_sync(0xFFFFFFFFu, tot[k]);
+    }
+    unsigned long long inc = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if ((int)lane >= d) inc += y;
+    }
+    __syncthreads();  // shared scratch of the previous tile / phase is no longer read
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            psum[warp][k] = bef[k];
+            psum[warp][4 + k] = tot[k];
+        }
+    }
+    if (lane == 31) wtot64[warp] = inc;
+    __syncthreads();
+    unsigned long long woff = 0, tile = 0;
+#pragma unroll
+    for (uint32_t w = 0; w < 8; ++w) {
+        const unsigned long long t = wtot64[w];
+        if (w < warp) woff += t;
+        tile += t;
+    }
+    uint32_t base[4], before_all = 0, acc = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        uint32_t b = 0, t = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            b += psum[w][k];
+            t += psum[w][4 + k];
+        }
+        before_all += b;
+        base[k] = acc + b;  // class base (all pods of lower classes) + pods of this class before the tile
+        acc += t;
+    }
+    unsigned long long excl = woff + inc - mine;  // per class: pending pods of this tile before this thread
+    uint32_t q = before_all + (uint32_t)(excl & 0xFFFFu) + (uint32_t)((excl >> 16) & 0xFFFFu) +
+                 (uint32_t)((excl >> 32) & 0xFFFFu) + (uint32_t)(excl >> 48);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if (!f[k]) continue;
+        const uint32_t c = f[k] - 1u;
+        const uint32_t o = base[c] + (uint32_t)((excl >> (16u * c)) & 0xFFFFu);
+        next_active[q] = act[k];
+        order[o] = q;
+        inv[q] = o;
+        excl += 1ull << (16u * c);
+        ++q;
+    }
+    return before_all + (uint32_t)(tile & 0xFFFFu) + (uint32_t)((tile >> 16) & 0xFFFFu) +
+           (uint32_t)((tile >> 32) & 0xFFFFu) + (uint32_t)(tile >> 48);
+}
+
+// Round 0: every pod is active at its own index.  flags / chunk counts come from pod_prep_kernel.
+__global__ void __launch_bounds__(256) order0_kernel(uint32_t m, const uint32_t *flags, uint32_t *active,
+                                                     const unsigned long long *chunk_tot, uint32_t *order, uint32_t *inv) {
+    class_partition_tile(blockIdx.x, m, flags, active, chunk_tot, active, order, inv);
+}
+
 // ------------------------------------------------------------------ admission, one launch
 //
 // The admission step above is ~20 small dependent kernels (each a few microseconds of launch and
@@ -687,7 +899,10 @@ __global__ void count_placed_kernel(const int32_t *__restrict__ assign, uint32_t
 struct AdmitArgs {
     const unsigned long long *best_key;  // by active position (score_kernel output)
     unsigned long long *best_key_clear;  // the same array: cleared at the end for the next round's atomicMax
-    const int32_t *proposals;            // or: node row per active position (exchanged between GPUs); else null
+    const int32_t *proposals;            // or: node row per scoring slot (exchanged between GPUs); else null
+    const uint32_t *inv_cur;             // active position -> scoring slot of this round (null: identity)
+    const uint8_t *pod_cls;              // eval_pair class per pod
+    uint32_t *order_next, *inv_next;     // next round's scoring order and its inverse (null: not built)
     const PodQ *podq;
     const uint32_t *active;
     uint32_t *next_active;
@@ -733,7 +948,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
             uint32_t i = vt * kSortTile + r * 256 + tid;
             pod[r] = i < na ? a.active[i] : 0u;
             if (a.proposals) {  // already decoded: re-encode as "distance 0 from rot = node" below
-                int32_t b = i < na ? a.proposals[i] : -1;
+                int32_t b = i < na ? a.proposals[a.inv_cur ? a.inv_cur[i] : i] : -1;  // proposals arrive by slot
                 if (b < -1 || b >= (int32_t)N) {  // not something score_kernel can produce: a stale or
                     atomicOr(&a.counters[0], kErrProposal);  // unsynchronised buffer was handed in
                     b = -1;
@@ -835,7 +1050,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
     const uint32_t nt = (na + kScanTile - 1) / kScanTile, nchunks = (na + 255u) / 256u;
     const bool local_scan = nt <= kLocalScanMaxTiles;
     uint32_t *chunk_tot = a.hist_scan;
-    __shared__ uint32_t red[8];
+    __shared__ uint32_t red[8], ccnt[4];
     for (uint32_t c = cta; c < nchunks; c += G) {
         const uint32_t i = c * 256 + tid;
         uint32_t f = 0;
@@ -851,14 +1066,50 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
                 if (rm) atomicSub(&a.freec[2 * (size_t)N + key], rm);
             }
             f = state == K8SGPU_ASSIGN_PENDING ? 1u : 0u;
+            if (a.order_next && f) f += a.pod_cls[pod_here];  // 1 + class (see class_partition_tile)
             a.flags[i] = f;
         }
-        const uint32_t cnt = (uint32_t)__syncthreads_count((int)f);
-        if (tid == 0) chunk_tot[c] = cnt;
+        if (a.order_next) {  // pending pods of the chunk per class, four 16-bit fields
+            // (ballots + shared counters: four __syncthreads_count in a row raised "illegal
+            // instruction" here on B200)
+            if (tid < 4) ccnt[tid] = 0;
+            __syncthreads();
+#pragma unroll
+            for (uint32_t k = 0; k < 4; ++k) {
+                const uint32_t mk = __ballot_sync(0xFFFFFFFFu, f == k + 1u);
+                if ((tid & 31u) == 0 && mk) atomicAdd(&ccnt[k], (uint32_t)__popc(mk));
+            }
+            __syncthreads();
+            if (tid == 0)
+                reinterpret_cast<unsigned long long *>(chunk_tot)[c] =
+                    (unsigned long long)ccnt[0] | ((unsigned long long)ccnt[1] << 16) |
+                    ((unsigned long long)ccnt[2] << 32) | ((unsigned long long)ccnt[3] << 48);
+            __syncthreads();  // ccnt is reused by the next chunk
+        } else {
+            const uint32_t cnt = (uint32_t)__syncthreads_count((int)f);
+            if (tid == 0) chunk_tot[c] = cnt;
+        }
     }
     grid.sync();
     prof_mark(a, 6);
-    if (local_scan) {
+    if (a.order_next) {
+        // Next active list (stable, pod order) and next scoring order (by class) in one pass over
+        // each tile; the CTA that owns the last tile knows the next round's length and tells the host.
+        for (uint32_t vt = cta; vt < nt; vt += G) {
+            const uint32_t upto = class_partition_tile(vt, na, a.flags, a.active,
+                                                       reinterpret_cast<const unsigned long long *>(chunk_tot),
+                                                       a.next_active, a.order_next, a.inv_next);
+            if (vt == nt - 1 && tid == 0) {
+                a.counters[1] = upto;
+                volatile uint32_t *mb = a.mailbox;
+                mb[1] = upto;
+                mb[2] = a.counters[0];
+                __threadfence_system();
+                mb[0] = a.seq;
+            }
+        }
+        prof_mark(a, 7);
+    } else if (local_scan) {
         // Stable compaction without a scan phase: each CTA adds up the pending counts of the tiles
         // before its own, scans its tile in registers and writes the survivors.  The CTA that owns
         // the last tile knows the next round's length and tells the host before it scatters.
@@ -992,6 +1243,11 @@ int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_p
     K8S_CUDA(ctx, st.assign.reserve(m * 4 + 16));
     K8S_CUDA(ctx, st.active[0].reserve(m * 4 + 16));
     K8S_CUDA(ctx, st.active[1].reserve(m * 4 + 16));
+    for (int b = 0; b < 2; ++b) {
+        K8S_CUDA(ctx, st.order[b].reserve(m * 4 + 16));
+        K8S_CUDA(ctx, st.inv[b].reserve(m * 4 + 16));
+    }
+    K8S_CUDA(ctx, st.pod_cls.reserve(m + 16));
     K8S_CUDA(ctx, st.best_key.reserve(m * 8 + 16));
     K8S_CUDA(ctx, st.best.reserve(m * 4 + 16));
     K8S_CUDA(ctx, st.sort_keys.reserve(m * 4 + 16));
@@ -1028,10 +1284,24 @@ int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
     K8S_CUDA(ctx, cudaMemsetAsync(st.counters.p, 0, 64 * 4, s));
     if (st.n)
         K8S_CUDA(ctx, cudaMemcpyAsync(st.free_cols.p, st.node_cols.p, 3 * (size_t)st.n * 4, cudaMemcpyDeviceToDevice, s));
-    if (st.m)
+    // Scoring order by pod class: only with the class-specialised eval_pair (RES = 4) and the
+    // one-launch admission, which rebuilds the order each round next to the active list.
+    const bool ordered = st.want_order && st.score_res == 4 && coop_admission(ctx) && ctx->tune.order != 0 && st.m > 0;
+    st.order_valid = false;
+    if (st.m) {
+        const uint32_t nb = ceil_div(st.m, kSortTile);
+        unsigned long long *chunk_tot = reinterpret_cast<unsigned long long *>(st.sort.hist.as<uint32_t>() + (size_t)nb * 256);
+        uint32_t *flags0 = st.flags.as<uint32_t>();
         K8S_LAUNCH(ctx, pod_prep_kernel, ceil_div(st.m, 256), 256, 0, s, st.pod_cols.as<uint32_t>(), st.m, st.n,
                    st.policy_flags, st.score_res == 4 ? 1 : 0, st.podq.as<PodQ>(), st.assign.as<int32_t>(),
-                   st.active[0].as<uint32_t>(), st.counters.as<uint32_t>());
+                   st.active[0].as<uint32_t>(), st.counters.as<uint32_t>(), st.pod_cls.as<uint8_t>(),
+                   ordered ? flags0 : nullptr, ordered ? chunk_tot : nullptr);
+        if (ordered) {
+            K8S_LAUNCH(ctx, order0_kernel, ceil_div(st.m, kScanTile), 256, 0, s, st.m, flags0, st.active[0].as<uint32_t>(),
+                       chunk_tot, st.order[0].as<uint32_t>(), st.inv[0].as<uint32_t>());
+            st.order_valid = true;
+        }
+    }
     return K8SGPU_OK;
 }
 
@@ -1077,16 +1347,21 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     }
     const int use_atomic = splits > 1;
     unsigned long long *bk = st.best_key.as<unsigned long long>();
-    if (use_atomic && !(st.best_cleared_len >= hi))  // (the single-launch admission leaves it cleared)
-        K8S_CUDA(ctx, cudaMemsetAsync(bk + lo, 0, (size_t)cnt * 8, s));
+    if (use_atomic && !(st.best_cleared_len >= (st.order_valid ? st.n_active : hi))) {  // (the single-launch admission leaves it cleared)
+        if (st.order_valid)  // slots [lo, hi) are scattered positions: clear the whole list
+            K8S_CUDA(ctx, cudaMemsetAsync(bk, 0, (size_t)st.n_active * 8, s));
+        else
+            K8S_CUDA(ctx, cudaMemsetAsync(bk + lo, 0, (size_t)cnt * 8, s));
+    }
     st.best_cleared_len = 0;
+    const uint32_t *order = st.order_valid ? st.order[st.cur].as<uint32_t>() : nullptr;  // class-sorted scoring order
     const bool timed = st.timed < kMaxTimedRounds;  // (the two event records cost ~4 us per round)
     if (timed) K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed], s));
     dim3 grid(xb, splits);
     const int res = st.score_res;  // fixed at round_begin: the pod records are laid out for it
 #define K8S_SCORE(P, R, B)                                                                                         \
     K8S_LAUNCH(ctx, (score_kernel<P, R, B>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
-               st.active[st.cur].as<uint32_t>(), lo, hi, bk, st.n, use_atomic, 0xFFFFFFFFu)
+               st.active[st.cur].as<uint32_t>(), lo, hi, bk, st.n, use_atomic, 0xFFFFFFFFu, ctx->tune.force_cls, order)
     // third argument: resident CTAs per SM the register budget is set for (measured best per variant)
     if (ppt == 4) K8S_SCORE(4, 4, 3);
     else if (ppt == 2 && res >= 4) K8S_SCORE(2, 4, 4);
@@ -1107,7 +1382,7 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     }
     if (finalize)
         K8S_LAUNCH(ctx, score_finalize_kernel, ceil_div(cnt, 256), 256, 0, s, bk, st.podq.as<PodQ>(),
-                   st.active[st.cur].as<uint32_t>(), lo, cnt, st.n, d_best);
+                   st.active[st.cur].as<uint32_t>(), order, lo, cnt, st.n, d_best);
     return K8SGPU_OK;
 }
 
@@ -1157,6 +1432,7 @@ int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t s, uint
     st.cur ^= 1;
     st.n_active = ctx->h_pinned[1];
     st.nodeq_stale = true;  // the free columns changed under the packed node records
+    st.order_valid = false; // (this path does not rebuild the class-sorted scoring order)
     if (n_active_out) *n_active_out = st.n_active;
     return K8SGPU_OK;
 }
@@ -1180,6 +1456,10 @@ int round_admit_coop_launch(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *prop
     a.best_key = st.best_key.as<unsigned long long>();
     a.best_key_clear = st.best_key.as<unsigned long long>();
     a.proposals = proposals;
+    a.inv_cur = st.order_valid ? st.inv[st.cur].as<uint32_t>() : nullptr;
+    a.pod_cls = st.pod_cls.as<uint8_t>();
+    a.order_next = st.order_valid ? st.order[st.cur ^ 1].as<uint32_t>() : nullptr;
+    a.inv_next = st.order_valid ? st.inv[st.cur ^ 1].as<uint32_t>() : nullptr;
     a.podq = st.podq.as<PodQ>();
     a.active = st.active[st.cur].as<uint32_t>();
     a.next_active = st.active[st.cur ^ 1].as<uint32_t>();
@@ -1274,7 +1554,8 @@ int round_finalize_peers(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *con
     for (int r = 0; r < 16; ++r) pp.p[r] = r < world ? peer[r] : nullptr;
     pp.world = world;
     K8S_LAUNCH(ctx, score_finalize_p2p_kernel, ceil_div(hi - lo, 256), 256, 0, s, st.best_key.as<unsigned long long>(),
-               st.podq.as<PodQ>(), st.active[st.cur].as<uint32_t>(), lo, hi - lo, st.n, pp);
+               st.podq.as<PodQ>(), st.active[st.cur].as<uint32_t>(),
+               st.order_valid ? st.order[st.cur].as<uint32_t>() : nullptr, lo, hi - lo, st.n, pp);
     return K8SGPU_OK;
 }
 
@@ -1329,6 +1610,7 @@ static int run_rounds(k8sgpu_ctx *ctx, cudaStream_t s) {
 
 int place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy) {
     cudaStream_t s = ctx->stream;
+    ctx->place.want_order = true;
     K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
     int rc = round_begin(ctx, policy, s);
     if (rc) return rc;
@@ -1468,6 +1750,7 @@ int gang_verdicts(k8sgpu_ctx *ctx, cudaStream_t s, uint32_t *n_retry_out) {
     }
     st.n_active = n_retry;
     st.nodeq_stale = true;  // free columns changed under the packed records
+    st.order_valid = false; // the retry list is a new active list: scored in plain order
     if (n_retry) st.gang_iters++;
     *n_retry_out = n_retry;
     return K8SGPU_OK;
@@ -1479,6 +1762,7 @@ static int place_gang_run(k8sgpu_ctx *ctx, const k8sgpu_gang_table *gangs, const
     int rc = gang_setup(ctx, gangs, s);
     if (rc) return rc;
     K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
+    st.want_order = true;
     rc = round_begin(ctx, policy, s);
     if (rc) return rc;
     for (;;) {
@@ -1598,6 +1882,7 @@ extern "C" int k8sgpu_place_gang_begin(k8sgpu_ctx *ctx, const k8sgpu_gang_table 
     cudaStream_t s = pick_stream(ctx, stream);
     int rc = gang_setup(ctx, gangs, s);
     if (rc) return rc;
+    ctx->place.want_order = false;  // the caller exchanges proposals by active position
     rc = round_begin(ctx, policy, s);
     if (rc) return rc;
     if (n_active) *n_active = ctx->place.n_active;
@@ -1627,6 +1912,7 @@ extern "C" int k8sgpu_score_once(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, i
     cudaStream_t s = ctx->stream;
     if (!best_node && st.m) return fail(ctx, K8SGPU_E_ARG, "score_once: NULL output");
     K8S_CUDA(ctx, cudaEventRecord(ctx->ev_begin, s));
+    st.want_order = false;  // best_node[] is indexed by pod
     int rc = round_begin(ctx, policy, s);
     if (rc) return rc;
     rc = round_score(ctx, 0, st.n_active, st.best.as<int32_t>(), s);
@@ -1649,6 +1935,7 @@ extern "C" int k8sgpu_place_round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *po
     K8S_ENTER(ctx);
     reset_call_stats(ctx);
     cudaStream_t s = ::k8sgpu::pick_stream(ctx, stream);
+    ctx->place.want_order = false;  // the caller exchanges proposals by active position
     int rc = round_begin(ctx, policy, s);
     if (rc) return rc;
     if (n_active) *n_active = ctx->place.n_active;

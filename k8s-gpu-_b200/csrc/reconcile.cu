@@ -366,7 +366,10 @@ __global__ void __launch_bounds__(kSmallWarps * 32) reconcile_small_kernel(RecSm
 // ------------------------------------------------------------------ paths 1 and 2: many pools
 
 // Tag filter, 4 VM rows per thread (128-bit loads and stores when the columns are 16-byte
-// aligned), and currentCount by one RED per managed row (counts only: order-free).
+// aligned), and currentCount by one RED per managed row (counts only: order-free).  With ~10^6
+// pools the pass is bound by the L2 atomic rate (measured ~1.4 x 10^11 per second on B200), not by
+// HBM.  (Folding the owner-id gather and the count into one 64-bit atomic that returns the pool row
+// was tried: an atomic with a return value costs what the gather plus the RED cost -- no gain.)
 __global__ void __launch_bounds__(256) match_count_kernel(const uint32_t *__restrict__ owner,
                                                           const uint32_t *__restrict__ flags, uint32_t V,
                                                           uint32_t n_owner_ids, const int32_t *__restrict__ lut,
@@ -401,8 +404,8 @@ __global__ void __launch_bounds__(256) match_count_kernel(const uint32_t *__rest
 __global__ void pool_kernel(const int32_t *__restrict__ desired, uint32_t P, const int32_t *__restrict__ current,
                             int32_t *__restrict__ ready, int32_t *__restrict__ delta,
                             int32_t *__restrict__ create_count, uint32_t *__restrict__ kvict,
-                            uint32_t *__restrict__ span_words, uint32_t *__restrict__ remaining,
-                            uint32_t *__restrict__ seen, uint32_t *__restrict__ counters) {
+                            uint32_t *__restrict__ span_words, int32_t *__restrict__ need,
+                            uint32_t *__restrict__ bits, uint32_t *__restrict__ counters) {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t down = 0;
     if (p < P) {
@@ -413,12 +416,15 @@ __global__ void pool_kernel(const int32_t *__restrict__ desired, uint32_t P, con
         create_count[p] = r.create_count;
         kvict[p] = r.kvict;
         span_words[p] = r.span_words;
-        remaining[p] = r.kvict;
-        seen[p] = 0;
+        need[p] = (int32_t)r.kvict;
         down = r.kvict ? 1u : 0u;
     }
-    const uint32_t n = __popc(__ballot_sync(0xFFFFFFFFu, down));
-    if ((threadIdx.x & 31u) == 0 && n) atomicAdd(&counters[2], n);
+    // thread p of a warp holds pool p: the ballot IS word p / 32 of the "still short" bitmap
+    const uint32_t word = __ballot_sync(0xFFFFFFFFu, down);
+    if ((threadIdx.x & 31u) == 0) {
+        if (p < P) bits[p >> 5] = word;
+        if (word) atomicAdd(&counters[2], (uint32_t)__popc(word));
+    }
 }
 
 __global__ void keys_from_pool_kernel(const int32_t *__restrict__ pool_of, uint32_t V, uint32_t P,
@@ -460,56 +466,70 @@ __global__ void ordinal_mark_kernel(const int32_t *__restrict__ pool_of, uint32_
 
 // Pruning pass of path 1.  A row can only be a victim while its pool has seen fewer than
 // scaleDownCount rows, so the table is walked in S row segments, in order, and a row of segment s
-// is kept as a CANDIDATE iff its pool was still short of victims when segment s began
-// (remaining[p] > 0, a value that depends only on the counts of earlier segments).  The
-// candidates of a pool are therefore a prefix, in list order, of that pool's rows, at least
-// scaleDownCount long: their stable sort by pool yields the victims.  The pass stops at the first
-// segment boundary where no pool is short any more -- on config-2-like data after about half the
-// table, with ~10 % of the rows kept.
-//   phase 1 of a segment: candidate flags (bit mask in shared memory), seen[p] += 1 per candidate
-//   phase 2: candidates written in list order (CTA bases from the per-CTA counts), remaining[p]
-//            refreshed from seen[p]; pools that reached their count leave counters[2]
+// is kept as a CANDIDATE iff its pool was still short of victims when segment s began -- one bit
+// per pool, a value that depends only on the counts of earlier segments.  The candidates of a pool
+// are therefore a prefix, in list order, of that pool's rows, at least scaleDownCount long: their
+// stable sort by pool yields the victims.  The pass stops at the first segment boundary where no
+// pool is short any more -- on config-2-like data after about half the table, with ~8 % of the
+// rows kept.
+//   start of a segment: every CTA copies the "still short" bitmap (P bits) into shared memory, so
+//            the test of a row costs no L2 request (SMEM_BITS; pools beyond ~1.6 M: read from L2)
+//   phase 1: candidate flags (bit mask in shared memory), need[p] -= 1 per candidate (RED)
+//   phase 2: candidates written in list order (CTA bases from the per-CTA counts); a pool whose
+//            need reached 0 has its bit cleared, and whoever cleared it takes it off counters[2]
 struct PruneArgs {
     const int32_t *pool_of;
-    const uint32_t *kvict;
-    uint32_t *remaining, *seen, *cta_cnt, *cand_keys, *cand_vals, *counters;
-    uint32_t V, segments, rows_per_cta;  // rows_per_cta: multiple of 256, per segment
+    int32_t *need;     // scaleDownCount minus the pool's candidates so far (may end below 0)
+    uint32_t *bits;    // bit p: pool p is still short of victims
+    uint32_t *cta_cnt, *cand_keys, *cand_vals, *counters;
+    uint32_t V, segments, rows_per_cta /* multiple of 1024, per segment */, bit_words;
 };
+constexpr uint32_t kPruneThreads = 1024, kPruneWarps = kPruneThreads / 32;
 constexpr uint32_t kPruneMaxRowsPerCta = 65536;  // 2048 mask words
+constexpr uint32_t kPruneMaxSmemBitWords = 50 * 1024;  // 200 KB of bitmap next to 16 KB of masks: 1.6 M pools
 
-__global__ void __launch_bounds__(256) prune_kernel(PruneArgs a) {
+template <bool SMEM_BITS>
+__global__ void __launch_bounds__(kPruneThreads, 1) prune_kernel(PruneArgs a) {
     cg::grid_group grid = cg::this_grid();
-    __shared__ uint32_t mask[kPruneMaxRowsPerCta / 32];  // candidate bits: word t*8+w = rows lo + t*256 + w*32 ..
+    extern __shared__ uint32_t sbits[];                  // copy of a.bits (SMEM_BITS)
+    __shared__ uint32_t mask[kPruneMaxRowsPerCta / 32];  // candidate bits: word w = rows lo + 32 w ..
     __shared__ uint32_t wpre[kPruneMaxRowsPerCta / 32];  // candidates of this CTA before that word
-    __shared__ uint32_t red[8], red2[8];
+    __shared__ uint32_t red[kPruneWarps], red2[kPruneWarps], wtot[kPruneWarps];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5, cta = blockIdx.x, G = gridDim.x;
     const uint32_t lt = (1u << lane) - 1u;
-    const uint32_t tiles = a.rows_per_cta / 256u, words = tiles * 8u;
+    const uint32_t tiles = a.rows_per_cta / kPruneThreads, words = tiles * kPruneWarps;
     const uint64_t seg_rows = (uint64_t)a.rows_per_cta * G;
-    constexpr uint32_t U = 8;  // tiles of 256 rows whose loads are issued together
+    constexpr uint32_t U = 4;  // tiles whose loads are issued together
     uint32_t total = 0;  // candidates of all earlier segments (every CTA computes the same number)
     for (uint32_t s = 0; s < a.segments; ++s) {
         const uint64_t lo64 = (uint64_t)s * seg_rows + (uint64_t)cta * a.rows_per_cta;
         const uint32_t lo = lo64 < a.V ? (uint32_t)lo64 : a.V;
         const uint32_t hi = (uint64_t)lo + a.rows_per_cta < a.V ? lo + a.rows_per_cta : a.V;
+        if (SMEM_BITS) {
+            for (uint32_t i = tid; i < a.bit_words; i += kPruneThreads) sbits[i] = __ldcg(&a.bits[i]);
+            __syncthreads();
+        }
         uint32_t mine = 0;
         for (uint32_t t0 = 0; t0 < tiles; t0 += U) {
             int32_t p[U];
-            uint32_t rem[U];
+            bool cand[U];
 #pragma unroll
             for (uint32_t u = 0; u < U; ++u) {
-                const uint32_t v = lo + (t0 + u) * 256u + tid;
+                const uint32_t v = lo + (t0 + u) * kPruneThreads + tid;
                 p[u] = (t0 + u < tiles && v < hi) ? __ldg(&a.pool_of[v]) : -1;
             }
 #pragma unroll
-            for (uint32_t u = 0; u < U; ++u) rem[u] = p[u] >= 0 ? __ldcg(&a.remaining[p[u]]) : 0u;
+            for (uint32_t u = 0; u < U; ++u) {
+                const uint32_t w = p[u] >= 0 ? ((uint32_t)p[u] >> 5) : 0u;
+                const uint32_t word = p[u] >= 0 ? (SMEM_BITS ? sbits[w] : __ldcg(&a.bits[w])) : 0u;
+                cand[u] = (word >> ((uint32_t)p[u] & 31u)) & 1u;
+            }
 #pragma unroll
             for (uint32_t u = 0; u < U; ++u) {
-                const bool cand = rem[u] > 0u;
-                if (cand) atomicAdd(&a.seen[p[u]], 1u);
-                const uint32_t m = __ballot_sync(0xFFFFFFFFu, cand);
+                if (cand[u]) atomicSub(&a.need[p[u]], 1);
+                const uint32_t m = __ballot_sync(0xFFFFFFFFu, cand[u]);
                 if (lane == 0 && t0 + u < tiles) {
-                    mask[(t0 + u) * 8u + warp] = m;
+                    mask[(t0 + u) * kPruneWarps + warp] = m;
                     mine += (uint32_t)__popc(m);
                 }
             }
@@ -518,80 +538,65 @@ __global__ void __launch_bounds__(256) prune_kernel(PruneArgs a) {
         __syncthreads();
         if (tid == 0) {
             uint32_t c = 0;
-            for (int w = 0; w < 8; ++w) c += red[w];
+            for (uint32_t w = 0; w < kPruneWarps; ++w) c += red[w];
             a.cta_cnt[cta] = c;
         }
         grid.sync();
         // my base = candidates so far + those of the CTAs before me in this segment
         uint32_t before = 0, all = 0;
-        for (uint32_t c = tid; c < G; c += 256u) {
+        for (uint32_t c = tid; c < G; c += kPruneThreads) {
             const uint32_t x = __ldcg(&a.cta_cnt[c]);
             all += x;
             before += c < cta ? x : 0u;
         }
         before = __reduce_add_sync(0xFFFFFFFFu, before);
         all = __reduce_add_sync(0xFFFFFFFFu, all);
-        // exclusive prefix of the per-word candidate counts: thread i owns words [8i, 8i+8)
-        uint32_t wc[8], wsum = 0;
-#pragma unroll
-        for (uint32_t k = 0; k < 8; ++k) {
-            const uint32_t w = tid * 8u + k;
-            wc[k] = w < words ? (uint32_t)__popc(mask[w]) : 0u;
-            wsum += wc[k];
-        }
-        const uint32_t winc = warp_incl_scan(wsum, (int)lane);
+        // exclusive prefix of the per-word candidate counts: thread i owns words 2i and 2i + 1
+        const uint32_t w0 = tid * 2u;
+        const uint32_t c0 = w0 < words ? (uint32_t)__popc(mask[w0]) : 0u;
+        const uint32_t c1 = w0 + 1u < words ? (uint32_t)__popc(mask[w0 + 1u]) : 0u;
+        const uint32_t winc = warp_incl_scan(c0 + c1, (int)lane);
         if (lane == 0) {
             red[warp] = before;
             red2[warp] = all;
         }
-        __shared__ uint32_t wtot[8];
         if (lane == 31) wtot[warp] = winc;
         __syncthreads();
         before = all = 0;
         uint32_t woff = 0;
-        for (uint32_t k = 0; k < 8; ++k) {
+        for (uint32_t k = 0; k < kPruneWarps; ++k) {
             before += red[k];
             all += red2[k];
             woff += k < warp ? wtot[k] : 0u;
         }
-        {
-            uint32_t run = woff + winc - wsum;
-#pragma unroll
-            for (uint32_t k = 0; k < 8; ++k) {
-                const uint32_t w = tid * 8u + k;
-                if (w < words) wpre[w] = run;
-                run += wc[k];
-            }
-        }
+        if (w0 < words) wpre[w0] = woff + winc - c0 - c1;
+        if (w0 + 1u < words) wpre[w0 + 1u] = woff + winc - c1;
         __syncthreads();
         const uint32_t base = total + before;
-        constexpr uint32_t U2 = 4;
-        for (uint32_t t0 = 0; t0 < tiles; t0 += U2) {
-            bool is[U2];
-            uint32_t v[U2], pos[U2], p[U2], k[U2], sn[U2];
+        for (uint32_t t0 = 0; t0 < tiles; t0 += U) {
+            bool is[U];
+            uint32_t v[U], pos[U], p[U];
+            int32_t nd[U];
 #pragma unroll
-            for (uint32_t u = 0; u < U2; ++u) {
-                const uint32_t w = (t0 + u) * 8u + warp;
+            for (uint32_t u = 0; u < U; ++u) {
+                const uint32_t w = (t0 + u) * kPruneWarps + warp;
                 const uint32_t m = t0 + u < tiles ? mask[w] : 0u;
                 is[u] = (m >> lane) & 1u;
-                v[u] = lo + (t0 + u) * 256u + tid;
+                v[u] = lo + (t0 + u) * kPruneThreads + tid;
                 pos[u] = is[u] ? base + wpre[w] + (uint32_t)__popc(m & lt) : 0u;
                 p[u] = is[u] ? (uint32_t)__ldg(&a.pool_of[v[u]]) : 0u;
             }
 #pragma unroll
-            for (uint32_t u = 0; u < U2; ++u) {
-                k[u] = is[u] ? __ldg(&a.kvict[p[u]]) : 0u;
-                sn[u] = is[u] ? __ldcg(&a.seen[p[u]]) : 0u;
-            }
+            for (uint32_t u = 0; u < U; ++u) nd[u] = is[u] ? __ldcg(&a.need[p[u]]) : 1;
 #pragma unroll
-            for (uint32_t u = 0; u < U2; ++u) {
+            for (uint32_t u = 0; u < U; ++u) {
                 if (!is[u]) continue;
                 a.cand_keys[pos[u]] = p[u];
                 a.cand_vals[pos[u]] = v[u];
-                const uint32_t rem = k[u] > sn[u] ? k[u] - sn[u] : 0u;
-                // every candidate of the pool stores the same value; whoever replaces the last
-                // non-zero one takes the pool off the list of pools still short
-                if (atomicExch(&a.remaining[p[u]], rem) > 0u && rem == 0u) atomicSub(&a.counters[2], 1u);
+                if (nd[u] <= 0) {  // the pool has its victims: no later row of it is a candidate
+                    const uint32_t bit = 1u << (p[u] & 31u);
+                    if (atomicAnd(&a.bits[p[u] >> 5], ~bit) & bit) atomicSub(&a.counters[2], 1u);
+                }
             }
         }
         total += all;
@@ -599,6 +604,13 @@ __global__ void __launch_bounds__(256) prune_kernel(PruneArgs a) {
         if (__ldcg(&a.counters[2]) == 0u) break;  // no pool is short of victims: the rest of the table cannot matter
     }
     if (cta == 0 && tid == 0) a.counters[3] = total;
+}
+
+// candidates kept per pool = scaleDownCount - need (need may have gone below zero)
+__global__ void cand_count_kernel(const uint32_t *__restrict__ kvict, const int32_t *__restrict__ need, uint32_t P,
+                                  uint32_t *__restrict__ count) {
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < P) count[p] = (uint32_t)((int32_t)kvict[p] - need[p]);
 }
 
 // ------------------------------------------------------------------ host side
@@ -644,7 +656,7 @@ static int rec_upload(k8sgpu_ctx *ctx, const k8sgpu_pool_table *pools, const k8s
     // upper bound of the ordinal bitmap: sum over pools of ceil((cur + cc)/32) <= (V + sum desired)/32 + P
     const size_t bitmap_words = (V + sum_desired) / 32 + P + 1;
     K8S_CUDA(ctx, st.lut.reserve(((size_t)n_owner_ids + 1) * 4));
-    K8S_CUDA(ctx, st.pool_tmp.reserve((6 * P + 8) * 4));
+    K8S_CUDA(ctx, st.pool_tmp.reserve((6 * P + P / 32 + 16) * 4));
     K8S_CUDA(ctx, st.bitmap.reserve(bitmap_words * 4));
     K8S_CUDA(ctx, st.counters.reserve(64 * 4));
     // owner id -> pool row: part of the uploaded state (every run of these tables uses it)
@@ -663,7 +675,8 @@ struct RecPtrs {
     const int32_t *desired;
     int32_t *pool_of, *current, *ready, *delta, *create_count, *victim_off, *member_off, *create_off;
     uint32_t *victim_vm, *member_vm, *create_ordinal;
-    uint32_t *kvict, *span_words, *word_off, *remaining, *seen, *cand_off;
+    uint32_t *kvict, *span_words, *word_off, *cand_cnt, *cand_off, *bits;
+    int32_t *need;
 };
 static RecPtrs rec_ptrs(const ReconcileState &st) {
     RecPtrs r;
@@ -690,9 +703,10 @@ static RecPtrs rec_ptrs(const ReconcileState &st) {
     r.kvict = t;
     r.span_words = t + P;
     r.word_off = t + 2 * P;          // P + 1
-    r.remaining = t + 3 * P + 1;
-    r.seen = t + 4 * P + 1;
+    r.need = reinterpret_cast<int32_t *>(t + 3 * P + 1);
+    r.cand_cnt = t + 4 * P + 1;
     r.cand_off = t + 5 * P + 1;      // P + 1
+    r.bits = t + ((6 * P + 2 + 3) & ~(size_t)3);  // P / 32 + 1 words, 16-byte aligned
     return r;
 }
 
@@ -797,7 +811,7 @@ static int rec_run_large(k8sgpu_ctx *ctx, cudaStream_t s, bool full_sort) {
     }
     if (P) {
         K8S_LAUNCH(ctx, pool_kernel, ceil_div(P, 256), 256, 0, s, q.desired, P, q.current, q.ready, q.delta,
-                   q.create_count, q.kvict, q.span_words, q.remaining, q.seen, cnts);
+                   q.create_count, q.kvict, q.span_words, q.need, q.bits, cnts);
         int rc = exclusive_scan_u32(ctx, s, q.kvict, (uint32_t *)q.victim_off, P, st.scan_tmp, (uint32_t *)q.victim_off + P);
         if (rc) return rc;
         rc = exclusive_scan_u32(ctx, s, (const uint32_t *)q.create_count, (uint32_t *)q.create_off, P, st.scan_tmp,
@@ -824,36 +838,34 @@ static int rec_run_large(k8sgpu_ctx *ctx, cudaStream_t s, bool full_sort) {
         st.members_src = vals;
     } else if (V && P) {
         st.last_path = 1;
-        if (st.prune_occ == 0) {
-            int per_sm = 0;
-            K8S_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, prune_kernel, 256, 0));
-            st.prune_occ = per_sm > 0 ? per_sm : -1;
+        const uint32_t bit_words = P / 32u + 1u;
+        const bool smem_bits = bit_words <= kPruneMaxSmemBitWords;
+        const size_t smem = smem_bits ? (size_t)bit_words * 4 : 0;
+        void *kern = smem_bits ? (void *)prune_kernel<true> : (void *)prune_kernel<false>;
+        if (smem_bits && !st.prune_attr_set) {  // more than 48 KB of dynamic shared memory needs the opt-in
+            K8S_CUDA(ctx, cudaFuncSetAttribute(prune_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)(kPruneMaxSmemBitWords * 4)));
+            st.prune_attr_set = true;
         }
-        if (st.prune_occ < 0) return fail(ctx, K8SGPU_E_CUDA, "cooperative pruning kernel cannot be resident");
-        uint32_t grid = (uint32_t)ctx->sm_count * (uint32_t)(st.prune_occ < 4 ? st.prune_occ : 4);
-        if (grid > ceil_div(V, 256u)) grid = ceil_div(V, 256u);
-        if (ctx->tune.rec_grid >= 1 && (uint32_t)ctx->tune.rec_grid <= (uint32_t)ctx->sm_count * (uint32_t)st.prune_occ)
-            grid = (uint32_t)ctx->tune.rec_grid;
+        // one CTA of 1024 threads per SM (the bitmap copy may fill its shared memory)
+        uint32_t grid = (uint32_t)ctx->sm_count;
+        if (grid > ceil_div(V, kPruneThreads)) grid = ceil_div(V, kPruneThreads);
+        if (ctx->tune.rec_grid >= 1 && (uint32_t)ctx->tune.rec_grid <= (uint32_t)ctx->sm_count) grid = (uint32_t)ctx->tune.rec_grid;
         // Segments: few enough that the two grid barriers per segment stay small beside the rows
         // walked, many enough that the pass can stop early and that a pool overshoots its victim
         // count by little; a CTA's share of a segment must fit the shared-memory mask.
-        uint32_t segs = V / (grid * 16384u);
+        uint32_t segs = V / (grid * 32768u);
         segs = segs < 4u ? 4u : (segs > 32u ? 32u : segs);
         if (ctx->tune.rec_segments >= 1) segs = (uint32_t)ctx->tune.rec_segments;
         uint32_t rows_per_cta = ceil_div(ceil_div(V, segs), grid);
-        rows_per_cta = ceil_div(rows_per_cta, 256u) * 256u;
-        if (rows_per_cta > kPruneMaxRowsPerCta) {
-            rows_per_cta = kPruneMaxRowsPerCta;
-            segs = ceil_div(V, rows_per_cta * grid);  // V < 2^31, grid >= 1: fits
-        } else {
-            segs = ceil_div(V, rows_per_cta * grid);
-        }
+        rows_per_cta = ceil_div(rows_per_cta, kPruneThreads) * kPruneThreads;
+        if (rows_per_cta > kPruneMaxRowsPerCta) rows_per_cta = kPruneMaxRowsPerCta;
+        segs = ceil_div(V, rows_per_cta * grid);  // V < 2^31, grid >= 1: fits
         K8S_CUDA(ctx, st.cta_cnt.reserve((size_t)grid * 4 + 16));
         PruneArgs a;
         a.pool_of = q.pool_of;
-        a.kvict = q.kvict;
-        a.remaining = q.remaining;
-        a.seen = q.seen;
+        a.need = q.need;
+        a.bits = q.bits;
         a.cta_cnt = st.cta_cnt.as<uint32_t>();
         a.cand_keys = keys;
         a.cand_vals = vals;
@@ -861,8 +873,9 @@ static int rec_run_large(k8sgpu_ctx *ctx, cudaStream_t s, bool full_sort) {
         a.V = V;
         a.segments = segs;
         a.rows_per_cta = rows_per_cta;
+        a.bit_words = bit_words;
         void *args[] = {&a};
-        K8S_CUDA(ctx, cudaLaunchCooperativeKernel((void *)prune_kernel, dim3(grid), dim3(256), args, 0, s));
+        K8S_CUDA(ctx, cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(kPruneThreads), args, smem, s));
         ctx->stats.kernel_launches++;
         K8S_CUDA(ctx, cudaMemcpyAsync(ctx->h_pinned + 8, cnts + 3, 4, cudaMemcpyDeviceToHost, s));
         K8S_CUDA(ctx, cudaStreamSynchronize(s));  // the sort's launch sizes depend on the candidate count
@@ -872,7 +885,8 @@ static int rec_run_large(k8sgpu_ctx *ctx, cudaStream_t s, bool full_sort) {
         st.last_candidates = n_cand;
         int rc = sort_pairs(ctx, s, keys, vals, n_cand, key_bits(P), st.sort);
         if (rc) return rc;
-        rc = exclusive_scan_u32(ctx, s, q.seen, q.cand_off, P, st.scan_tmp, q.cand_off + P);
+        K8S_LAUNCH(ctx, cand_count_kernel, ceil_div(P, 256), 256, 0, s, q.kvict, q.need, P, q.cand_cnt);
+        rc = exclusive_scan_u32(ctx, s, q.cand_cnt, q.cand_off, P, st.scan_tmp, q.cand_off + P);
         if (rc) return rc;
         if (n_cand)
             K8S_LAUNCH(ctx, victim_gather_kernel, ceil_div(n_cand, 256), 256, 0, s, keys, vals, n_cand, P, q.cand_off,

@@ -62,7 +62,8 @@ def case_place(rng, ctx):
     n, m = pick_size(rng, 3000), pick_size(rng, 12000)
     nodes, pods = random_nodes(rng, n), random_pods(rng, m)
     flags = int(rng.random() < 0.2)
-    env = dict(res=int(rng.integers(0, 5)), ppt=int(rng.choice([1, 2, 4])), coop=int(rng.integers(0, 2)))
+    env = dict(res=int(rng.choice([0, 1, 2, 3, 4, 4, 4, 4])), ppt=int(rng.choice([1, 2, 4])), coop=int(rng.choice([0, 1, 1])),
+               order=int(rng.choice([0, 1, 1])))  # order: scoring order sorted by pod class (RES 4 + one-launch admission)
     if rng.random() < 0.5:
         env["splits"] = int(rng.integers(1, 9))
     if rng.random() < 0.5:  # few CTAs in the single-launch admission: every CTA loops over several tiles

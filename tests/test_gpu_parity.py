@@ -203,6 +203,17 @@ def test_place_single_launch_admission(ctx, name, grid):
     assert got["kernel_launches"] <= 2 * got["rounds"] + 8
 
 
+@pytest.mark.parametrize("order", [0, 1])
+@pytest.mark.parametrize("n,m,coop_grid", [(500, 60_000, 3), (1500, 9_000, None), (200, 140_000, None), (37, 300, 1)])
+def test_place_class_sorted_scoring_order(ctx, orc, synth, order, n, m, coop_grid):
+    """The scoring kernel walks each round's active list through an order sorted by pod class, so
+    that whole warps can drop the clauses none of their pods need.  With the order on and off the
+    result is the oracle's: short and long lists, few CTAs (many tiles per CTA in the partition)."""
+    nodes, pods = synth.gen_nodes(n, config_id=5), synth.gen_pods(m, config_id=5)
+    ctx.set_tuning(order=order, coop_grid=coop_grid)
+    same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
+
+
 def test_k12_ties_rot_zero(ctx, synth):
     nodes, pods = synth.gen_identical(5, 41)
     r = ctx.place(nodes, pods, flags=1)
