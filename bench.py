@@ -224,7 +224,7 @@ def main():
     ap.add_argument("--no-reconcile", action="store_true")
     ap.add_argument("--no-scaling-base", action="store_true")
     ap.add_argument("--exchange", default=None, choices=["allgather", "peer"],
-                    help="N>1: force how a round's proposals travel (default: chosen per round by list length)")
+                    help="N>1: force how a round's proposals travel (default: peer stores where peers can be mapped)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -354,8 +354,8 @@ def main():
                    "parallelism": f"pods sharded x{world}, nodes replicated",
                    "exchange": "none" if world == 1 else {"peer": "peer stores + 1-word ncclAllReduce (forced)",
                                                           "allgather": "ncclAllGather of the proposals (forced)",
-                                                          None: "per round, in the library: ncclAllGather above 2^18 "
-                                                                "proposals, peer stores + 1-word ncclAllReduce below"}[args.exchange],
+                                                          None: "in the library: peer stores from the score-decoding kernel + "
+                                                                "1-word ncclAllReduce (ncclAllGather where peers cannot be mapped)"}[args.exchange],
                    "l2": "flushed between timed steps (256 MB write)", "wall_s_timed_region": wall,
                    "launches_per_e2e_step": launches_e2e},
         "roofline": {"bound": "instruction issue (INT32), not hbm: see roofline_contract", "achieved": score_rate,

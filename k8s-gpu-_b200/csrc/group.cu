@@ -17,7 +17,7 @@
 //   0  ncclAllGather, in place in the exchange buffer
 //   1  peer stores: the kernel that decodes the scores writes each proposal into every rank's
 //      exchange buffer over NVLink peer memory, followed by a 1-word ncclAllReduce as the barrier
-//  -1  (default) per round: peer stores for short proposal lists, ncclAllGather for long ones
+//  -1  (default) peer stores when every rank can map every other rank's buffer, else ncclAllGather
 // NCCL is loaded with dlopen when a group is first formed: single-GPU users never need it, and a
 // process that already carries an NCCL (PyTorch's) shares that copy.
 #include <dlfcn.h>
@@ -44,8 +44,6 @@ struct NcclApi {
     void *handle;
     char err[256];
 };
-
-constexpr uint32_t kPeerStoreMaxProposals = 1u << 18;  // automatic exchange: peer stores up to this many proposals per round
 
 static NcclApi g_nccl = {};
 static std::mutex g_nccl_mu;
@@ -258,11 +256,12 @@ static int group_rounds(k8sgpu_ctx *ctx, const NcclApi *api) {
     const uint32_t world = (uint32_t)ctx->world;
     while (lead.n_active > 0 && (lead.max_rounds == 0 || lead.rounds < lead.max_rounds)) {
         const uint32_t na = lead.n_active, slice = ceil_div(na, world);
-        // Which exchange this round (same decision on every rank: it depends on na alone).  Forced
-        // by the "exchange" knob, else: peer stores while the round is short (no collective launch
-        // besides the 1-word barrier: measured 75 us instead of 220 us per round on 2 GPUs),
-        // ncclAllGather for long proposal lists, where both measure the same.
-        const bool p2p = ctx->xpeer_ready && (ctx->tune.exchange == 1 || (ctx->tune.exchange < 0 && slice * world <= kPeerStoreMaxProposals));
+        // Which exchange this round (the same on every rank).  Forced by the "exchange" knob, else
+        // peer stores wherever every rank could map every other rank's buffer -- the kernel that
+        // decodes the scores does the exchange, and the only collective left is a 1-word barrier:
+        // measured 75 us instead of 220 us per short round on 2 GPUs, and equal to ncclAllGather
+        // at 10^6 proposals (profiles/r02_group_ranks_x2_check.log) -- and ncclAllGather otherwise.
+        const bool p2p = ctx->xpeer_ready && ctx->tune.exchange != 0;
         // Rounds alternate between the two halves of the exchange buffer, whichever exchange they
         // use: a fast rank's peer stores of round r+1 must not land where a slower rank is still
         // reading round r.
