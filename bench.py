@@ -24,6 +24,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+EMIT = None  # set in main(): prints the one JSON line on the real stdout
 NODE_REC_BYTES = 32  # algorithmic bytes per pod-node eval: one packed node record
 WORKLOADS = {
     "c3": dict(n=10_000, m=100_000, config_id=3, desc="config3: 10k nodes x 100k pods"),
@@ -171,7 +172,7 @@ def reference_arm(args, rank, world):
         "e2e": {"value": v, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    EMIT(line)
 
 
 def pinned_block(torch, n_elems):
@@ -229,6 +230,20 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE line, the JSON: anything a library prints there meanwhile (NCCL's
+    # version banner under NCCL_DEBUG) is sent to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
+
+    global EMIT
+    EMIT = emit
     if args.impl == "reference":
         reference_arm(args, rank, world)
         return
@@ -481,7 +496,7 @@ def main():
         v, ev, dt, sample = cpu_port(nodes, pods, frac, threads)
         line["cpu_baseline"] = {"value": v, "unit": "evals/s", "cores": threads, "kind": "port", "sample": sample,
                                 "sample_frac": frac, "seconds": dt}
-    print(json.dumps(line), flush=True)
+    EMIT(line)
     ctx.close()
     if dist is not None:
         dist.destroy_process_group()

@@ -20,7 +20,7 @@ static int *tuning_slot(Tuning &t, const char *key) {
     } table[] = {{"res", &t.res}, {"ppt", &t.ppt}, {"splits", &t.splits}, {"coop", &t.coop},
                  {"coop_grid", &t.coop_grid}, {"rec_path", &t.rec_path}, {"rec_grid", &t.rec_grid},
                  {"rec_segments", &t.rec_segments}, {"coop_prof", &t.coop_prof}, {"rec_prof", &t.rec_prof},
-                 {"shard_admit", &t.shard_admit}, {"exchange", &t.exchange}, {"force_cls", &t.force_cls}, {"order", &t.order}};
+                 {"shard_admit", &t.shard_admit}, {"exchange", &t.exchange}, {"force_cls", &t.force_cls}, {"order", &t.order}, {"shard_upload", &t.shard_upload}};
     for (auto &e : table)
         if (strcmp(e.name, key) == 0) return e.slot;
     return nullptr;
@@ -28,7 +28,7 @@ static int *tuning_slot(Tuning &t, const char *key) {
 
 static void tuning_from_env(Tuning &t) {
     static const char *names[] = {"res", "ppt", "splits", "coop", "coop_grid", "rec_path", "rec_grid",
-                                  "rec_segments", "coop_prof", "rec_prof", "shard_admit", "exchange", "force_cls", "order"};
+                                  "rec_segments", "coop_prof", "rec_prof", "shard_admit", "exchange", "force_cls", "order", "shard_upload"};
     for (const char *n : names) {
         char env[64] = "K8SGPU_";
         size_t k = strlen(env);

@@ -137,6 +137,7 @@ struct Tuning {
     int rec_grid = -1;   // CTAs of the cooperative reconcile launches
     int rec_segments = -1;  // row segments of the pruned ranking pass
     int coop_prof = 0, rec_prof = 0;  // print phase times (stderr)
+    int shard_upload = -1;  // multi-GPU: 0 = every rank copies the whole pod table from the host
     int shard_admit = -1;   // multi-GPU: 1 = admission sharded by node range, 0 = replicated
     int order = -1;         // 0: do not sort the scoring order by pod class
     int force_cls = -1;     // timing experiments only: eval_pair class for every warp (results are wrong)
@@ -170,7 +171,7 @@ struct k8sgpu_ctx {
     k8sgpu_ctx *local[16] = {};
     void *comm = nullptr;
     k8sgpu::DevBuf xchg;      // proposals of all ranks (all-gather target / peer-store target, two halves)
-    k8sgpu::DevBuf xsend;     // this rank's proposals of the round (all-gather source)
+    k8sgpu::DevBuf xsend;     // pod-table staging of a sharded upload (8 columns x padded rows)
     k8sgpu::DevBuf xsmall;    // barrier word, IPC handles
     uint32_t xchg_m = 0;      // proposals per half of xchg
     int32_t *xpeer[16] = {};  // every rank's xchg as seen from this GPU (peer-store exchange)
@@ -269,7 +270,12 @@ inline int key_bits(uint32_t max_key) {  // bits needed to hold values 0..max_ke
 
 // place.cu (host side of the round loop; group.cu drives them across GPUs)
 int check_tables(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods);
-int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods);
+struct PodShare {  // one rank's share of a pod-table upload (see place_upload)
+    uint32_t lo, hi, stride;
+    uint32_t *staging;
+};
+int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods,
+                 const PodShare *share = nullptr);
 int place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out);
 int place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy);
 int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s);

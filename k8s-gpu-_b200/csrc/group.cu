@@ -382,14 +382,60 @@ int group_place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, const k8sgpu_g
     return K8SGPU_OK;
 }
 
+// Tables to every GPU of the group.  The node table (32 B x N) goes to each GPU from the host; of
+// the pod table each rank copies only its 1/world of the rows over PCIe, and the ranks complete
+// each other's copies with one ncclAllGather per column over NVLink.
 int group_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods) {
-    for (int i = 0; i < ctx->nlocal; ++i) {  // queued on every device's own stream: the copies overlap
+    if (ctx->world == 1 || !pods || pods->m < 4096u * (uint32_t)ctx->world || ctx->tune.shard_upload == 0) {
+        for (int i = 0; i < ctx->nlocal; ++i) {  // queued on every device's own stream: the copies overlap
+            k8sgpu_ctx *c = ctx->local[i];
+            K8S_DEV(ctx, c);
+            if (c != ctx) reset_call_stats(c);
+            int rc = place_upload(c, nodes, pods);
+            if (rc) return lift(ctx, c, rc);
+            if (c != ctx) ctx->stats.h2d_bytes += c->stats.h2d_bytes;
+        }
+        K8S_DEV(ctx, ctx);
+        return K8SGPU_OK;
+    }
+    const NcclApi *api = nccl_api(ctx);
+    if (!api) return K8SGPU_E_NCCL;
+    const uint32_t world = (uint32_t)ctx->world, m = pods->m, slice = ceil_div(m, world), stride = slice * world;
+    const int npc = pods->priority ? 8 : 7;
+    for (int i = 0; i < ctx->nlocal; ++i) {
         k8sgpu_ctx *c = ctx->local[i];
         K8S_DEV(ctx, c);
         if (c != ctx) reset_call_stats(c);
-        int rc = place_upload(c, nodes, pods);
+        K8S_CUDA(ctx, c->xsend.reserve((size_t)8 * stride * 4 + 64));
+        PodShare sh;
+        sh.lo = (uint32_t)c->rank * slice < m ? (uint32_t)c->rank * slice : m;
+        sh.hi = sh.lo + slice < m ? sh.lo + slice : m;
+        sh.stride = stride;
+        sh.staging = c->xsend.as<uint32_t>();
+        int rc = place_upload(c, nodes, pods, &sh);
         if (rc) return lift(ctx, c, rc);
         if (c != ctx) ctx->stats.h2d_bytes += c->stats.h2d_bytes;
+    }
+    K8S_NCCL(ctx, api, api->GroupStart());
+    for (int i = 0; i < ctx->nlocal; ++i) {
+        k8sgpu_ctx *c = ctx->local[i];
+        for (int col = 0; col < npc; ++col) {
+            uint32_t *base = c->xsend.as<uint32_t>() + (size_t)col * stride;
+            ncclResult_t r = api->AllGather(base + (size_t)c->rank * slice, base, slice, ncclUint32, (ncclComm_t)c->comm, c->stream);
+            if (r != ncclSuccess) {
+                api->GroupEnd();
+                return fail(ctx, K8SGPU_E_NCCL, "ncclAllGather (pod table): %s", api->GetErrorString(r));
+            }
+        }
+    }
+    K8S_NCCL(ctx, api, api->GroupEnd());
+    for (int i = 0; i < ctx->nlocal; ++i) {
+        k8sgpu_ctx *c = ctx->local[i];
+        K8S_DEV(ctx, c);
+        for (int col = 0; col < npc; ++col)
+            K8S_CUDA(ctx, cudaMemcpyAsync(c->place.pod_cols.as<uint32_t>() + (size_t)col * m,
+                                          c->xsend.as<uint32_t>() + (size_t)col * stride, (size_t)m * 4,
+                                          cudaMemcpyDeviceToDevice, c->stream));
     }
     K8S_DEV(ctx, ctx);
     return K8SGPU_OK;

@@ -1205,7 +1205,10 @@ int check_tables(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_p
     return K8SGPU_OK;
 }
 
-int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods) {
+// share != null (placement groups): only pod rows [lo, hi) are copied from the host, into a staging
+// block with `stride` rows per column; the group's ranks then all-gather the staging block over
+// NVLink and copy it into place (group.cu), so each rank moves 1/world of the pod table over PCIe.
+int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_pod_table *pods, const PodShare *share) {
     int rc = check_tables(ctx, nodes, pods);
     if (rc) return rc;
     PlaceState &st = ctx->place;
@@ -1228,14 +1231,18 @@ int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_p
     for (int c = 0; c + 1 < 8; ++c) nslab = nslab && nc[c + 1] == nc[c] + n;
     for (int c = 0; c + 1 < npc; ++c) pslab = pslab && pc[c + 1] == pc[c] + m;
     if (nslab) K8S_CUDA(ctx, cudaMemcpyAsync(st.node_cols.p, nc[0], 8 * n * 4, cudaMemcpyHostToDevice, s));
+    if (share) pslab = false;
     if (pslab) K8S_CUDA(ctx, cudaMemcpyAsync(st.pod_cols.p, pc[0], (size_t)npc * m * 4, cudaMemcpyHostToDevice, s));
     for (int c = 0; c < 8; ++c) {
         if (n && !nslab)
             K8S_CUDA(ctx, cudaMemcpyAsync(st.node_cols.as<uint32_t>() + c * n, nc[c], n * 4, cudaMemcpyHostToDevice, s));
-        if (m && !pslab && c < npc)
+        if (m && !pslab && c < npc && !share)
             K8S_CUDA(ctx, cudaMemcpyAsync(st.pod_cols.as<uint32_t>() + c * m, pc[c], m * 4, cudaMemcpyHostToDevice, s));
+        if (share && c < npc && share->hi > share->lo)
+            K8S_CUDA(ctx, cudaMemcpyAsync(share->staging + (size_t)c * share->stride + share->lo, pc[c] + share->lo,
+                                          (size_t)(share->hi - share->lo) * 4, cudaMemcpyHostToDevice, s));
     }
-    ctx->stats.h2d_bytes += (8 * n + (size_t)npc * m) * 4;
+    ctx->stats.h2d_bytes += (8 * n + (size_t)npc * (share ? share->hi - share->lo : m)) * 4;
     // run-state buffers
     K8S_CUDA(ctx, st.free_cols.reserve(3 * n * 4 + 16));
     K8S_CUDA(ctx, st.nodeq.reserve((size_t)st.n_pad * sizeof(NodeQ)));

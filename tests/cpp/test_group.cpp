@@ -130,8 +130,10 @@ int main(int argc, char **argv) {
         for (int gangs = 0; gangs < 2; ++gangs)
             for (int variant = 0; variant < 5; ++variant) {
                 // variant: 0 all-gather + one-launch admission, 1 peer stores, 2 all-gather + kernel chain,
-                // 3 rot = 0 (all-gather), 4 automatic exchange (chosen per round by the list length)
+                // 3 rot = 0 (all-gather, every GPU copies the whole pod table from the host), 4 defaults
+                // (peer stores where peers map, pod-table upload shared out between the GPUs)
                 k8sgpu_set_tuning(grp, "exchange", variant == 1 ? 1 : variant == 4 ? -1 : 0);
+                k8sgpu_set_tuning(grp, "shard_upload", variant == 3 ? 0 : -1);
                 k8sgpu_set_tuning(grp, "coop", variant == 2 ? 0 : -1);
                 const uint32_t flags = variant == 3 ? K8SGPU_POLICY_ROT_ZERO : 0;
                 Result a, b;
