@@ -93,6 +93,7 @@ struct PlaceState {
     int peer_world = 0, peer_rank = -1;
     uint32_t peer_m = 0;         // proposals per half of the exchange buffer
     DevBuf gang_id, gang_min, gang_count, gang_state;  // gang placement: [m], [g], [g], [2g] (rejected, newly)
+    uint32_t last_score_slots = 0;        // local slots of the last scoring launch
     uint32_t coop_seq = 0, coop_grid = 0;  // admission launch in flight: mailbox sequence number, CTAs
     int timed = 0;        // scoring launches timed so far in this run
     uint64_t timed_evals = 0;
@@ -280,11 +281,13 @@ int place_download(k8sgpu_ctx *ctx, k8sgpu_place_out *out);
 int place_run(k8sgpu_ctx *ctx, const k8sgpu_policy *policy);
 int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s);
 int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cudaStream_t s, bool prep = true,
-                bool finalize = true);
-int round_finalize_peers(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *const *peer, int world, cudaStream_t s);
+                bool finalize = true, uint32_t xw = 1, uint32_t xrank = 0);
+int round_finalize_peers(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *const *peer, int world, cudaStream_t s,
+                         uint32_t xw, uint32_t xrank);
+uint32_t group_slot_count(uint32_t na, uint32_t xw);
 int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t s, uint32_t *n_active_out);
 int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals);
-int round_admit_coop_launch(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals);
+int round_admit_coop_launch(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals, uint32_t xw = 1);
 int round_admit_coop_finish(k8sgpu_ctx *ctx, cudaStream_t s);
 int round_end(k8sgpu_ctx *ctx, cudaStream_t s);
 bool coop_admission(const k8sgpu_ctx *ctx);

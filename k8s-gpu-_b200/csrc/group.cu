@@ -161,7 +161,8 @@ static int group_reserve(k8sgpu_ctx *ctx, uint32_t m) {
     const NcclApi *api = nccl_api(ctx);
     if (!api) return K8SGPU_E_NCCL;
     const uint32_t world = (uint32_t)ctx->world;
-    const uint32_t half = (ceil_div(m ? m : 1u, world) + 1u) * world;  // >= slice_len * world for every n_active <= m
+    // >= the exchanged array of any round: world runs of whole 2048-slot blocks (see SlotMap)
+    const uint32_t half = group_slot_count(m ? m : 1u, world) * world + world;
     bool grew = false;
     if (ctx->xpeer_ipc && ctx->xchg_m < half) {
         // The exchange buffers are about to be replaced (every rank takes this branch in the same
@@ -254,8 +255,16 @@ static int group_barrier(k8sgpu_ctx *ctx, const NcclApi *api) {
 static int group_rounds(k8sgpu_ctx *ctx, const NcclApi *api) {
     PlaceState &lead = ctx->place;
     const uint32_t world = (uint32_t)ctx->world;
+    const bool coop = coop_admission(ctx);
     while (lead.n_active > 0 && (lead.max_rounds == 0 || lead.rounds < lead.max_rounds)) {
-        const uint32_t na = lead.n_active, slice = ceil_div(na, world);
+        const uint32_t na = lead.n_active;
+        // How the round's scoring slots are shared out.  With the one-launch admission: blocks of
+        // 2048 slots dealt round-robin (the slots are sorted by pod class, cheap classes first, so
+        // contiguous shares would be unequal work); each rank's proposals are then one contiguous
+        // run of `slice` entries in the exchanged array.  With the kernel chain (a test path, no
+        // class order): contiguous shares of the active list.
+        const uint32_t xw = coop ? world : 1u;
+        const uint32_t slice = coop ? group_slot_count(na, world) : ceil_div(na, world);
         // Which exchange this round (the same on every rank).  Forced by the "exchange" knob, else
         // peer stores wherever every rank could map every other rank's buffer -- the kernel that
         // decodes the scores does the exchange, and the only collective left is a 1-word barrier:
@@ -269,18 +278,23 @@ static int group_rounds(k8sgpu_ctx *ctx, const NcclApi *api) {
         for (int i = 0; i < ctx->nlocal; ++i) {
             k8sgpu_ctx *c = ctx->local[i];
             K8S_DEV(ctx, c);
-            const uint32_t lo = (uint32_t)c->rank * slice < na ? (uint32_t)c->rank * slice : na;
-            const uint32_t hi = lo + slice < na ? lo + slice : na;
+            const uint32_t rank = (uint32_t)c->rank;
+            uint32_t lo = 0, hi = na;
+            if (!coop) {
+                lo = rank * slice < na ? rank * slice : na;
+                hi = lo + slice < na ? lo + slice : na;
+            }
             int rc;
             if (p2p) {
-                rc = round_score(c, lo, hi, nullptr, c->stream, c->place.nodeq_stale, /*finalize=*/false);
+                rc = round_score(c, lo, hi, nullptr, c->stream, c->place.nodeq_stale, /*finalize=*/false, xw, rank);
                 if (!rc) {
                     int32_t *pp[16];
                     for (uint32_t r = 0; r < 16; ++r) pp[r] = r < world ? c->xpeer[r] + half : nullptr;
-                    rc = round_finalize_peers(c, lo, hi, pp, (int)world, c->stream);
+                    rc = round_finalize_peers(c, lo, hi, pp, (int)world, c->stream, xw, rank);
                 }
-            } else {  // the slice lands where the in-place all-gather expects it
-                rc = round_score(c, lo, hi, c->xchg.as<int32_t>() + half + lo, c->stream, c->place.nodeq_stale, true);
+            } else {  // this rank's run lands where the in-place all-gather expects it
+                rc = round_score(c, lo, hi, c->xchg.as<int32_t>() + half + (size_t)rank * slice, c->stream,
+                                 c->place.nodeq_stale, true, xw, rank);
             }
             if (rc) return lift(ctx, c, rc);
         }
@@ -301,12 +315,11 @@ static int group_rounds(k8sgpu_ctx *ctx, const NcclApi *api) {
             K8S_NCCL(ctx, api, api->GroupEnd());
         }
         // admission on every replica: queue all of them, then wait for each
-        const bool coop = coop_admission(ctx);
         for (int i = 0; i < ctx->nlocal; ++i) {
             k8sgpu_ctx *c = ctx->local[i];
             K8S_DEV(ctx, c);
             const int32_t *prop = c->xchg.as<int32_t>() + half;
-            int rc = coop ? round_admit_coop_launch(c, c->stream, prop) : round_admit(c, prop, c->stream, nullptr);
+            int rc = coop ? round_admit_coop_launch(c, c->stream, prop, xw) : round_admit(c, prop, c->stream, nullptr);
             if (rc) return lift(ctx, c, rc);
         }
         for (int i = 0; i < ctx->nlocal; ++i) {

@@ -364,6 +364,30 @@ __device__ __forceinline__ void eval_pair(const uint4 &a, const uint4 &b, uint32
     }
 }
 
+// Which scoring slots a launch covers.  One GPU, or the round-at-a-time API: the contiguous range
+// [lo, hi).  A placement group of xw ranks: blocks of kXBlock slots dealt round-robin, rank r
+// taking blocks r, r + xw, ... -- the slots are sorted by pod class (cheap classes first), so
+// contiguous ranges would give the ranks unequal work.  A rank's slots are numbered 0 .. xcnt by
+// their local index jj; in the exchanged proposal array rank r's slot jj sits at r * xcnt + jj.
+constexpr uint32_t kXBlock = 2048;
+struct SlotMap {
+    uint32_t lo, hi, xw, xrank, xcnt;
+};
+__device__ __forceinline__ bool slot_of(const SlotMap &m, uint32_t jj, uint32_t *slot) {
+    if (m.xw <= 1u) {
+        *slot = m.lo + jj;
+        return *slot < m.hi;
+    }
+    *slot = ((jj / kXBlock) * m.xw + m.xrank) * kXBlock + (jj % kXBlock);
+    return jj < m.xcnt && *slot < m.hi;
+}
+// where slot s of the round sits in the exchanged proposal array
+__device__ __forceinline__ uint32_t exchange_index(uint32_t s, uint32_t xw, uint32_t xcnt) {
+    if (xw <= 1u) return s;
+    const uint32_t b = s / kXBlock;
+    return (b % xw) * xcnt + (b / xw) * kXBlock + (s % kXBlock);
+}
+
 constexpr int kDefaultRes = 4;
 constexpr uint32_t kStages = K8S_STAGES;  // node tiles in flight per CTA
 constexpr uint32_t kGroup = 64;        // nodes per index group (index bits 1..6 of the key)
@@ -382,7 +406,7 @@ constexpr uint32_t kIdxMask = 0x7Eu;   // those bits
 template <int PPT, int RES, int MB>
 __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict__ nodeq, uint32_t n_tiles,
                                                     uint32_t tiles_per_split, const PodQ *__restrict__ podq,
-                                                    const uint32_t *__restrict__ active, uint32_t lo, uint32_t hi,
+                                                    const uint32_t *__restrict__ active, SlotMap sm,
                                                     unsigned long long *__restrict__ best_key, uint32_t n_nodes,
                                                     int use_atomic, uint32_t negone, int cls_force,
                                                     const uint32_t *__restrict__ order) {
@@ -417,11 +441,12 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
         // thread -> active position: straight, or through the round's class-sorted scoring order
-        const uint32_t slot = lo + (blockIdx.x * PPT + j) * 256u + tid;
-        pos[j] = slot < hi ? (order ? __ldg(&order[slot]) : slot) : 0xFFFFFFFFu;
+        uint32_t slot;
+        const bool live = slot_of(sm, (blockIdx.x * PPT + j) * 256u + tid, &slot);
+        pos[j] = live ? (order ? __ldg(&order[slot]) : slot) : 0xFFFFFFFFu;
         best[j] = 0;
         bestn[j] = 0;
-        if (slot < hi) {
+        if (live) {
             const uint4 *q = reinterpret_cast<const uint4 *>(podq + active[pos[j]]);
             uint4 a = __ldg(q), b = __ldg(q + 1);
             rg[j] = a.x; rc[j] = a.y; rm[j] = a.z; nsku[j] = a.w;
@@ -569,12 +594,13 @@ __device__ __forceinline__ int32_t decode_proposal(const unsigned long long *__r
 
 __global__ void score_finalize_kernel(const unsigned long long *__restrict__ best_key, const PodQ *__restrict__ podq,
                                       const uint32_t *__restrict__ active, const uint32_t *__restrict__ order,
-                                      uint32_t lo, uint32_t cnt, uint32_t n_nodes, int32_t *__restrict__ out) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < cnt) out[i] = decode_proposal(best_key, podq, active, order, lo + i, n_nodes);
+                                      SlotMap sm, uint32_t cnt, uint32_t n_nodes, int32_t *__restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, slot;
+    if (i >= cnt) return;
+    out[i] = slot_of(sm, i, &slot) ? decode_proposal(best_key, podq, active, order, slot, n_nodes) : -1;
 }
 
-// Decode the packed best key of slots [lo, lo+cnt) and store the proposal straight into EVERY
+// Decode the packed best key of this launch's slots and store each proposal straight into EVERY
 // rank's exchange buffer (peer stores over NVLink; the own buffer is just another pointer): the
 // all-gather of the round is done by the kernel that produces the values.
 struct PeerPtrs {
@@ -583,13 +609,13 @@ struct PeerPtrs {
 };
 __global__ void score_finalize_p2p_kernel(const unsigned long long *__restrict__ best_key,
                                           const PodQ *__restrict__ podq, const uint32_t *__restrict__ active,
-                                          const uint32_t *__restrict__ order, uint32_t lo, uint32_t cnt,
-                                          uint32_t n_nodes, PeerPtrs peers) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= cnt) return;
-    const int32_t node = decode_proposal(best_key, podq, active, order, lo + i, n_nodes);
+                                          const uint32_t *__restrict__ order, SlotMap sm, uint32_t cnt,
+                                          uint32_t n_nodes, uint32_t base, PeerPtrs peers) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, slot;
+    if (i >= cnt || !slot_of(sm, i, &slot)) return;
+    const int32_t node = decode_proposal(best_key, podq, active, order, slot, n_nodes);
 #pragma unroll 1
-    for (int r = 0; r < peers.world; ++r) peers.p[r][lo + i] = node;
+    for (int r = 0; r < peers.world; ++r) peers.p[r][base + i] = node;
 }
 
 // ------------------------------------------------------------------ admission (a13)
@@ -903,6 +929,7 @@ struct AdmitArgs {
     const uint32_t *inv_cur;             // active position -> scoring slot of this round (null: identity)
     const uint8_t *pod_cls;              // eval_pair class per pod
     uint32_t *order_next, *inv_next;     // next round's scoring order and its inverse (null: not built)
+    uint32_t xw, xcnt;                   // placement group: ranks, local slots per rank (see SlotMap); else 1, 0
     const PodQ *podq;
     const uint32_t *active;
     uint32_t *next_active;
@@ -948,7 +975,8 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
             uint32_t i = vt * kSortTile + r * 256 + tid;
             pod[r] = i < na ? a.active[i] : 0u;
             if (a.proposals) {  // already decoded: re-encode as "distance 0 from rot = node" below
-                int32_t b = i < na ? a.proposals[a.inv_cur ? a.inv_cur[i] : i] : -1;  // proposals arrive by slot
+                // proposals arrive by slot, and in a group by (rank, local slot)
+                int32_t b = i < na ? a.proposals[exchange_index(a.inv_cur ? a.inv_cur[i] : i, a.xw, a.xcnt)] : -1;
                 if (b < -1 || b >= (int32_t)N) {  // not something score_kernel can produce: a stale or
                     atomicOr(&a.counters[0], kErrProposal);  // unsynchronised buffer was handed in
                     b = -1;
@@ -1315,9 +1343,15 @@ int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
 // Scores active positions [lo,hi) into d_best[0 .. hi-lo).
 // prep: rebuild the packed node records first; finalize: decode the packed keys into d_best.
 // (The single-launch admission path needs neither after round 0.)
-int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cudaStream_t s, bool prep, bool finalize) {
+// Local slots of one rank of xw when the round's na slots are dealt in blocks (see SlotMap).
+uint32_t group_slot_count(uint32_t na, uint32_t xw) { return ceil_div(ceil_div(na, kXBlock), xw) * kXBlock; }
+
+int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cudaStream_t s, bool prep, bool finalize,
+                uint32_t xw, uint32_t xrank) {
     PlaceState &st = ctx->place;
     if (hi > st.n_active || lo > hi) return fail(ctx, K8SGPU_E_ARG, "score: bad slice [%u,%u) of %u", lo, hi, st.n_active);
+    if (xw > 1 && (lo != 0 || hi != st.n_active || xrank >= xw))
+        return fail(ctx, K8SGPU_E_ARG, "score: a group round covers the whole active list");
     // node records from the current free columns (validated on the first round)
     if (prep) {
         K8S_LAUNCH(ctx, node_prep_kernel, ceil_div(st.n_pad, 256), 256, 0, s, st.node_cols.as<uint32_t>(),
@@ -1325,7 +1359,19 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
                    st.rounds == 0 ? 1 : 0);
         st.nodeq_stale = false;
     }
-    const uint32_t cnt = hi - lo;
+    SlotMap sm;
+    sm.lo = lo;
+    sm.hi = hi;
+    sm.xw = xw;
+    sm.xrank = xrank;
+    sm.xcnt = xw > 1 ? group_slot_count(hi, xw) : hi - lo;
+    const uint32_t cnt = sm.xcnt;  // local slots of this launch (a group rank's last block may be short or empty)
+    uint32_t live = hi - lo;        // ... and how many of them hold a pod
+    if (xw > 1) {
+        live = 0;
+        for (uint32_t b = xrank; (uint64_t)b * kXBlock < hi; b += xw) live += hi - b * kXBlock < kXBlock ? hi - b * kXBlock : kXBlock;
+    }
+    st.last_score_slots = cnt;
     if (cnt == 0) return K8SGPU_OK;
     const uint32_t n_tiles = st.n_pad / kNodeTile;
     // Grid shape.  The kernel is bound by the ALU pipe and the issue slots, so what matters is an
@@ -1354,8 +1400,8 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     }
     const int use_atomic = splits > 1;
     unsigned long long *bk = st.best_key.as<unsigned long long>();
-    if (use_atomic && !(st.best_cleared_len >= (st.order_valid ? st.n_active : hi))) {  // (the single-launch admission leaves it cleared)
-        if (st.order_valid)  // slots [lo, hi) are scattered positions: clear the whole list
+    if (use_atomic && !(st.best_cleared_len >= ((st.order_valid || xw > 1) ? st.n_active : hi))) {  // (the single-launch admission leaves it cleared)
+        if (st.order_valid || xw > 1)  // the launch's slots are scattered positions: clear the whole list
             K8S_CUDA(ctx, cudaMemsetAsync(bk, 0, (size_t)st.n_active * 8, s));
         else
             K8S_CUDA(ctx, cudaMemsetAsync(bk + lo, 0, (size_t)cnt * 8, s));
@@ -1368,7 +1414,7 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     const int res = st.score_res;  // fixed at round_begin: the pod records are laid out for it
 #define K8S_SCORE(P, R, B)                                                                                         \
     K8S_LAUNCH(ctx, (score_kernel<P, R, B>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
-               st.active[st.cur].as<uint32_t>(), lo, hi, bk, st.n, use_atomic, 0xFFFFFFFFu, ctx->tune.force_cls, order)
+               st.active[st.cur].as<uint32_t>(), sm, bk, st.n, use_atomic, 0xFFFFFFFFu, ctx->tune.force_cls, order)
     // third argument: resident CTAs per SM the register budget is set for (measured best per variant)
     if (ppt == 4) K8S_SCORE(4, 4, 3);
     else if (ppt == 2 && res >= 4) K8S_SCORE(2, 4, 4);
@@ -1385,11 +1431,11 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     if (timed) {
         K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed + 1], s));
         st.timed++;
-        st.timed_evals += (uint64_t)cnt * st.n;
+        st.timed_evals += (uint64_t)live * st.n;
     }
     if (finalize)
         K8S_LAUNCH(ctx, score_finalize_kernel, ceil_div(cnt, 256), 256, 0, s, bk, st.podq.as<PodQ>(),
-                   st.active[st.cur].as<uint32_t>(), order, lo, cnt, st.n, d_best);
+                   st.active[st.cur].as<uint32_t>(), order, sm, cnt, st.n, d_best);
     return K8SGPU_OK;
 }
 
@@ -1448,7 +1494,7 @@ int round_admit(k8sgpu_ctx *ctx, const int32_t *d_best_all, cudaStream_t s, uint
 // best_key[0..n_active) as score_kernel left it, and leaves the next round's node records ready.
 // Launch half: returns as soon as the kernel is queued, so that a caller driving several GPUs can
 // queue all of them before it waits for any (round_admit_coop_finish).
-int round_admit_coop_launch(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals) {
+int round_admit_coop_launch(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals, uint32_t xw) {
     PlaceState &st = ctx->place;
     const uint32_t na = st.n_active;
     uint32_t *cnts = st.counters.as<uint32_t>();
@@ -1464,6 +1510,8 @@ int round_admit_coop_launch(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *prop
     a.best_key_clear = st.best_key.as<unsigned long long>();
     a.proposals = proposals;
     a.inv_cur = st.order_valid ? st.inv[st.cur].as<uint32_t>() : nullptr;
+    a.xw = xw;
+    a.xcnt = xw > 1 ? group_slot_count(st.n_active, xw) : 0;
     a.pod_cls = st.pod_cls.as<uint8_t>();
     a.order_next = st.order_valid ? st.order[st.cur ^ 1].as<uint32_t>() : nullptr;
     a.inv_next = st.order_valid ? st.inv[st.cur ^ 1].as<uint32_t>() : nullptr;
@@ -1547,22 +1595,31 @@ int round_admit_coop_finish(k8sgpu_ctx *ctx, cudaStream_t s) {
 
 
 int round_admit_coop(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *proposals) {
-    int rc = round_admit_coop_launch(ctx, s, proposals);
+    int rc = round_admit_coop_launch(ctx, s, proposals, 1);
     if (rc) return rc;
     return round_admit_coop_finish(ctx, s);
 }
 
 // Decode the packed best keys of active positions [lo, hi) and store each proposal at its
 // position in every buffer of `peer` (this GPU's own and the other ranks', mapped peer memory).
-int round_finalize_peers(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *const *peer, int world, cudaStream_t s) {
+int round_finalize_peers(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *const *peer, int world, cudaStream_t s,
+                         uint32_t xw, uint32_t xrank) {
     PlaceState &st = ctx->place;
-    if (hi <= lo) return K8SGPU_OK;
+    SlotMap sm;
+    sm.lo = lo;
+    sm.hi = hi;
+    sm.xw = xw;
+    sm.xrank = xrank;
+    sm.xcnt = xw > 1 ? group_slot_count(hi, xw) : hi - lo;
+    if (sm.xcnt == 0) return K8SGPU_OK;
     PeerPtrs pp;
     for (int r = 0; r < 16; ++r) pp.p[r] = r < world ? peer[r] : nullptr;
     pp.world = world;
-    K8S_LAUNCH(ctx, score_finalize_p2p_kernel, ceil_div(hi - lo, 256), 256, 0, s, st.best_key.as<unsigned long long>(),
+    // where this launch's first slot sits in every exchange buffer
+    const uint32_t base = xw > 1 ? xrank * sm.xcnt : lo;
+    K8S_LAUNCH(ctx, score_finalize_p2p_kernel, ceil_div(sm.xcnt, 256), 256, 0, s, st.best_key.as<unsigned long long>(),
                st.podq.as<PodQ>(), st.active[st.cur].as<uint32_t>(),
-               st.order_valid ? st.order[st.cur].as<uint32_t>() : nullptr, lo, hi - lo, st.n, pp);
+               st.order_valid ? st.order[st.cur].as<uint32_t>() : nullptr, sm, sm.xcnt, st.n, base, pp);
     return K8SGPU_OK;
 }
 
@@ -2028,7 +2085,7 @@ extern "C" int k8sgpu_place_round_score_p2p(k8sgpu_ctx *ctx, uint32_t lo, uint32
         const size_t half = (size_t)(st.rounds & 1u) * st.peer_m;
         int32_t *pp[16];
         for (int r = 0; r < 16; ++r) pp[r] = r < st.peer_world ? st.peer_ptr[r] + half : nullptr;
-        rc = round_finalize_peers(ctx, lo, hi, pp, st.peer_world, s);
+        rc = round_finalize_peers(ctx, lo, hi, pp, st.peer_world, s, 1, 0);
         if (rc) return rc;
     }
     return K8SGPU_OK;
