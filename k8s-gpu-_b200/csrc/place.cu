@@ -169,6 +169,20 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
 
 // ------------------------------------------------------------------ scoring
 
+template <int PPT> __device__ __forceinline__ uint4 ldrec(const uint4 *p);
+// One 128-bit shared-memory load, kept whole: the class-specialised loops use only some words of a
+// node record, and left to itself the compiler splits the load into narrower ones (3 LDS per node
+// instead of 2 -- issue slots the loop does not have).
+__device__ __forceinline__ uint4 lds128(const uint4 *p) {
+    uint4 v;
+    asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
+    return v;
+}
+// Half a node record for the inner loops.  With four pods per thread one record feeds four evals,
+// the loads are a smaller share of the issue slots, and the freedom to schedule them matters more
+// (measured: config 4 is 6 % slower with the pinned loads), so that variant keeps plain loads.
+template <int PPT> __device__ __forceinline__ uint4 ldrec(const uint4 *p) { return PPT >= 4 ? *p : lds128(p); }
+
 // One pod x one node: filter (a11), key (a12), running max.  Written as PTX so that the
 // feasibility clauses stay one predicate chain with no separate predicate-combine instruction:
 // the loop is bound by the integer ALU pipe (ncu: >90 % busy), so every ALU instruction removed
@@ -488,7 +502,7 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
 #define K8S_GROUP(CLS)                                                                                           \
     _Pragma("unroll 1") for (uint32_t kb = g; kb < g + kGroup; kb += 16) {                                       \
         _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
-            const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];                                          \
+            const uint4 a = ldrec<PPT>(&tl[2 * (kb + i)]), b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                \
             _Pragma("unroll") for (int j = 0; j < PPT; ++j)                                                      \
                 eval_pair<RES, CLS>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j], negone); \
         }                                                                                                        \
@@ -510,14 +524,26 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
 #pragma unroll
                     for (int j = 0; j < PPT; ++j) cx |= (rrel[j] - kb) < 8u;
                     if (!__any_sync(0xFFFFFFFFu, cx)) {
-#pragma unroll
-                        for (uint32_t i = 0; i < 8; ++i) {
-                            const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];
-#pragma unroll
-                            for (int j = 0; j < PPT; ++j)
-                                eval_pair<RES>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j],
-                                               best[j], negone);
+                        // (with ~64 pods per warp and 157 groups of 64 nodes at config 3, four in ten
+                        // groups come through here: these chunks are class-specialised as well)
+#define K8S_CHUNK(CLS)                                                                                           \
+    _Pragma("unroll") for (uint32_t i = 0; i < 8; ++i) {                                                         \
+        const uint4 a = ldrec<PPT>(&tl[2 * (kb + i)]), b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                    \
+        _Pragma("unroll") for (int j = 0; j < PPT; ++j)                                                          \
+            eval_pair<RES, CLS>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j], negone); \
+    }
+                        // (not with four pods per thread: on wide node tables few groups come this
+                        // way, and the extra code cost config 4 10 % -- registers spilled)
+                        if (RES != 4 || PPT >= 4 || wcls == 3) {
+                            K8S_CHUNK(3)
+                        } else if (wcls == 0) {
+                            K8S_CHUNK(0)
+                        } else if (wcls == 2) {
+                            K8S_CHUNK(2)
+                        } else {
+                            K8S_CHUNK(1)
                         }
+#undef K8S_CHUNK
                     } else {  // rare: rot(p) of some pod of this warp falls inside this 8-node chunk
 #pragma unroll 1
                         for (uint32_t i = 0; i < 8; ++i) {
