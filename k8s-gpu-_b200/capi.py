@@ -32,7 +32,7 @@ EXPORTS = (
 )
 UNIQUE_ID_BYTES = 128
 TUNING_KEYS = ("res", "ppt", "splits", "coop", "coop_grid", "rec_path", "rec_grid", "rec_segments", "coop_prof",
-               "rec_prof", "shard_admit", "exchange", "order", "force_cls", "shard_upload")
+               "rec_prof", "shard_admit", "exchange", "order", "force_cls", "shard_upload", "slot_admit")
 ASSIGN_GANG = -3
 SCAN_NOALLOC_MAX_N = 1 << 24
 

@@ -20,7 +20,7 @@ static int *tuning_slot(Tuning &t, const char *key) {
     } table[] = {{"res", &t.res}, {"ppt", &t.ppt}, {"splits", &t.splits}, {"coop", &t.coop},
                  {"coop_grid", &t.coop_grid}, {"rec_path", &t.rec_path}, {"rec_grid", &t.rec_grid},
                  {"rec_segments", &t.rec_segments}, {"coop_prof", &t.coop_prof}, {"rec_prof", &t.rec_prof},
-                 {"shard_admit", &t.shard_admit}, {"exchange", &t.exchange}, {"force_cls", &t.force_cls}, {"order", &t.order}, {"shard_upload", &t.shard_upload}};
+                 {"shard_admit", &t.shard_admit}, {"exchange", &t.exchange}, {"force_cls", &t.force_cls}, {"order", &t.order}, {"shard_upload", &t.shard_upload}, {"slot_admit", &t.slot_admit}};
     for (auto &e : table)
         if (strcmp(e.name, key) == 0) return e.slot;
     return nullptr;
@@ -28,7 +28,7 @@ static int *tuning_slot(Tuning &t, const char *key) {
 
 static void tuning_from_env(Tuning &t) {
     static const char *names[] = {"res", "ppt", "splits", "coop", "coop_grid", "rec_path", "rec_grid",
-                                  "rec_segments", "coop_prof", "rec_prof", "shard_admit", "exchange", "force_cls", "order", "shard_upload"};
+                                  "rec_segments", "coop_prof", "rec_prof", "shard_admit", "exchange", "force_cls", "order", "shard_upload", "slot_admit"};
     for (const char *n : names) {
         char env[64] = "K8SGPU_";
         size_t k = strlen(env);
@@ -174,7 +174,7 @@ extern "C" int k8sgpu_destroy(k8sgpu_ctx *ctx) {
     group_destroy(ctx);
     PlaceState &p = ctx->place;
     DevBuf *pb[] = {&p.node_cols, &p.pod_cols, &p.free_cols, &p.nodeq,     &p.podq,      &p.assign, &p.active[0],
-                    &p.active[1], &p.order[0], &p.order[1], &p.inv[0], &p.inv[1], &p.pod_cls, &p.best_key, &p.best,      &p.sort_keys, &p.sort_vals, &p.seg,    &p.flags,
+                    &p.active[1], &p.order[0], &p.order[1], &p.inv[0], &p.inv[1], &p.pod_cls, &p.slots, &p.best_key, &p.best,      &p.sort_keys, &p.sort_vals, &p.seg,    &p.flags,
                     &p.counters,  &p.scan_tmp,  &p.gang_id,  &p.gang_min,  &p.gang_count, &p.gang_state};
     for (int r = 0; r < p.peer_world; ++r)
         if (r != p.peer_rank && p.peer_ptr[r]) cudaIpcCloseMemHandle(p.peer_ptr[r]);

@@ -69,6 +69,7 @@ struct PlaceState {
     DevBuf order[2];   // m u32: active positions sorted by pod class = the scoring kernel's thread -> pod map
     DevBuf inv[2];     // m u32: inverse of order (position -> slot), for proposals that arrive by slot
     DevBuf pod_cls;    // m u8: eval_pair class of each pod
+    DevBuf slots;      // n x 8 u32: slot admission, first proposers of the round per node
     bool want_order = false;   // this run sorts its scoring order by class (the in-library loops do)
     bool order_valid = false;  // order[cur] / inv[cur] describe active[cur]
     DevBuf best_key;   // m u64, indexed by active position
@@ -140,6 +141,7 @@ struct Tuning {
     int coop_prof = 0, rec_prof = 0;  // print phase times (stderr)
     int shard_upload = -1;  // multi-GPU: 0 = every rank copies the whole pod table from the host
     int shard_admit = -1;   // multi-GPU: 1 = admission sharded by node range, 0 = replicated
+    int slot_admit = -1;    // 0: always the sort-based admission
     int order = -1;         // 0: do not sort the scoring order by pod class
     int force_cls = -1;     // timing experiments only: eval_pair class for every warp (results are wrong)
     int exchange = -1;      // multi-GPU: 0 = NCCL all-gather, 1 = peer stores, -1 = per round by list length

@@ -38,6 +38,10 @@ struct __align__(16) PodQ {
 static_assert(sizeof(PodQ) == 32, "pod record is 32 B");
 
 constexpr uint32_t kErrNode = 1u, kErrPod = 2u, kErrProposal = 4u;
+constexpr uint32_t kSlotsPerNode = 8;  // slot admission (admit_coop_kernel): first proposers kept per node
+// counters[5] != 0 rules the slot admission out for this run: 1 = some pod asks for 0 GPUs,
+// 2 = some node has more than kSlotsPerNode free GPUs
+constexpr int kSlotVeto = 5;
 
 __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -76,6 +80,7 @@ __global__ void __launch_bounds__(256) pod_prep_kernel(const uint32_t *__restric
                     ? 0u
                     : (uint32_t)(mix64((uint64_t)p + 0x9E3779B97F4A7C15ull) % (uint64_t)n_nodes);
         if ((q.req_gpu | q.req_mcpu | q.req_mib) & 0x80000000u) atomicOr(err, kErrPod);
+        if (q.req_gpu == 0u) atomicOr(err + kSlotVeto, 1u);
         if (pz >= 32u && pz != K8SGPU_NONE_U32) atomicOr(err, kErrPod);
         podq[p] = q;
         assign[p] = K8SGPU_ASSIGN_PENDING;
@@ -110,6 +115,7 @@ __device__ __forceinline__ NodeQ make_nodeq(const uint32_t *__restrict__ cols, c
         uint32_t taint = cols[6 * (size_t)n + i], flags = cols[7 * (size_t)n + i];
         if (validate && (fg > 0x7FFFu || cap > 255u || sku >= 32u || zone >= 32u || ((fc | fm) & 0x80000000u)))
             atomicOr(err, kErrNode);
+        if (validate && fg > kSlotsPerNode) atomicOr(err + kSlotVeto, 2u);
         q.free_gpu_s = (flags & 1u) ? fg : 0xFFFFFFFFu;
         q.free_mcpu = fc;
         q.free_mib = fm;
@@ -956,6 +962,7 @@ struct AdmitArgs {
     const uint8_t *pod_cls;              // eval_pair class per pod
     uint32_t *order_next, *inv_next;     // next round's scoring order and its inverse (null: not built)
     uint32_t xw, xcnt;                   // placement group: ranks, local slots per rank (see SlotMap); else 1, 0
+    uint32_t *slots;                     // kSlotsPerNode per node: first proposers of the round (0xFFFFFFFF = empty)
     const PodQ *podq;
     const uint32_t *active;
     uint32_t *next_active;
@@ -990,6 +997,106 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
     const uint32_t na = a.na, N = a.n_nodes;
     const uint32_t nb = (na + kSortTile - 1) / kSortTile;
 
+    // Which admission.  A node with f free GPUs can admit at most f pods that each ask for at
+    // least one GPU, and the admitted pods are a PREFIX of its proposers in pod order (the sums S
+    // only grow).  So when every pod asks for >= 1 GPU and no node has more than kSlotsPerNode
+    // free (checked once per run on the device: counters[5]), the round needs, per node, only its
+    // first free_gpu proposers: they are collected in a small sorted slot array per node by a
+    // cascade of atomicMin (keep the smaller, carry the larger down), and one thread per node
+    // walks its slots.  No sort, no segmented scan, 3 grid barriers instead of 7.  The cascade is
+    // exact whatever the interleaving: every operation conserves the multiset {slot, carried
+    // value} and slots only decrease, so a value among the k smallest can never be carried past
+    // slot k - 1, and what reaches slot s + 1 is larger than slot s ends up.
+    const bool slot_path = a.slots != nullptr && __ldcg(&a.counters[kSlotVeto]) == 0u;
+    uint32_t *sk = a.keys, *sv = a.vals;
+    if (slot_path) {
+        for (uint32_t i0 = cta * 256; i0 < na; i0 += G * 256) {  // (whole warps: the votes below need every lane)
+            const uint32_t i = i0 + tid;
+            int32_t b = -1;
+            if (i < na) {
+                const uint32_t pod = a.active[i];
+                if (a.proposals) {
+                    b = a.proposals[exchange_index(a.inv_cur ? a.inv_cur[i] : i, a.xw, a.xcnt)];
+                    if (b < -1 || b >= (int32_t)N) {
+                        atomicOr(&a.counters[0], kErrProposal);
+                        b = -1;
+                    }
+                } else {
+                    const unsigned long long k64 = a.best_key[i];
+                    if (k64 != 0ull) {
+                        const uint32_t n = (0xFFFFFFFFu - (uint32_t)k64) + a.podq[pod].rot;
+                        b = (int32_t)(n >= N ? n - N : n);
+                    }
+                }
+                if (b < 0) a.assign[pod] = K8SGPU_ASSIGN_NONE;
+            }
+            // Lanes are consecutive positions: of the lanes of this warp that propose to the same
+            // node only the first k can be among that node's first k proposers.  On a contested
+            // node this takes most of the traffic off its eight slot words.
+            const uint32_t peers = __match_any_sync(0xFFFFFFFFu, b);
+            if (b < 0) continue;
+            uint32_t *sl = a.slots + (size_t)b * kSlotsPerNode;
+            const uint32_t k = a.freec[b];  // 1 .. kSlotsPerNode: the node was feasible for this pod
+            if (k - 1u >= kSlotsPerNode) {  // a proposal the scoring kernel cannot have made for these tables
+                atomicOr(&a.counters[0], kErrProposal);
+                continue;
+            }
+            if ((uint32_t)__popc(peers & ((1u << (tid & 31u)) - 1u)) >= k) continue;
+            // the k-th smallest so far is already before me: I cannot be among the first k
+            if (__ldcg(&sl[k - 1]) < i) continue;
+            uint32_t v = i;
+            for (uint32_t j = 0; j < k; ++j) {
+                const uint32_t old = atomicMin(&sl[j], v);
+                if (old > v) {
+                    if (old == 0xFFFFFFFFu) break;  // took an empty slot: nothing to carry
+                    v = old;
+                }
+            }
+        }
+        grid.sync();
+        prof_mark(a, 1);
+        for (uint32_t n = cta * 256 + tid; n < N; n += G * 256) {
+            uint4 *sl = reinterpret_cast<uint4 *>(a.slots + (size_t)n * kSlotsPerNode);
+            const uint4 s0 = __ldcg(sl), s1 = __ldcg(sl + 1);
+            if (s0.x == 0xFFFFFFFFu) continue;  // nobody proposed to this node
+            const uint32_t pos[kSlotsPerNode] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+            uint32_t pod[kSlotsPerNode];
+            uint4 rq[kSlotsPerNode];
+#pragma unroll
+            for (uint32_t j = 0; j < kSlotsPerNode; ++j) pod[j] = pos[j] != 0xFFFFFFFFu ? a.active[pos[j]] : 0u;
+#pragma unroll
+            for (uint32_t j = 0; j < kSlotsPerNode; ++j)
+                rq[j] = pos[j] != 0xFFFFFFFFu ? *reinterpret_cast<const uint4 *>(a.podq + pod[j]) : make_uint4(0, 0, 0, 0);
+            const uint32_t fg = a.freec[n], fc = a.freec[(size_t)N + n], fm = a.freec[2 * (size_t)N + n];
+            uint32_t sg = 0, sc = 0, sm = 0, ag = 0, ac = 0, am = 0;
+            bool open = true;
+#pragma unroll
+            for (uint32_t j = 0; j < kSlotsPerNode; ++j) {
+                if (pos[j] == 0xFFFFFFFFu) open = false;
+                if (!open) continue;
+                sg = sat_add(sg, rq[j].x);  // a13: inclusive sums over the proposers, in pod order
+                sc = sat_add(sc, rq[j].y);
+                sm = sat_add(sm, rq[j].z);
+                if (sg <= fg && sc <= fc && sm <= fm) {
+                    a.assign[pod[j]] = (int32_t)n;
+                    ag += rq[j].x;
+                    ac += rq[j].y;
+                    am += rq[j].z;
+                } else {
+                    open = false;  // the sums only grow: nobody after this one fits either
+                }
+            }
+            a.freec[n] = fg - ag;  // this thread owns the node: plain stores
+            a.freec[(size_t)N + n] = fc - ac;
+            a.freec[2 * (size_t)N + n] = fm - am;
+            sl[0] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);  // empty again for the next round
+            sl[1] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+        }
+        grid.sync();
+        prof_mark(a, 2);
+        prof_mark(a, 3);
+        prof_mark(a, 4);
+    } else {
     // phase 0: packed best key -> proposal; sort key = node (N for "no feasible node"); digit-0 histogram
     for (uint32_t vt = cta; vt < nb; vt += G) {
         // all loads of the tile first: the stores below would otherwise order each row's loads
@@ -1037,7 +1144,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
     prof_mark(a, 1);
 
     // stable LSD radix sort by node, 8 bits a pass
-    uint32_t *sk = a.keys, *sv = a.vals, *dk = a.keys_alt, *dv = a.vals_alt;
+    uint32_t *dk = a.keys_alt, *dv = a.vals_alt;
     for (int shift = 0; shift < a.bits; shift += 8) {
         const int w = a.bits - shift < 8 ? a.bits - shift : 8;
         const uint32_t mask = (1u << w) - 1u;
@@ -1098,6 +1205,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
         __syncthreads();
     }
     grid.sync();
+    }  // (sort-based admission)
     prof_mark(a, 5);
     // free -= admitted (commutative integer atomics), pending flags in ORIGINAL active order, and
     // the number of still-pending pods per 256-element chunk (in hist_scan: the sort is done with it)
@@ -1110,9 +1218,11 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
         uint32_t f = 0;
         if (i < na) {
             // independent loads first (the two chains then overlap instead of running back to back)
-            const uint32_t admitted = a.offs[i], key = sk[i], pod_sorted = sv[i], pod_here = a.active[i];
+            const uint32_t pod_here = a.active[i];
+            const uint32_t admitted = slot_path ? 0u : a.offs[i], key = slot_path ? 0u : sk[i],
+                           pod_sorted = slot_path ? 0u : sv[i];
             const int32_t state = a.assign[pod_here];
-            if (admitted) {
+            if (admitted) {  // (sort-based admission; the slot walk has updated its nodes already)
                 const PodQ *q = a.podq + pod_sorted;
                 const uint32_t rg = q->req_gpu, rc = q->req_mcpu, rm = q->req_mib;
                 if (rg) atomicSub(&a.freec[key], rg);
@@ -1309,6 +1419,7 @@ int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_p
         K8S_CUDA(ctx, st.inv[b].reserve(m * 4 + 16));
     }
     K8S_CUDA(ctx, st.pod_cls.reserve(m + 16));
+    K8S_CUDA(ctx, st.slots.reserve(((size_t)n + 1) * kSlotsPerNode * 4));
     K8S_CUDA(ctx, st.best_key.reserve(m * 8 + 16));
     K8S_CUDA(ctx, st.best.reserve(m * 4 + 16));
     K8S_CUDA(ctx, st.sort_keys.reserve(m * 4 + 16));
@@ -1343,6 +1454,7 @@ int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
     st.score_res = kDefaultRes;  // which eval_pair variant (see its comment); all are bit-identical
     if (ctx->tune.res >= 0) st.score_res = ctx->tune.res;
     K8S_CUDA(ctx, cudaMemsetAsync(st.counters.p, 0, 64 * 4, s));
+    K8S_CUDA(ctx, cudaMemsetAsync(st.slots.p, 0xFF, ((size_t)st.n + 1) * kSlotsPerNode * 4, s));  // every node's slots empty
     if (st.n)
         K8S_CUDA(ctx, cudaMemcpyAsync(st.free_cols.p, st.node_cols.p, 3 * (size_t)st.n * 4, cudaMemcpyDeviceToDevice, s));
     // Scoring order by pod class: only with the class-specialised eval_pair (RES = 4) and the
@@ -1538,6 +1650,7 @@ int round_admit_coop_launch(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *prop
     a.inv_cur = st.order_valid ? st.inv[st.cur].as<uint32_t>() : nullptr;
     a.xw = xw;
     a.xcnt = xw > 1 ? group_slot_count(st.n_active, xw) : 0;
+    a.slots = ctx->tune.slot_admit != 0 ? st.slots.as<uint32_t>() : nullptr;
     a.pod_cls = st.pod_cls.as<uint8_t>();
     a.order_next = st.order_valid ? st.order[st.cur ^ 1].as<uint32_t>() : nullptr;
     a.inv_next = st.order_valid ? st.inv[st.cur ^ 1].as<uint32_t>() : nullptr;

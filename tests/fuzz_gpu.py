@@ -31,7 +31,10 @@ def pick_size(rng, hi):
 
 def random_nodes(rng, n):
     skew = rng.random()
-    cap = rng.choice([1, 2, 4, 8, 16], n).astype(np.uint32) if skew > 0.2 else np.full(n, 8, np.uint32)
+    # (half the cases keep every node at <= 8 free GPUs: with pods that all ask for >= 1 GPU that is
+    # the domain of the slot admission; the other half, and pods asking for 0 GPUs, veto it)
+    caps = [1, 2, 4, 8, 16] if rng.random() < 0.5 else [1, 2, 4, 8]
+    cap = rng.choice(caps, n).astype(np.uint32) if skew > 0.2 else np.full(n, 8, np.uint32)
     free = (rng.integers(0, 17, n) % (cap + 1)).astype(np.uint32) if skew > 0.1 else cap.copy()
     return dict(free_gpu=free, free_mcpu=(free * rng.choice([4000, 12000])).astype(np.uint32),
                 free_mib=(free * rng.choice([28672, 243200])).astype(np.uint32), cap_gpu=cap,
@@ -43,7 +46,8 @@ def random_nodes(rng, n):
 
 def random_pods(rng, m):
     alike = rng.random() < 0.25
-    g = np.full(m, rng.choice([1, 2]), np.uint32) if alike else rng.choice([0, 1, 1, 1, 2, 4, 8, 40], m).astype(np.uint32)
+    sizes = [0, 1, 1, 1, 2, 4, 8, 40] if rng.random() < 0.4 else [1, 1, 1, 2, 4, 8]
+    g = np.full(m, rng.choice([1, 2]), np.uint32) if alike else rng.choice(sizes, m).astype(np.uint32)
     anymask = lambda p: np.where(rng.random(m) < p, rng.integers(0, 2 ** 32, m, dtype=np.uint64), NONE).astype(np.uint32)
     return dict(req_gpu=g, req_mcpu=(g * 4000).astype(np.uint32), req_mib=(g * 28672).astype(np.uint32),
                 sku_mask=np.full(m, NONE, np.uint32) if alike else anymask(0.3),
@@ -63,7 +67,8 @@ def case_place(rng, ctx):
     nodes, pods = random_nodes(rng, n), random_pods(rng, m)
     flags = int(rng.random() < 0.2)
     env = dict(res=int(rng.choice([0, 1, 2, 3, 4, 4, 4, 4])), ppt=int(rng.choice([1, 2, 4])), coop=int(rng.choice([0, 1, 1])),
-               order=int(rng.choice([0, 1, 1])))  # order: scoring order sorted by pod class (RES 4 + one-launch admission)
+               order=int(rng.choice([0, 1, 1])),  # order: scoring order sorted by pod class (RES 4 + one-launch admission)
+               slot_admit=int(rng.choice([0, 1, 1])))  # slot admission where its domain holds, else the sort
     if rng.random() < 0.5:
         env["splits"] = int(rng.integers(1, 9))
     if rng.random() < 0.5:  # few CTAs in the single-launch admission: every CTA loops over several tiles

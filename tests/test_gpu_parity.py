@@ -214,6 +214,34 @@ def test_place_class_sorted_scoring_order(ctx, orc, synth, order, n, m, coop_gri
     same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
 
 
+@pytest.mark.parametrize("slot_admit", [0, 1])
+@pytest.mark.parametrize("case", ["hetero", "ties_rot0", "zero_gpu_pod", "big_node", "one_node", "coop_grid_1"])
+def test_place_slot_admission(ctx, orc, synth, slot_admit, case):
+    """Admission by per-node slot arrays (the first free_gpu proposers of each node, no sort) against
+    the oracle, next to the sort-based admission: mixed tables, everyone proposing to one node, and
+    the two inputs that rule the slot path out for a run (a pod asking for 0 GPUs; a node with more
+    than 8 free GPUs), where the kernel must take the sort on its own."""
+    flags = 0
+    if case == "ties_rot0":
+        nodes, pods = synth.gen_identical(40, 700)
+        flags = 1
+    elif case == "one_node":
+        nodes, pods = synth.gen_identical(1, 3000)
+    else:
+        nodes, pods = synth.gen_nodes(900, config_id=5), synth.gen_pods(30_000, config_id=5)
+    if case == "zero_gpu_pod":
+        pods["req_gpu"] = pods["req_gpu"].copy()
+        pods["req_gpu"][::7] = 0
+    if case == "big_node":
+        for k, per in (("free_gpu", 1), ("free_mcpu", 12000), ("free_mib", 243200)):
+            nodes[k] = nodes[k].copy()
+            nodes[k][5] = 12 * per
+        nodes["cap_gpu"] = nodes["cap_gpu"].copy()
+        nodes["cap_gpu"][5] = 16
+    ctx.set_tuning(slot_admit=slot_admit, coop_grid=1 if case == "coop_grid_1" else None)
+    same_placement(ctx.place(nodes, pods, flags=flags), orc.place(nodes, pods, flags=flags, nthreads=NCPU))
+
+
 def test_k12_ties_rot_zero(ctx, synth):
     nodes, pods = synth.gen_identical(5, 41)
     r = ctx.place(nodes, pods, flags=1)
