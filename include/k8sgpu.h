@@ -279,6 +279,10 @@ int k8sgpu_place_gang_end(k8sgpu_ctx *ctx, void *stream, int32_t *gang_ok);
  *            1-element all-reduce on the same stream) before k8sgpu_place_round_admit.
  * No reference counterpart. */
 int k8sgpu_peer_export(k8sgpu_ctx *ctx, uint32_t m, void *handle64, void **d_local);
+/* Unmaps the peers' buffers.  Before a group exports NEW buffers (a larger pod table), every rank
+ * calls this and the ranks meet at a barrier of their own: exported memory must not be freed
+ * while another process still maps it. */
+int k8sgpu_peer_close(k8sgpu_ctx *ctx);
 int k8sgpu_peer_import(k8sgpu_ctx *ctx, int rank, int world, const void *handles);
 int k8sgpu_place_round_score_p2p(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, void *stream);
 

@@ -28,7 +28,7 @@ EXPORTS = (
     "k8sgpu_place_gang", "k8sgpu_peer_export", "k8sgpu_peer_import", "k8sgpu_place_round_score_p2p",
     "k8sgpu_place_gang_begin", "k8sgpu_place_gang_verdicts", "k8sgpu_place_gang_end",
     "k8sgpu_create_ex", "k8sgpu_set_tuning", "k8sgpu_reconcile_out_size", "k8sgpu_comm_unique_id",
-    "k8sgpu_comm_init_rank", "k8sgpu_group_info",
+    "k8sgpu_comm_init_rank", "k8sgpu_group_info", "k8sgpu_peer_close",
 )
 UNIQUE_ID_BYTES = 128
 TUNING_KEYS = ("res", "ppt", "splits", "coop", "coop_grid", "rec_path", "rec_grid", "rec_segments", "coop_prof",
@@ -134,6 +134,7 @@ def load() -> C.CDLL:
         L.k8sgpu_place_round_end.argtypes = [vp, vp]
         L.k8sgpu_peer_export.argtypes = [vp, C.c_uint32, vp, C.POINTER(vp)]
         L.k8sgpu_peer_import.argtypes = [vp, C.c_int, C.c_int, vp]
+        L.k8sgpu_peer_close.argtypes = [vp]
         L.k8sgpu_place_round_score_p2p.argtypes = [vp, C.c_uint32, C.c_uint32, vp]
         L.k8sgpu_place_gang_begin.argtypes = [vp, C.POINTER(GangTable), C.POINTER(Policy), vp, u32p]
         L.k8sgpu_place_gang_verdicts.argtypes = [vp, vp, u32p]
@@ -371,6 +372,9 @@ class Context:
         p = C.c_void_p()
         self._check(self._L.k8sgpu_peer_export(self._h, m, C.cast(h, C.c_void_p), C.byref(p)))
         return bytes(h), p.value
+
+    def peer_close(self):
+        self._check(self._L.k8sgpu_peer_close(self._h))
 
     def peer_import(self, rank: int, world: int, handles: bytes):
         buf = (C.c_ubyte * len(handles)).from_buffer_copy(handles)

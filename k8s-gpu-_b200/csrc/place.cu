@@ -2169,15 +2169,27 @@ extern "C" int k8sgpu_place_round_end(k8sgpu_ctx *ctx, void *stream) {
 
 // ------------------------------------------------------------------ peer exchange (one process per GPU)
 
+// Unmaps every peer's exchange buffer.  Memory exported over CUDA IPC must not be freed while
+// another process still maps it, so before a group re-exports (k8sgpu_peer_export frees the old
+// buffer) every rank calls this and the ranks meet at a barrier of their own.
+extern "C" int k8sgpu_peer_close(k8sgpu_ctx *ctx) {
+    K8S_ENTER(ctx);
+    PlaceState &st = ctx->place;
+    for (int r = 0; r < 16; ++r) {
+        if (r != st.peer_rank && st.peer_ptr[r]) cudaIpcCloseMemHandle(st.peer_ptr[r]);
+        st.peer_ptr[r] = nullptr;
+    }
+    st.peer_world = 0;
+    st.peer_rank = -1;
+    return K8SGPU_OK;
+}
+
 extern "C" int k8sgpu_peer_export(k8sgpu_ctx *ctx, uint32_t m, void *handle64, void **d_local) {
     K8S_ENTER(ctx);
     if (!handle64) return fail(ctx, K8SGPU_E_ARG, "peer_export: NULL handle buffer");
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
     PlaceState &st = ctx->place;
-    for (int r = 0; r < st.peer_world; ++r)  // drop mappings of an earlier exchange buffer
-        if (r != st.peer_rank && st.peer_ptr[r]) cudaIpcCloseMemHandle(st.peer_ptr[r]);
-    st.peer_world = 0;
-    st.peer_rank = -1;
+    k8sgpu_peer_close(ctx);  // (our own mappings; see k8sgpu_peer_close for the other direction)
     st.peer_local.release();  // a fresh allocation: its handle must match what peers will open
     K8S_CUDA(ctx, st.peer_local.reserve((size_t)(m ? m : 1u) * 2 * 4));  // two halves, used by round parity
     st.peer_m = m ? m : 1u;
@@ -2194,17 +2206,23 @@ extern "C" int k8sgpu_peer_import(k8sgpu_ctx *ctx, int rank, int world, const vo
     if (world < 1 || world > 16 || rank < 0 || rank >= world || !handles)
         return fail(ctx, K8SGPU_E_ARG, "peer_import: bad rank/world (%d/%d; at most 16 ranks)", rank, world);
     if (!st.peer_local.p) return fail(ctx, K8SGPU_E_ARG, "peer_import: call k8sgpu_peer_export first");
+    for (int r = 0; r < 16; ++r) st.peer_ptr[r] = nullptr;
     for (int r = 0; r < world; ++r) {
-        if (r == rank) {
-            st.peer_ptr[r] = st.peer_local.as<int32_t>();
-            continue;
-        }
+        if (r == rank) continue;
         cudaIpcMemHandle_t h;
         memcpy(&h, static_cast<const char *>(handles) + 64 * (size_t)r, 64);
         void *p = nullptr;
-        K8S_CUDA(ctx, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {  // leave nothing half-mapped behind
+            for (int q = 0; q < r; ++q) {
+                if (st.peer_ptr[q]) cudaIpcCloseMemHandle(st.peer_ptr[q]);
+                st.peer_ptr[q] = nullptr;
+            }
+            return fail(ctx, K8SGPU_E_CUDA, "peer_import: mapping rank %d's buffer: %s", r, cudaGetErrorString(e));
+        }
         st.peer_ptr[r] = static_cast<int32_t *>(p);
     }
+    st.peer_ptr[rank] = st.peer_local.as<int32_t>();
     st.peer_world = world;
     st.peer_rank = rank;
     return K8SGPU_OK;

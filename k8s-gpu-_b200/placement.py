@@ -64,6 +64,9 @@ class CudaEngine:
         Done once; repeated only if a later upload has more pods than the buffer holds."""
         if self.p2p_ready and self.m <= self._peer_m:
             return
+        if self.p2p_ready:  # a larger table: nobody may free a buffer that a peer still maps
+            self.ctx.peer_close()
+            dist.barrier()
         self._peer_m = max(self.m, 1)
         handle, self._peer_local = self.ctx.peer_export(self._peer_m)
         handles = [None] * world
