@@ -1517,10 +1517,11 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     // CTA at config 3), which measured 3-4 % faster than ~20 (profiles/r01_sweep_res4_ppt.txt).
     const uint32_t sms = (uint32_t)ctx->sm_count;
     // Pods per thread: two share every shared-memory read of a node record, which is what makes
-    // the 7-ALU variant (RES = 4) pay -- with one pod per thread it is issue bound at 15 slots per
-    // eval.  Four pay only on wide node tables, where few 64-node groups contain some pod's rot(p)
-    // (profiles/r01_sweep_res4_ppt.txt).
-    int ppt = st.score_res == 4 ? ((st.n >= 65536u && cnt >= 4u * 256u * 2u * sms) ? 4 : 2) : 1;
+    // the 7-ALU variant (RES = 4) pay -- with one pod per thread it is issue bound.  Four per thread
+    // used to win on wide node tables (fewer 64-node groups contain some pod's rot(p)); since the
+    // loops are class-specialised two win everywhere (config 4: 377 vs 411 ms per placement), so
+    // four is a knob only.
+    int ppt = st.score_res == 4 ? 2 : 1;
     if (ctx->tune.ppt >= 1) ppt = ctx->tune.ppt >= 4 ? 4 : ctx->tune.ppt >= 2 ? 2 : 1;
     if (ppt == 4 && st.score_res != 4) ppt = 2;
     const uint32_t xb = ceil_div(cnt, 256u * ppt);
