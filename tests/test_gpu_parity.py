@@ -242,6 +242,33 @@ def test_place_slot_admission(ctx, orc, synth, slot_admit, case):
     same_placement(ctx.place(nodes, pods, flags=flags), orc.place(nodes, pods, flags=flags, nthreads=NCPU))
 
 
+def test_context_creation_and_knob_errors(ctx, capi):
+    """k8sgpu_create_ex reports its failures in the caller's buffer; an unknown knob is an error,
+    not a silent no-op; a one-GPU context is a group of one."""
+    with pytest.raises(capi.K8sGpuError) as e:
+        capi.Context([0, 0])
+    assert e.value.code == capi.E_ARG and "twice" in str(e.value)
+    with pytest.raises(capi.K8sGpuError) as e:
+        capi.Context(4096)
+    assert e.value.code == capi.E_ARG and "out of range" in str(e.value)
+    with pytest.raises(capi.K8sGpuError) as e:
+        ctx.set_tuning(no_such_knob=1)
+    assert e.value.code == capi.E_ARG and "no_such_knob" in str(e.value)
+    info = ctx.group_info()
+    assert (info["world"], info["rank"], info["nlocal"]) == (1, 0, 1)
+    with pytest.raises(capi.K8sGpuError):  # a context cannot join a group with a bad rank
+        ctx.comm_init_rank(3, 2, b"\0" * capi.UNIQUE_ID_BYTES)
+
+
+def test_place_without_priority_column(ctx, orc, synth):
+    """priority is reserved (policy v0 admits in pod-index order): it may be left out."""
+    nodes, pods = synth.gen_nodes(300, config_id=5), synth.gen_pods(4000, config_id=5)
+    want = orc.place(nodes, pods, nthreads=NCPU)
+    slim = {k: v for k, v in pods.items() if k != "priority"}
+    slim["priority"] = None
+    same_placement(ctx.place(nodes, slim), want)
+
+
 def test_k12_ties_rot_zero(ctx, synth):
     nodes, pods = synth.gen_identical(5, 41)
     r = ctx.place(nodes, pods, flags=1)
