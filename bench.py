@@ -175,8 +175,16 @@ def reference_arm(args, rank, world):
     EMIT(line)
 
 
+_PINNED = []  # page-locked blocks stay alive until the process ends
+
+
 def pinned_block(torch, n_elems):
-    return torch.empty(max(int(n_elems), 1), dtype=torch.int32).pin_memory().numpy().view(np.uint32)
+    """uint32 array in page-locked host memory from the library's own allocator (k8sgpu_host_alloc)."""
+    from k8sgpu_b200 import capi
+
+    blk = capi.PinnedBlock(max(int(n_elems), 1))
+    _PINNED.append(blk)
+    return blk.array
 
 
 def slab(torch, cols, order):

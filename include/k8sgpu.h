@@ -172,6 +172,13 @@ int k8sgpu_comm_init_rank(k8sgpu_ctx *ctx, int rank, int world, const void *id12
  * any pointer may be NULL. */
 int k8sgpu_group_info(const k8sgpu_ctx *ctx, int *world, int *rank, int *nlocal, int *nccl_version);
 
+/* Page-locked ("pinned") host memory for tables and results.  Not required -- any host memory works
+ * -- but copies from and to pinned buffers are asynchronous and run at the full PCIe rate; a cgo
+ * caller gets that without binding the CUDA runtime itself (snapshot staging).  Free
+ * with k8sgpu_host_free.  K8SGPU_E_CUDA when no device / no memory.  No reference counterpart. */
+int k8sgpu_host_alloc(size_t bytes, void **out);
+int k8sgpu_host_free(void *p);
+
 /* Developer and test knobs by name ("res", "ppt", "splits", "coop", "coop_grid", "rec_path",
  * "rec_grid", "rec_segments", "coop_prof", "rec_prof", "exchange", "shard_admit"; -1 = automatic).
  * Every setting gives bit-identical results: they select kernel variants and launch shapes.  The

@@ -28,7 +28,7 @@ EXPORTS = (
     "k8sgpu_place_gang", "k8sgpu_peer_export", "k8sgpu_peer_import", "k8sgpu_place_round_score_p2p",
     "k8sgpu_place_gang_begin", "k8sgpu_place_gang_verdicts", "k8sgpu_place_gang_end",
     "k8sgpu_create_ex", "k8sgpu_set_tuning", "k8sgpu_reconcile_out_size", "k8sgpu_comm_unique_id",
-    "k8sgpu_comm_init_rank", "k8sgpu_group_info", "k8sgpu_peer_close",
+    "k8sgpu_comm_init_rank", "k8sgpu_group_info", "k8sgpu_peer_close", "k8sgpu_host_alloc", "k8sgpu_host_free",
 )
 UNIQUE_ID_BYTES = 128
 TUNING_KEYS = ("res", "ppt", "splits", "coop", "coop_grid", "rec_path", "rec_grid", "rec_segments", "coop_prof",
@@ -135,6 +135,8 @@ def load() -> C.CDLL:
         L.k8sgpu_peer_export.argtypes = [vp, C.c_uint32, vp, C.POINTER(vp)]
         L.k8sgpu_peer_import.argtypes = [vp, C.c_int, C.c_int, vp]
         L.k8sgpu_peer_close.argtypes = [vp]
+        L.k8sgpu_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
+        L.k8sgpu_host_free.argtypes = [vp]
         L.k8sgpu_place_round_score_p2p.argtypes = [vp, C.c_uint32, C.c_uint32, vp]
         L.k8sgpu_place_gang_begin.argtypes = [vp, C.POINTER(GangTable), C.POINTER(Policy), vp, u32p]
         L.k8sgpu_place_gang_verdicts.argtypes = [vp, vp, u32p]
@@ -186,6 +188,27 @@ def pod_table(pods: dict):
         keep.append(a)
         setattr(t, c, p)
     return t, keep
+
+
+class PinnedBlock:
+    """`n` uint32 elements of page-locked host memory from k8sgpu_host_alloc, as a numpy array
+    (`.array`); freed when the object is closed or collected."""
+
+    def __init__(self, n: int):
+        self._L = load()
+        self._p = C.c_void_p()
+        rc = self._L.k8sgpu_host_alloc(max(int(n), 1) * 4, C.byref(self._p))
+        if rc != OK:
+            raise K8sGpuError(rc, "k8sgpu_host_alloc failed")
+        self.array = np.ctypeslib.as_array(C.cast(self._p, u32p), shape=(max(int(n), 1),))[: int(n)]
+
+    def close(self):
+        if getattr(self, "_p", None) and self._p.value:
+            self.array = None
+            self._L.k8sgpu_host_free(self._p)
+            self._p = C.c_void_p()
+
+    __del__ = close
 
 
 def unique_id() -> bytes:

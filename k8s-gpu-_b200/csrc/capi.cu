@@ -198,6 +198,24 @@ extern "C" int k8sgpu_destroy(k8sgpu_ctx *ctx) {
     return K8SGPU_OK;
 }
 
+// Page-locked host memory for the caller's tables and results: a cgo or ctypes caller gets the
+// asynchronous, full-rate PCIe copies of pinned buffers without binding the CUDA runtime itself.
+extern "C" int k8sgpu_host_alloc(size_t bytes, void **out) {
+    if (!out) return K8SGPU_E_ARG;
+    *out = nullptr;
+    cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return K8SGPU_E_CUDA;
+    }
+    return K8SGPU_OK;
+}
+
+extern "C" int k8sgpu_host_free(void *p) {
+    if (!p) return K8SGPU_OK;
+    return cudaFreeHost(p) == cudaSuccess ? K8SGPU_OK : K8SGPU_E_CUDA;
+}
+
 extern "C" int k8sgpu_get_stats(const k8sgpu_ctx *ctx, k8sgpu_stats *out) {
     if (!ctx || !out) return K8SGPU_E_ARG;
     *out = ctx->stats;

@@ -260,6 +260,25 @@ def test_context_creation_and_knob_errors(ctx, capi):
         ctx.comm_init_rank(3, 2, b"\0" * capi.UNIQUE_ID_BYTES)
 
 
+def test_pinned_host_blocks_from_the_library(ctx, capi, orc, synth):
+    """Tables and results in page-locked memory handed out by k8sgpu_host_alloc (what a cgo caller
+    would use), columns back to back: same bytes as from ordinary numpy arrays."""
+    nodes, pods = synth.gen_nodes(500, config_id=5), synth.gen_pods(6000, config_id=5)
+    nb, pb, ob = capi.PinnedBlock(8 * 500), capi.PinnedBlock(8 * 6000), capi.PinnedBlock(3 * 500 + 6000)
+    hn = {k: nb.array[c * 500:(c + 1) * 500] for c, k in enumerate(capi.NODE_COLS)}
+    hp = {k: pb.array[c * 6000:(c + 1) * 6000] for c, k in enumerate(capi.POD_COLS)}
+    for k in hn:
+        hn[k][:] = nodes[k]
+    for k in hp:
+        hp[k][:] = pods[k]
+    out = {k: ob.array[c * 500:(c + 1) * 500] for c, k in enumerate(("free_gpu", "free_mcpu", "free_mib"))}
+    out["assign"] = ob.array[1500:].view(np.int32)
+    got = ctx.place(hn, hp, out=out)
+    same_placement(got, orc.place(nodes, pods, nthreads=NCPU))
+    for b in (nb, pb, ob):
+        b.close()
+
+
 def test_place_without_priority_column(ctx, orc, synth):
     """priority is reserved (policy v0 admits in pod-index order): it may be left out."""
     nodes, pods = synth.gen_nodes(300, config_id=5), synth.gen_pods(4000, config_id=5)
