@@ -174,7 +174,7 @@ extern "C" int k8sgpu_destroy(k8sgpu_ctx *ctx) {
     group_destroy(ctx);
     PlaceState &p = ctx->place;
     DevBuf *pb[] = {&p.node_cols, &p.pod_cols, &p.free_cols, &p.nodeq,     &p.podq,      &p.assign, &p.active[0],
-                    &p.active[1], &p.order[0], &p.order[1], &p.inv[0], &p.inv[1], &p.pod_cls, &p.slots, &p.best_key, &p.best,      &p.sort_keys, &p.sort_vals, &p.seg,    &p.flags,
+                    &p.active[1], &p.order[0], &p.order[1], &p.inv[0], &p.inv[1], &p.slots, &p.best_key, &p.best,      &p.sort_keys, &p.sort_vals, &p.seg,    &p.flags,
                     &p.counters,  &p.scan_tmp,  &p.gang_id,  &p.gang_min,  &p.gang_count, &p.gang_state};
     for (int r = 0; r < p.peer_world; ++r)
         if (r != p.peer_rank && p.peer_ptr[r]) cudaIpcCloseMemHandle(p.peer_ptr[r]);

@@ -66,9 +66,8 @@ struct PlaceState {
     DevBuf podq;       // m x 32 B packed pod records (built at begin)
     DevBuf assign;     // m i32
     DevBuf active[2];  // m u32 each
-    DevBuf order[2];   // m u32: active positions sorted by pod class = the scoring kernel's thread -> pod map
-    DevBuf inv[2];     // m u32: inverse of order (position -> slot), for proposals that arrive by slot
-    DevBuf pod_cls;    // m u8: eval_pair class of each pod
+    DevBuf order[2];   // m u32: the active pods in scoring order (class, rot bucket): the scoring kernel's slot -> pod map
+    DevBuf inv[2];     // m u32 each: [0] posof[pod] = position in the active list, [1] slotof[pod] = slot in order[cur]
     DevBuf slots;      // n x 8 u32: slot admission, first proposers of the round per node
     bool want_order = false;   // this run sorts its scoring order by class (the in-library loops do)
     bool order_valid = false;  // order[cur] / inv[cur] describe active[cur]

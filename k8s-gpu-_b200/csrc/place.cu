@@ -51,59 +51,45 @@ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
 
 // ------------------------------------------------------------------ table preparation
 
-// Also: the pod's eval_pair class (bit 0: restricts SKUs or zones, bit 1: prefers a zone) in
-// pod_cls[p], and -- when the run sorts its scoring order by class -- flags0[p] = 1 + class and the
-// per-class counts of this block's 256 pods in chunk_tot[block] (see class_partition_tile).
+// Also, when the run keeps a scoring order (see "scoring order" below): the pod's sort key
+// (eval_pair class << 8 | which 256th of the node table rot(p) falls into), its own index as the
+// sort payload, and posof[p] = p (every pod starts active at its own position).
 __global__ void __launch_bounds__(256) pod_prep_kernel(const uint32_t *__restrict__ cols, uint32_t m, uint32_t n_nodes,
                                                        uint32_t policy, int mul_masks, PodQ *__restrict__ podq,
                                                        int32_t *__restrict__ assign, uint32_t *__restrict__ active,
-                                                       uint32_t *__restrict__ err, uint8_t *__restrict__ pod_cls,
-                                                       uint32_t *__restrict__ flags0,
-                                                       unsigned long long *__restrict__ chunk_tot) {
+                                                       uint32_t *__restrict__ err, uint32_t *__restrict__ sort_key,
+                                                       uint32_t *__restrict__ sort_val, uint32_t *__restrict__ posof) {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t cls = 4;  // 4 = no pod here
-    if (p < m) {
-        PodQ q;
-        q.req_gpu = cols[0 * (size_t)m + p];
-        q.req_mcpu = cols[1 * (size_t)m + p];
-        q.req_mib = cols[2 * (size_t)m + p];
-        q.nsku = ~cols[3 * (size_t)m + p];
-        q.nzone = __brev(~cols[4 * (size_t)m + p]);  // bit-reversed, like NodeQ::zone_bit
-        if (mul_masks) {  // eval_pair RES = 4: each mask is mirrored against its node-side one-hot word
-            q.nsku = __brev(q.nsku);
-            q.nzone = __brev(q.nzone);
-        }
-        q.ntol = ~cols[5 * (size_t)m + p];
-        uint32_t pz = cols[6 * (size_t)m + p];
-        q.pzb = pz < 32u ? (1u << pz) : 0u;
-        q.rot = ((policy & K8SGPU_POLICY_ROT_ZERO) || n_nodes == 0)
-                    ? 0u
-                    : (uint32_t)(mix64((uint64_t)p + 0x9E3779B97F4A7C15ull) % (uint64_t)n_nodes);
-        if ((q.req_gpu | q.req_mcpu | q.req_mib) & 0x80000000u) atomicOr(err, kErrPod);
-        if (q.req_gpu == 0u) atomicOr(err + kSlotVeto, 1u);
-        if (pz >= 32u && pz != K8SGPU_NONE_U32) atomicOr(err, kErrPod);
-        podq[p] = q;
-        assign[p] = K8SGPU_ASSIGN_PENDING;
-        active[p] = p;
-        cls = ((q.nsku | q.nzone) ? 1u : 0u) | (q.pzb ? 2u : 0u);
-        pod_cls[p] = (uint8_t)cls;
-        if (flags0) flags0[p] = 1u + cls;
+    if (p >= m) return;
+    PodQ q;
+    q.req_gpu = cols[0 * (size_t)m + p];
+    q.req_mcpu = cols[1 * (size_t)m + p];
+    q.req_mib = cols[2 * (size_t)m + p];
+    q.nsku = ~cols[3 * (size_t)m + p];
+    q.nzone = __brev(~cols[4 * (size_t)m + p]);  // bit-reversed, like NodeQ::zone_bit
+    if (mul_masks) {  // eval_pair RES = 4: each mask is mirrored against its node-side one-hot word
+        q.nsku = __brev(q.nsku);
+        q.nzone = __brev(q.nzone);
     }
-    if (!chunk_tot) return;  // (block-uniform)
-    // (ballots + shared counters, not four __syncthreads_count in a row: back-to-back barrier
-    // reductions raised "illegal instruction" in the admission kernel on B200)
-    __shared__ uint32_t ccnt[4];
-    if (threadIdx.x < 4) ccnt[threadIdx.x] = 0;
-    __syncthreads();
-#pragma unroll
-    for (uint32_t k = 0; k < 4; ++k) {
-        const uint32_t mk = __ballot_sync(0xFFFFFFFFu, cls == k);
-        if ((threadIdx.x & 31u) == 0 && mk) atomicAdd(&ccnt[k], (uint32_t)__popc(mk));
+    q.ntol = ~cols[5 * (size_t)m + p];
+    uint32_t pz = cols[6 * (size_t)m + p];
+    q.pzb = pz < 32u ? (1u << pz) : 0u;
+    q.rot = ((policy & K8SGPU_POLICY_ROT_ZERO) || n_nodes == 0)
+                ? 0u
+                : (uint32_t)(mix64((uint64_t)p + 0x9E3779B97F4A7C15ull) % (uint64_t)n_nodes);
+    if ((q.req_gpu | q.req_mcpu | q.req_mib) & 0x80000000u) atomicOr(err, kErrPod);
+    if (q.req_gpu == 0u) atomicOr(err + kSlotVeto, 1u);
+    if (pz >= 32u && pz != K8SGPU_NONE_U32) atomicOr(err, kErrPod);
+    podq[p] = q;
+    assign[p] = K8SGPU_ASSIGN_PENDING;
+    active[p] = p;
+    if (sort_key) {
+        const uint32_t cls = ((q.nsku | q.nzone) ? 1u : 0u) | (q.pzb ? 2u : 0u);
+        const uint32_t bucket = n_nodes ? (uint32_t)(((unsigned long long)q.rot << 8) / n_nodes) : 0u;  // 0 .. 255
+        sort_key[p] = (cls << 8) | bucket;
+        sort_val[p] = p;
+        posof[p] = p;
     }
-    __syncthreads();
-    if (threadIdx.x == 0)
-        chunk_tot[blockIdx.x] = (unsigned long long)ccnt[0] | ((unsigned long long)ccnt[1] << 16) |
-                                ((unsigned long long)ccnt[2] << 32) | ((unsigned long long)ccnt[3] << 48);
 }
 
 __device__ __forceinline__ NodeQ make_nodeq(const uint32_t *__restrict__ cols, const uint32_t *__restrict__ freec,
@@ -429,7 +415,8 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
                                                     const uint32_t *__restrict__ active, SlotMap sm,
                                                     unsigned long long *__restrict__ best_key, uint32_t n_nodes,
                                                     int use_atomic, uint32_t negone, int cls_force,
-                                                    const uint32_t *__restrict__ order) {
+                                                    const uint32_t *__restrict__ spod,
+                                                    const uint32_t *__restrict__ posof) {
     // kStages-deep ring of node tiles.  full[b]: the TMA copy into buffer b has landed (one
     // arrival + its byte count); empty[b]: all 8 warps are done reading buffer b (one arrival per
     // warp).  No __syncthreads in the tile loop: a warp may run a tile ahead of its slowest sibling.
@@ -460,14 +447,24 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
     uint32_t best[PPT], bestn[PPT];
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
-        // thread -> active position: straight, or through the round's class-sorted scoring order
+        // thread -> pod: the active position itself, or the slot of the round's scoring order
         uint32_t slot;
         const bool live = slot_of(sm, (blockIdx.x * PPT + j) * 256u + tid, &slot);
-        pos[j] = live ? (order ? __ldg(&order[slot]) : slot) : 0xFFFFFFFFu;
+        uint32_t pod = 0;
+        pos[j] = 0xFFFFFFFFu;
+        if (live) {
+            if (spod) {
+                pod = __ldg(&spod[slot]);
+                pos[j] = __ldg(&posof[pod]);
+            } else {
+                pos[j] = slot;
+                pod = active[slot];
+            }
+        }
         best[j] = 0;
         bestn[j] = 0;
         if (live) {
-            const uint4 *q = reinterpret_cast<const uint4 *>(podq + active[pos[j]]);
+            const uint4 *q = reinterpret_cast<const uint4 *>(podq + pod);
             uint4 a = __ldg(q), b = __ldg(q + 1);
             rg[j] = a.x; rc[j] = a.y; rm[j] = a.z; nsku[j] = a.w;
             nzone[j] = b.x; ntol[j] = b.y; pzb[j] = b.z; rot[j] = b.w;
@@ -612,24 +609,35 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
     }
 }
 
-// Proposals travel by SLOT (the index the scoring kernel's threads are numbered by): slot i of
-// [lo, lo + cnt) belongs to active position order[lo + i], or to position lo + i without an order.
+// Proposals travel by SLOT (the index the scoring kernel's threads are numbered by): slot s is the
+// pod spod[s] of the round's scoring order, at active position posof[pod]; without an order, slot
+// and active position are the same thing.
+struct SlotView {
+    const uint32_t *active, *spod, *posof;
+};
 __device__ __forceinline__ int32_t decode_proposal(const unsigned long long *__restrict__ best_key,
-                                                   const PodQ *__restrict__ podq, const uint32_t *__restrict__ active,
-                                                   const uint32_t *__restrict__ order, uint32_t slot, uint32_t n_nodes) {
-    const uint32_t pos = order ? __ldg(&order[slot]) : slot;
+                                                   const PodQ *__restrict__ podq, const SlotView &v, uint32_t slot,
+                                                   uint32_t n_nodes) {
+    uint32_t pod, pos;
+    if (v.spod) {
+        pod = __ldg(&v.spod[slot]);
+        pos = __ldg(&v.posof[pod]);
+    } else {
+        pos = slot;
+        pod = v.active[slot];
+    }
     const unsigned long long key = best_key[pos];
     if (key == 0ull) return -1;
-    const uint32_t n = (0xFFFFFFFFu - (uint32_t)key) + podq[active[pos]].rot;  // < 2N < 2^32
+    const uint32_t n = (0xFFFFFFFFu - (uint32_t)key) + podq[pod].rot;  // < 2N < 2^32
     return (int32_t)(n >= n_nodes ? n - n_nodes : n);
 }
 
 __global__ void score_finalize_kernel(const unsigned long long *__restrict__ best_key, const PodQ *__restrict__ podq,
-                                      const uint32_t *__restrict__ active, const uint32_t *__restrict__ order,
-                                      SlotMap sm, uint32_t cnt, uint32_t n_nodes, int32_t *__restrict__ out) {
+                                      SlotView view, SlotMap sm, uint32_t cnt, uint32_t n_nodes,
+                                      int32_t *__restrict__ out) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, slot;
     if (i >= cnt) return;
-    out[i] = slot_of(sm, i, &slot) ? decode_proposal(best_key, podq, active, order, slot, n_nodes) : -1;
+    out[i] = slot_of(sm, i, &slot) ? decode_proposal(best_key, podq, view, slot, n_nodes) : -1;
 }
 
 // Decode the packed best key of this launch's slots and store each proposal straight into EVERY
@@ -640,12 +648,11 @@ struct PeerPtrs {
     int world;
 };
 __global__ void score_finalize_p2p_kernel(const unsigned long long *__restrict__ best_key,
-                                          const PodQ *__restrict__ podq, const uint32_t *__restrict__ active,
-                                          const uint32_t *__restrict__ order, SlotMap sm, uint32_t cnt,
+                                          const PodQ *__restrict__ podq, SlotView view, SlotMap sm, uint32_t cnt,
                                           uint32_t n_nodes, uint32_t base, PeerPtrs peers) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, slot;
     if (i >= cnt || !slot_of(sm, i, &slot)) return;
-    const int32_t node = decode_proposal(best_key, podq, active, order, slot, n_nodes);
+    const int32_t node = decode_proposal(best_key, podq, view, slot, n_nodes);
 #pragma unroll 1
     for (int r = 0; r < peers.world; ++r) peers.p[r][base + i] = node;
 }
@@ -841,110 +848,67 @@ __global__ void count_placed_kernel(const int32_t *__restrict__ assign, uint32_t
     if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(out, cnt);
 }
 
-// ------------------------------------------------------------------ scoring order by pod class
+// ------------------------------------------------------------------ scoring order
 //
-// eval_pair leaves out the clauses no pod of a warp needs (its CLS parameter), which only pays if
-// warps are uniform.  So each round's scoring kernel walks the active list through `order`: the
-// active positions sorted by pod class (0..3), stable inside a class.  The order is built where
-// the next active list is built, from the same per-chunk counts: flags[i] = 0 (settled) or
-// 1 + class of the pod at active position i; chunk_tot[c] = pending pods of chunk c (256
-// positions) per class, four 16-bit fields.  One CTA handles one tile of 2048 positions: it sums the
-// chunk counts before its tile (and all of them, for the class bases), scans its own tile with one
-// 64-bit scan (the four class counts side by side), and writes
-//   next_active[q] = pod       q = stable position among the pending pods (pod order kept)
-//   order[o] = q, inv[q] = o   o = class base + rank inside the class
-// Admission order is untouched (next_active stays in pod order); only which THREAD scores which
-// pod changes.  Returns the number of pending pods up to and including this tile (all threads).
-__device__ __forceinline__ uint32_t class_partition_tile(uint32_t vt, uint32_t na, const uint32_t *flags,
-                                                         const uint32_t *active, const unsigned long long *chunk_tot,
-                                                         uint32_t *next_active, uint32_t *order, uint32_t *inv) {
-    __shared__ uint32_t psum[8][8];
-    __shared__ unsigned long long wtot64[8];
+// eval_pair leaves out the clauses no pod of a warp needs (its CLS parameter), and the scan takes
+// its slow path only in the 64-node groups that hold some pod's rot(p).  Both pay only if the pods
+// of a warp are alike, so the scoring kernel does not walk the active list in pod order: it walks
+// `spod`, the active pods sorted ONCE per run by (class, which 256th of the node table rot(p)
+// falls into) -- one 10-bit stable sort -- and compacted every round next to the active list.
+// Warps are then class-uniform, and the 64 pods of a warp cross into "n >= rot(p)" inside one or
+// two groups instead of in four groups out of ten (config 3: 11 % of the scoring time).
+// Admission order is untouched -- the active list stays in pod order; only which THREAD scores
+// which pod changes.  posof[pod] = the pod's position in the active list, slotof[pod] = its slot
+// in spod (proposals are exchanged between GPUs by slot).
+//
+// One tile (2048 entries) of a stable compaction: dst[q] = src[i] for the flagged entries, in
+// order, and index_of[src[i]] = q.  chunk_tot[c] = flagged entries of chunk c (256 entries).
+// Returns the number of flagged entries up to and including this tile (all threads).
+__device__ __forceinline__ uint32_t compact_tile(uint32_t vt, uint32_t na, const uint32_t *flags, const uint32_t *src,
+                                                 const uint32_t *chunk_tot, uint32_t *dst, uint32_t *index_of) {
+    __shared__ uint32_t part[8], wtot[8];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    const uint32_t nchunks = (na + 255u) / 256u, first = vt * (kScanTile / 256u);
-    uint32_t bef[4] = {0, 0, 0, 0}, tot[4] = {0, 0, 0, 0};
-    for (uint32_t c = tid; c < nchunks; c += 256u) {
-        const unsigned long long x = __ldcg(&chunk_tot[c]);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint32_t v = (uint32_t)(x >> (16 * k)) & 0xFFFFu;
-            tot[k] += v;
-            bef[k] += c < first ? v : 0u;
-        }
-    }
+    const uint32_t first = vt * (kScanTile / 256u);
+    uint32_t before = 0;
+    for (uint32_t c = tid; c < first; c += 256u) before += __ldcg(&chunk_tot[c]);
     const uint32_t i0 = vt * kScanTile + tid * 8u;
-    uint32_t f[8], act[8];
-    unsigned long long mine = 0;
+    uint32_t f[8], v[8], mine = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         const bool in = i0 + k < na;
         f[k] = in ? flags[i0 + k] : 0u;
-        act[k] = in ? active[i0 + k] : 0u;
-        if (f[k]) mine += 1ull << (16u * (f[k] - 1u));
+        v[k] = in ? src[i0 + k] : 0u;
+        mine += f[k];
     }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        bef[k] = __reduce_add_sync(0xFFFFFFFFu, bef[k]);
-        tot[k] = __reduce_add_sync(0xFFFFFFFFu, tot[k]);
-    }
-    unsigned long long inc = mine;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const unsigned long long y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
-        if ((int)lane >= d) inc += y;
-    }
+    before = __reduce_add_sync(0xFFFFFFFFu, before);
+    const uint32_t inc = warp_incl_scan(mine, (int)lane);
     __syncthreads();  // shared scratch of the previous tile / phase is no longer read
-    if (lane == 0) {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            psum[warp][k] = bef[k];
-            psum[warp][4 + k] = tot[k];
-        }
-    }
-    if (lane == 31) wtot64[warp] = inc;
+    if (lane == 0) part[warp] = before;
+    if (lane == 31) wtot[warp] = inc;
     __syncthreads();
-    unsigned long long woff = 0, tile = 0;
+    uint32_t woff = 0, tile = 0;
+    before = 0;
 #pragma unroll
     for (uint32_t w = 0; w < 8; ++w) {
-        const unsigned long long t = wtot64[w];
-        if (w < warp) woff += t;
-        tile += t;
+        before += part[w];
+        woff += w < warp ? wtot[w] : 0u;
+        tile += wtot[w];
     }
-    uint32_t base[4], before_all = 0, acc = 0;
+    uint32_t q = before + woff + inc - mine;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        uint32_t b = 0, t = 0;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) {
-            b += psum[w][k];
-            t += psum[w][4 + k];
+    for (int k = 0; k < 8; ++k)
+        if (f[k]) {
+            dst[q] = v[k];
+            index_of[v[k]] = q;
+            ++q;
         }
-        before_all += b;
-        base[k] = acc + b;  // class base (all pods of lower classes) + pods of this class before the tile
-        acc += t;
-    }
-    unsigned long long excl = woff + inc - mine;  // per class: pending pods of this tile before this thread
-    uint32_t q = before_all + (uint32_t)(excl & 0xFFFFu) + (uint32_t)((excl >> 16) & 0xFFFFu) +
-                 (uint32_t)((excl >> 32) & 0xFFFFu) + (uint32_t)(excl >> 48);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        if (!f[k]) continue;
-        const uint32_t c = f[k] - 1u;
-        const uint32_t o = base[c] + (uint32_t)((excl >> (16u * c)) & 0xFFFFu);
-        next_active[q] = act[k];
-        order[o] = q;
-        inv[q] = o;
-        excl += 1ull << (16u * c);
-        ++q;
-    }
-    return before_all + (uint32_t)(tile & 0xFFFFu) + (uint32_t)((tile >> 16) & 0xFFFFu) +
-           (uint32_t)((tile >> 32) & 0xFFFFu) + (uint32_t)(tile >> 48);
+    return before + tile;
 }
 
-// Round 0: every pod is active at its own index.  flags / chunk counts come from pod_prep_kernel.
-__global__ void __launch_bounds__(256) order0_kernel(uint32_t m, const uint32_t *flags, uint32_t *active,
-                                                     const unsigned long long *chunk_tot, uint32_t *order, uint32_t *inv) {
-    class_partition_tile(blockIdx.x, m, flags, active, chunk_tot, active, order, inv);
+// slotof[spod[j]] = j after the one-time sort of a run.
+__global__ void slot_init_kernel(const uint32_t *__restrict__ spod, uint32_t m, uint32_t *__restrict__ slotof) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < m) slotof[spod[j]] = j;
 }
 
 // ------------------------------------------------------------------ admission, one launch
@@ -958,9 +922,10 @@ struct AdmitArgs {
     const unsigned long long *best_key;  // by active position (score_kernel output)
     unsigned long long *best_key_clear;  // the same array: cleared at the end for the next round's atomicMax
     const int32_t *proposals;            // or: node row per scoring slot (exchanged between GPUs); else null
-    const uint32_t *inv_cur;             // active position -> scoring slot of this round (null: identity)
-    const uint8_t *pod_cls;              // eval_pair class per pod
-    uint32_t *order_next, *inv_next;     // next round's scoring order and its inverse (null: not built)
+    const uint32_t *spod;                // this round's scoring order (pods; null: none, slot = active position)
+    uint32_t *spod_next;                 // ... the next round's, compacted here
+    uint32_t *posof, *slotof;            // per pod: position in the active list / slot in spod (updated here)
+    uint32_t *gflags;                    // na u32 scratch: pending flag per slot
     uint32_t xw, xcnt;                   // placement group: ranks, local slots per rank (see SlotMap); else 1, 0
     uint32_t *slots;                     // kSlotsPerNode per node: first proposers of the round (0xFFFFFFFF = empty)
     const PodQ *podq;
@@ -1016,7 +981,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
             if (i < na) {
                 const uint32_t pod = a.active[i];
                 if (a.proposals) {
-                    b = a.proposals[exchange_index(a.inv_cur ? a.inv_cur[i] : i, a.xw, a.xcnt)];
+                    b = a.proposals[exchange_index(a.spod ? a.slotof[pod] : i, a.xw, a.xcnt)];
                     if (b < -1 || b >= (int32_t)N) {
                         atomicOr(&a.counters[0], kErrProposal);
                         b = -1;
@@ -1109,7 +1074,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
             pod[r] = i < na ? a.active[i] : 0u;
             if (a.proposals) {  // already decoded: re-encode as "distance 0 from rot = node" below
                 // proposals arrive by slot, and in a group by (rank, local slot)
-                int32_t b = i < na ? a.proposals[exchange_index(a.inv_cur ? a.inv_cur[i] : i, a.xw, a.xcnt)] : -1;
+                int32_t b = i < na ? a.proposals[exchange_index(a.spod ? a.slotof[pod[r]] : i, a.xw, a.xcnt)] : -1;
                 if (b < -1 || b >= (int32_t)N) {  // not something score_kernel can produce: a stale or
                     atomicOr(&a.counters[0], kErrProposal);  // unsynchronised buffer was handed in
                     b = -1;
@@ -1212,7 +1177,7 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
     const uint32_t nt = (na + kScanTile - 1) / kScanTile, nchunks = (na + 255u) / 256u;
     const bool local_scan = nt <= kLocalScanMaxTiles;
     uint32_t *chunk_tot = a.hist_scan;
-    __shared__ uint32_t red[8], ccnt[4];
+    __shared__ uint32_t red[8];
     for (uint32_t c = cta; c < nchunks; c += G) {
         const uint32_t i = c * 256 + tid;
         uint32_t f = 0;
@@ -1230,39 +1195,32 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
                 if (rm) atomicSub(&a.freec[2 * (size_t)N + key], rm);
             }
             f = state == K8SGPU_ASSIGN_PENDING ? 1u : 0u;
-            if (a.order_next && f) f += a.pod_cls[pod_here];  // 1 + class (see class_partition_tile)
             a.flags[i] = f;
         }
-        if (a.order_next) {  // pending pods of the chunk per class, four 16-bit fields
-            // (ballots + shared counters: four __syncthreads_count in a row raised "illegal
-            // instruction" here on B200)
-            if (tid < 4) ccnt[tid] = 0;
-            __syncthreads();
-#pragma unroll
-            for (uint32_t k = 0; k < 4; ++k) {
-                const uint32_t mk = __ballot_sync(0xFFFFFFFFu, f == k + 1u);
-                if ((tid & 31u) == 0 && mk) atomicAdd(&ccnt[k], (uint32_t)__popc(mk));
+        const uint32_t cnt = (uint32_t)__syncthreads_count((int)f);
+        if (tid == 0) chunk_tot[c] = cnt;
+    }
+    uint32_t *chunk_tot2 = chunk_tot + nchunks;  // the same count per chunk of the scoring order
+    if (a.spod) {
+        for (uint32_t c = cta; c < nchunks; c += G) {
+            const uint32_t j = c * 256 + tid;
+            uint32_t g = 0;
+            if (j < na) {
+                g = a.assign[a.spod[j]] == K8SGPU_ASSIGN_PENDING ? 1u : 0u;
+                a.gflags[j] = g;
             }
-            __syncthreads();
-            if (tid == 0)
-                reinterpret_cast<unsigned long long *>(chunk_tot)[c] =
-                    (unsigned long long)ccnt[0] | ((unsigned long long)ccnt[1] << 16) |
-                    ((unsigned long long)ccnt[2] << 32) | ((unsigned long long)ccnt[3] << 48);
-            __syncthreads();  // ccnt is reused by the next chunk
-        } else {
-            const uint32_t cnt = (uint32_t)__syncthreads_count((int)f);
-            if (tid == 0) chunk_tot[c] = cnt;
+            const uint32_t cnt = (uint32_t)__syncthreads_count((int)g);
+            if (tid == 0) chunk_tot2[c] = cnt;
         }
     }
     grid.sync();
     prof_mark(a, 6);
-    if (a.order_next) {
-        // Next active list (stable, pod order) and next scoring order (by class) in one pass over
-        // each tile; the CTA that owns the last tile knows the next round's length and tells the host.
+    if (a.spod) {
+        // Next active list (pod order) and next scoring order (its own order), each a stable
+        // compaction by the same pending test; the CTA that owns the last tile of the active list
+        // knows the next round's length and tells the host before it goes on.
         for (uint32_t vt = cta; vt < nt; vt += G) {
-            const uint32_t upto = class_partition_tile(vt, na, a.flags, a.active,
-                                                       reinterpret_cast<const unsigned long long *>(chunk_tot),
-                                                       a.next_active, a.order_next, a.inv_next);
+            const uint32_t upto = compact_tile(vt, na, a.flags, a.active, chunk_tot, a.next_active, a.posof);
             if (vt == nt - 1 && tid == 0) {
                 a.counters[1] = upto;
                 volatile uint32_t *mb = a.mailbox;
@@ -1272,6 +1230,8 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
                 mb[0] = a.seq;
             }
         }
+        for (uint32_t vt = cta; vt < nt; vt += G)
+            compact_tile(vt, na, a.gflags, a.spod, chunk_tot2, a.spod_next, a.slotof);
         prof_mark(a, 7);
     } else if (local_scan) {
         // Stable compaction without a scan phase: each CTA adds up the pending counts of the tiles
@@ -1418,7 +1378,6 @@ int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_p
         K8S_CUDA(ctx, st.order[b].reserve(m * 4 + 16));
         K8S_CUDA(ctx, st.inv[b].reserve(m * 4 + 16));
     }
-    K8S_CUDA(ctx, st.pod_cls.reserve(m + 16));
     K8S_CUDA(ctx, st.slots.reserve(((size_t)n + 1) * kSlotsPerNode * 4));
     K8S_CUDA(ctx, st.best_key.reserve(m * 8 + 16));
     K8S_CUDA(ctx, st.best.reserve(m * 4 + 16));
@@ -1457,21 +1416,20 @@ int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
     K8S_CUDA(ctx, cudaMemsetAsync(st.slots.p, 0xFF, ((size_t)st.n + 1) * kSlotsPerNode * 4, s));  // every node's slots empty
     if (st.n)
         K8S_CUDA(ctx, cudaMemcpyAsync(st.free_cols.p, st.node_cols.p, 3 * (size_t)st.n * 4, cudaMemcpyDeviceToDevice, s));
-    // Scoring order by pod class: only with the class-specialised eval_pair (RES = 4) and the
-    // one-launch admission, which rebuilds the order each round next to the active list.
+    // Scoring order (see "scoring order" above): only with the class-specialised eval_pair (RES = 4)
+    // and the one-launch admission, which compacts it every round next to the active list.
     const bool ordered = st.want_order && st.score_res == 4 && coop_admission(ctx) && ctx->tune.order != 0 && st.m > 0;
     st.order_valid = false;
     if (st.m) {
-        const uint32_t nb = ceil_div(st.m, kSortTile);
-        unsigned long long *chunk_tot = reinterpret_cast<unsigned long long *>(st.sort.hist.as<uint32_t>() + (size_t)nb * 256);
-        uint32_t *flags0 = st.flags.as<uint32_t>();
+        uint32_t *spod = st.order[0].as<uint32_t>(), *posof = st.inv[0].as<uint32_t>(), *slotof = st.inv[1].as<uint32_t>();
+        uint32_t *keys = st.sort_keys.as<uint32_t>();
         K8S_LAUNCH(ctx, pod_prep_kernel, ceil_div(st.m, 256), 256, 0, s, st.pod_cols.as<uint32_t>(), st.m, st.n,
                    st.policy_flags, st.score_res == 4 ? 1 : 0, st.podq.as<PodQ>(), st.assign.as<int32_t>(),
-                   st.active[0].as<uint32_t>(), st.counters.as<uint32_t>(), st.pod_cls.as<uint8_t>(),
-                   ordered ? flags0 : nullptr, ordered ? chunk_tot : nullptr);
+                   st.active[0].as<uint32_t>(), st.counters.as<uint32_t>(), ordered ? keys : nullptr, spod, posof);
         if (ordered) {
-            K8S_LAUNCH(ctx, order0_kernel, ceil_div(st.m, kScanTile), 256, 0, s, st.m, flags0, st.active[0].as<uint32_t>(),
-                       chunk_tot, st.order[0].as<uint32_t>(), st.inv[0].as<uint32_t>());
+            int rc = sort_pairs(ctx, s, keys, spod, st.m, 10, st.sort);  // by (class, rot bucket), pod order inside
+            if (rc) return rc;
+            K8S_LAUNCH(ctx, slot_init_kernel, ceil_div(st.m, 256), 256, 0, s, spod, st.m, slotof);
             st.order_valid = true;
         }
     }
@@ -1546,14 +1504,18 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
             K8S_CUDA(ctx, cudaMemsetAsync(bk + lo, 0, (size_t)cnt * 8, s));
     }
     st.best_cleared_len = 0;
-    const uint32_t *order = st.order_valid ? st.order[st.cur].as<uint32_t>() : nullptr;  // class-sorted scoring order
+    SlotView view;  // scoring order of this round, if the run keeps one
+    view.active = st.active[st.cur].as<uint32_t>();
+    view.spod = st.order_valid ? st.order[st.cur].as<uint32_t>() : nullptr;
+    view.posof = st.inv[0].as<uint32_t>();
     const bool timed = st.timed < kMaxTimedRounds;  // (the two event records cost ~4 us per round)
     if (timed) K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed], s));
     dim3 grid(xb, splits);
     const int res = st.score_res;  // fixed at round_begin: the pod records are laid out for it
 #define K8S_SCORE(P, R, B)                                                                                         \
     K8S_LAUNCH(ctx, (score_kernel<P, R, B>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
-               st.active[st.cur].as<uint32_t>(), sm, bk, st.n, use_atomic, 0xFFFFFFFFu, ctx->tune.force_cls, order)
+               st.active[st.cur].as<uint32_t>(), sm, bk, st.n, use_atomic, 0xFFFFFFFFu, ctx->tune.force_cls, view.spod,  \
+               view.posof)
     // third argument: resident CTAs per SM the register budget is set for (measured best per variant)
     if (ppt == 4) K8S_SCORE(4, 4, 3);
     else if (ppt == 2 && res >= 4) K8S_SCORE(2, 4, 4);
@@ -1573,8 +1535,8 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
         st.timed_evals += (uint64_t)live * st.n;
     }
     if (finalize)
-        K8S_LAUNCH(ctx, score_finalize_kernel, ceil_div(cnt, 256), 256, 0, s, bk, st.podq.as<PodQ>(),
-                   st.active[st.cur].as<uint32_t>(), order, sm, cnt, st.n, d_best);
+        K8S_LAUNCH(ctx, score_finalize_kernel, ceil_div(cnt, 256), 256, 0, s, bk, st.podq.as<PodQ>(), view, sm, cnt, st.n,
+                   d_best);
     return K8SGPU_OK;
 }
 
@@ -1648,13 +1610,14 @@ int round_admit_coop_launch(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *prop
     a.best_key = st.best_key.as<unsigned long long>();
     a.best_key_clear = st.best_key.as<unsigned long long>();
     a.proposals = proposals;
-    a.inv_cur = st.order_valid ? st.inv[st.cur].as<uint32_t>() : nullptr;
+    a.spod = st.order_valid ? st.order[st.cur].as<uint32_t>() : nullptr;
+    a.spod_next = st.order[st.cur ^ 1].as<uint32_t>();
+    a.posof = st.inv[0].as<uint32_t>();
+    a.slotof = st.inv[1].as<uint32_t>();
+    a.gflags = st.best.as<uint32_t>();  // (m words the one-launch admission does not use otherwise)
     a.xw = xw;
     a.xcnt = xw > 1 ? group_slot_count(st.n_active, xw) : 0;
     a.slots = ctx->tune.slot_admit != 0 ? st.slots.as<uint32_t>() : nullptr;
-    a.pod_cls = st.pod_cls.as<uint8_t>();
-    a.order_next = st.order_valid ? st.order[st.cur ^ 1].as<uint32_t>() : nullptr;
-    a.inv_next = st.order_valid ? st.inv[st.cur ^ 1].as<uint32_t>() : nullptr;
     a.podq = st.podq.as<PodQ>();
     a.active = st.active[st.cur].as<uint32_t>();
     a.next_active = st.active[st.cur ^ 1].as<uint32_t>();
@@ -1757,9 +1720,12 @@ int round_finalize_peers(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *con
     pp.world = world;
     // where this launch's first slot sits in every exchange buffer
     const uint32_t base = xw > 1 ? xrank * sm.xcnt : lo;
+    SlotView view;
+    view.active = st.active[st.cur].as<uint32_t>();
+    view.spod = st.order_valid ? st.order[st.cur].as<uint32_t>() : nullptr;
+    view.posof = st.inv[0].as<uint32_t>();
     K8S_LAUNCH(ctx, score_finalize_p2p_kernel, ceil_div(sm.xcnt, 256), 256, 0, s, st.best_key.as<unsigned long long>(),
-               st.podq.as<PodQ>(), st.active[st.cur].as<uint32_t>(),
-               st.order_valid ? st.order[st.cur].as<uint32_t>() : nullptr, sm, sm.xcnt, st.n, base, pp);
+               st.podq.as<PodQ>(), view, sm, sm.xcnt, st.n, base, pp);
     return K8SGPU_OK;
 }
 

@@ -200,7 +200,9 @@ def test_place_single_launch_admission(ctx, name, grid):
     for k in ("assign", "free_gpu", "free_mcpu", "free_mib"):
         assert np.array_equal(got[k], g[k]), k
     assert (got["rounds"], got["placed"], got["evals"]) == (int(g["rounds"]), int(g["placed"]), int(g["evals"]))
-    assert got["kernel_launches"] <= 2 * got["rounds"] + 8
+    # two launches per round, plus the once-per-run table preparation (pod and node records, the
+    # 10-bit sort of the scoring order: 2 passes x histogram / scan / scatter, slot table, count)
+    assert got["kernel_launches"] <= 2 * got["rounds"] + 16
 
 
 @pytest.mark.parametrize("order", [0, 1])
