@@ -142,7 +142,7 @@ struct Tuning {
     int shard_admit = -1;   // multi-GPU: 1 = admission sharded by node range, 0 = replicated
     int slot_admit = -1;    // 0: always the sort-based admission
     int order = -1;         // 0: do not sort the scoring order by pod class
-    int force_cls = -1;     // timing experiments only: eval_pair class for every warp (results are wrong)
+    int force_cls = -1;     // 0..11: eval_pair4 class (CLS | TT << 2) for every warp -- timing experiments only, results are wrong; 16: toleration clause always evaluated (results stay right)
     int exchange = -1;      // multi-GPU: 0 = NCCL all-gather, 1 = peer stores, -1 = per round by list length
 };
 

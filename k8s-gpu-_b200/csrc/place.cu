@@ -19,13 +19,20 @@
 namespace k8sgpu {
 
 struct __align__(16) NodeQ {  // what the inner loop reads; rebuilt from the free columns each round
-    uint32_t free_gpu_s;  // free_gpu, or 0xFFFFFFFF (= -1 signed) when the node is not schedulable
-    uint32_t free_mcpu, free_mib;
+    // first half: read only by warps with a pod that restricts SKUs or zones, or whose toleration
+    // clause has to be evaluated (eval_pair4 CLS bit 0, TT = 2)
     uint32_t sku_bit;     // 1 << sku_id
     uint32_t zone_bit;    // 1 << (31 - zone_id): bit-reversed one-hot (see eval_pair RES = 3)
     uint32_t taint;
+    uint32_t free_gpu_s;  // free_gpu, or 0xFFFFFFFF (= -1 signed) when not schedulable (RES < 4 only)
+    // second half: everything the other warps need -- one 128-bit shared-memory load per node
+    uint32_t free_mcpu_s; // free_mcpu, or 0xFFFFFFFF (= -1 signed) when the node is not schedulable
+    uint32_t free_mib;
     uint32_t khi;         // 1<<31 | (0x7FFF - free_gpu) << 16 | (255 - cap_gpu) << 8 | (63 - n % 64) << 1
-    uint32_t zrot;        // (zone_id - 7) mod 32: rotates the pod's one-hot preferred zone onto bit 7
+                          // (RES = 4 also takes the free-GPU test from here: see eval_pair4)
+    uint32_t zrot;        // bits 0..4: (zone_id - 7) mod 32, rotates the pod's one-hot preferred zone onto bit 7
+                          // bits 5..31: free_gpu, or -1 when the node is not schedulable OR carries a taint
+                          // (eval_pair4 TT = 1; the funnel shift reads only the low five bits)
 };
 static_assert(sizeof(NodeQ) == 32, "node record is 32 B: the algorithmic bytes per eval");
 
@@ -42,6 +49,7 @@ constexpr uint32_t kSlotsPerNode = 8;  // slot admission (admit_coop_kernel): fi
 // counters[5] != 0 rules the slot admission out for this run: 1 = some pod asks for 0 GPUs,
 // 2 = some node has more than kSlotsPerNode free GPUs
 constexpr int kSlotVeto = 5;
+constexpr int kTaintUnion = 6;  // counters[6]: OR of every node's taint mask (per run, before pod_prep)
 
 __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -51,8 +59,21 @@ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
 
 // ------------------------------------------------------------------ table preparation
 
+__global__ void taint_union_kernel(const uint32_t *__restrict__ taint, uint32_t n, uint32_t *__restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t v = __reduce_or_sync(0xFFFFFFFFu, i < n ? taint[i] : 0u);
+    if ((threadIdx.x & 31u) == 0u && v) atomicOr(out, v);
+}
+// How a pod's toleration test can be scored (eval_pair4 TT), given the union of the node taints:
+// 0 = it tolerates every taint that occurs (the clause is always true), 1 = it tolerates none of
+// them (the clause is "the node has no taint"), 2 = anything else (the clause is evaluated).
+__device__ __forceinline__ uint32_t taint_class(uint32_t ntol, uint32_t tunion) {
+    const uint32_t x = ntol & tunion;
+    return x == 0u ? 0u : (x == tunion ? 1u : 2u);
+}
+
 // Also, when the run keeps a scoring order (see "scoring order" below): the pod's sort key
-// (eval_pair class << 8 | which 256th of the node table rot(p) falls into), its own index as the
+// (eval_pair4 class, CLS | TT << 2, << 8 | which 256th of the node table rot(p) falls into), its own index as the
 // sort payload, and posof[p] = p (every pod starts active at its own position).
 __global__ void __launch_bounds__(256) pod_prep_kernel(const uint32_t *__restrict__ cols, uint32_t m, uint32_t n_nodes,
                                                        uint32_t policy, int mul_masks, PodQ *__restrict__ podq,
@@ -84,7 +105,7 @@ __global__ void __launch_bounds__(256) pod_prep_kernel(const uint32_t *__restric
     assign[p] = K8SGPU_ASSIGN_PENDING;
     active[p] = p;
     if (sort_key) {
-        const uint32_t cls = ((q.nsku | q.nzone) ? 1u : 0u) | (q.pzb ? 2u : 0u);
+        const uint32_t cls = ((q.nsku | q.nzone) ? 1u : 0u) | (q.pzb ? 2u : 0u) | (taint_class(q.ntol, err[kTaintUnion]) << 2);
         const uint32_t bucket = n_nodes ? (uint32_t)(((unsigned long long)q.rot << 8) / n_nodes) : 0u;  // 0 .. 255
         sort_key[p] = (cls << 8) | bucket;
         sort_val[p] = p;
@@ -103,20 +124,20 @@ __device__ __forceinline__ NodeQ make_nodeq(const uint32_t *__restrict__ cols, c
             atomicOr(err, kErrNode);
         if (validate && fg > kSlotsPerNode) atomicOr(err + kSlotVeto, 2u);
         q.free_gpu_s = (flags & 1u) ? fg : 0xFFFFFFFFu;
-        q.free_mcpu = fc;
+        q.free_mcpu_s = (flags & 1u) ? fc : 0xFFFFFFFFu;
         q.free_mib = fm;
         q.sku_bit = 1u << (sku & 31u);
         q.zone_bit = 0x80000000u >> (zone & 31u);
         q.taint = taint;
         q.khi = 0x80000000u | ((0x7FFFu - (fg & 0x7FFFu)) << 16) | ((255u - (cap & 255u)) << 8) |
                 ((63u - (i & 63u)) << 1);
-        q.zrot = (zone - 7u) & 31u;
+        q.zrot = ((zone - 7u) & 31u) | ((((flags & 1u) && taint == 0u) ? fg : 0xFFFFFFFFu) << 5);
     } else {  // padding up to a whole tile: never feasible
-        q.free_gpu_s = 0xFFFFFFFFu;
-        q.free_mcpu = q.free_mib = 0;
+        q.free_gpu_s = q.free_mcpu_s = 0xFFFFFFFFu;
+        q.free_mib = 0;
         q.sku_bit = q.zone_bit = q.taint = 0;
         q.khi = 0;
-        q.zrot = 0;
+        q.zrot = 0xFFFFFFE0u;
     }
     return q;
 }
@@ -179,7 +200,9 @@ template <int PPT> __device__ __forceinline__ uint4 ldrec(const uint4 *p) { retu
 // feasibility clauses stay one predicate chain with no separate predicate-combine instruction:
 // the loop is bound by the integer ALU pipe (ncu: >90 % busy), so every ALU instruction removed
 // here is throughput.
-//   a = {free_gpu or -1, free_mcpu, free_mib, sku_bit}   b = {zone_bit, taint, khi, zrot}
+//   a = {sku_bit, zone_bit, taint, free_gpu or -1}   b = {free_mcpu or -1, free_mib, khi, zrot}
+//   (the two halves of a NodeQ; the RES < 4 bodies below were written for an older word order
+//   and get the words renamed on the way in)
 //   key = khi | (rotr(pzb, zrot) & 0x80): bit 7 of the rotated one-hot preferred-zone word is
 //   set exactly when the node's zone is the preferred one (zrot = (zone_id - 7) mod 32).
 //   khi carries 63 - (n mod 64) in bits 1..6, so inside a 64-node group the lowest n wins ties
@@ -202,66 +225,78 @@ template <int PPT> __device__ __forceinline__ uint4 ldrec(const uint4 *p) { retu
 //   bit 1: some pod prefers a zone         (else the funnel shift and the key LOP3 go:      -2)
 // A pod without the feature has an all-zero mask / one-hot word, for which the dropped instructions
 // compute the identity, so every CLS gives the same bits as CLS = 3 for the pods it is used on.
+// The RES = 4 body, assembled from its clauses.  Operands (the same list for every variant; a
+// variant that leaves a clause out is handed a register it uses anyway in that operand's place):
+//   %0 best | %1 sku_bit %2 zone_bit %3 taint | %4 free_mcpu %5 free_mib %6 khi %7 zrot
+//   %8 rq (the GPU request, see below) %9 rc %10 rm | %11 nsku %12 nzone %13 ntol %14 pzb
+//   %15 runtime -1, %16 runtime 1
+// The free-GPU test needs no word of its own.  TT != 1: khi holds 0x7FFF - free_gpu in bits 16..30
+// under a set bit 31, so khi + (0x80000000 + (req << 16)) has bit 31 set exactly when
+// 0x7FFF - free + req carries out of the field, i.e. when free < req (rq = minus that constant,
+// req clamped to 0x8000 -- no node has more than 0x7FFF free).  TT = 1: zrot's bits 5..31 hold
+// free_gpu, or -1 on a tainted node; rq = req << 5.  An unschedulable node has free_mcpu = -1.
+#define K8S_EP4(FREEW, MASKMUL, TAND, TSETP, MASKOR, SIGN, PREF, KEY)                                              \
+    asm("{\n\t"                                                                                                    \
+        ".reg .pred pf;\n\t"                                                                                       \
+        ".reg .b32 m, z, key, d1, d2, d3, d4, d5;\n\t"                                                             \
+        "mad.lo.s32 d1, %8, %15, " FREEW ";\n\t"                                                                   \
+        "mad.lo.s32 d2, %9, %15, %4;\n\t"                                                                          \
+        "mad.lo.s32 d3, %10, %15, %5;\n\t" MASKMUL TAND "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t" TSETP MASKOR SIGN PREF \
+        "setp.gt.and.u32 pf, " KEY ", %0, pf;\n\t"                                                                 \
+        "@pf mad.lo.u32 %0, " KEY ", %16, 0;\n\t"                                                                  \
+        "}"                                                                                                        \
+        : "+r"(best)                                                                                               \
+        : "r"(o_sku), "r"(o_zone), "r"(o_taint), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w), "r"(rq), "r"(rc), "r"(rm), \
+          "r"(o_nsku), "r"(o_nzone), "r"(o_ntol), "r"(o_pzb), "r"(negone), "r"(one))
+#define K8S_EP4_MUL "mul.lo.u32 d4, %11, %1;\n\tmul.lo.u32 d5, %12, %2;\n\t"
+#define K8S_EP4_MOR "lop3.b32 d1, d1, d4, d5, 0xFE;\n\t"
+#define K8S_EP4_TAND "and.b32 m, %3, %13;\n\t"
+#define K8S_EP4_TSETP "setp.eq.u32 pf, m, 0;\n\t"
+#define K8S_EP4_SIGN_AND "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
+#define K8S_EP4_SIGN "setp.ge.s32 pf, d1, 0;\n\t"
+#define K8S_EP4_PREF "shf.r.wrap.b32 z, %14, %14, %7;\n\tlop3.b32 key, z, 0x80, %6, 0xEA;\n\t"
+// CLS: which clauses some pod of the warp needs (bit 0: SKU / zone masks, bit 1: zone preference).
+// TT: the taint clause -- 2: tested (and + setp); 0: left out (every pod of the warp tolerates every
+// taint any node carries); 1: left out, free GPUs read from the field that is -1 on a tainted node
+// (every pod of the warp tolerates none of the taints that occur).
+// Instructions per eval: 12 - 3 [no masks] - 2 [no preference] - 2 [TT < 2], and with CLS bit 0
+// clear and TT < 2 the first half of the node record is not even loaded.
+template <int CLS, int TT> __host__ __device__ constexpr bool ep4_needs_first_half() { return (CLS & 1) || TT == 2; }
+__device__ __forceinline__ uint32_t ep4_request(uint32_t req_gpu, bool tainted_field) {
+    const uint32_t r = min(req_gpu, 0x8000u);
+    return tainted_field ? r << 5 : 0u - (0x80000000u + (r << 16));
+}
+template <int CLS, int TT>
+__device__ __forceinline__ void eval_pair4(const uint4 &a, const uint4 &b, uint32_t rq, uint32_t rc, uint32_t rm,
+                                           uint32_t nsku, uint32_t nzone, uint32_t ntol, uint32_t pzb,
+                                           uint32_t &best, uint32_t negone, uint32_t one) {
+    const uint32_t o_sku = (CLS & 1) ? a.x : b.x, o_zone = (CLS & 1) ? a.y : b.x, o_taint = TT == 2 ? a.z : b.x;
+    const uint32_t o_nsku = (CLS & 1) ? nsku : rc, o_nzone = (CLS & 1) ? nzone : rc, o_ntol = TT == 2 ? ntol : rc;
+    const uint32_t o_pzb = (CLS & 2) ? pzb : rc;
+#define K8S_EP4_T(MASKMUL, MASKOR, PREF, KEY)                                                                  \
+    if (TT == 2) K8S_EP4("%6", MASKMUL, K8S_EP4_TAND, K8S_EP4_TSETP, MASKOR, K8S_EP4_SIGN_AND, PREF, KEY);     \
+    else if (TT == 1) K8S_EP4("%7", MASKMUL, "", "", MASKOR, K8S_EP4_SIGN, PREF, KEY);                         \
+    else K8S_EP4("%6", MASKMUL, "", "", MASKOR, K8S_EP4_SIGN, PREF, KEY)
+    if (CLS == 0) {
+        K8S_EP4_T("", "", "", "%6");
+    } else if (CLS == 1) {
+        K8S_EP4_T(K8S_EP4_MUL, K8S_EP4_MOR, "", "%6");
+    } else if (CLS == 2) {
+        K8S_EP4_T("", "", K8S_EP4_PREF, "key");
+    } else {
+        K8S_EP4_T(K8S_EP4_MUL, K8S_EP4_MOR, K8S_EP4_PREF, "key");
+    }
+#undef K8S_EP4_T
+}
+
+// (RES = 4: rg is ep4_request(req_gpu, false), as the kernel keeps it)
 template <int RES, int CLS = 3>
-__device__ __forceinline__ void eval_pair(const uint4 &a, const uint4 &b, uint32_t rg, uint32_t rc, uint32_t rm,
+__device__ __forceinline__ void eval_pair(const uint4 &na, const uint4 &nb, uint32_t rg, uint32_t rc, uint32_t rm,
                                           uint32_t nsku, uint32_t nzone, uint32_t ntol, uint32_t pzb,
                                           uint32_t &best, uint32_t negone) {
-    if (RES == 4 && CLS == 0) {  // 9 instructions: 5 ALU + 4 FMA-pipe
-        asm("{\n\t"
-            ".reg .pred pf;\n\t"
-            ".reg .b32 m, d1, d2, d3;\n\t"
-            "mad.lo.s32 d1, %5, %8, %1;\n\t"
-            "mad.lo.s32 d2, %6, %8, %2;\n\t"
-            "mad.lo.s32 d3, %7, %8, %3;\n\t"
-            "and.b32 m, %4, %10;\n\t"
-            "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t"
-            "setp.eq.u32 pf, m, 0;\n\t"
-            "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
-            "setp.gt.and.u32 pf, %11, %0, pf;\n\t"
-            "@pf mad.lo.u32 %0, %11, %9, 0;\n\t"
-            "}"
-            : "+r"(best)
-            : "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.y), "r"(rg), "r"(rc), "r"(rm), "r"(negone), "r"(0u - negone),
-              "r"(ntol), "r"(b.z));
-    } else if (RES == 4 && CLS == 2) {  // 11: no mask multiplies
-        asm("{\n\t"
-            ".reg .pred pf;\n\t"
-            ".reg .b32 m, z, key, d1, d2, d3;\n\t"
-            "mad.lo.s32 d1, %5, %8, %1;\n\t"
-            "mad.lo.s32 d2, %6, %8, %2;\n\t"
-            "mad.lo.s32 d3, %7, %8, %3;\n\t"
-            "and.b32 m, %4, %10;\n\t"
-            "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t"
-            "setp.eq.u32 pf, m, 0;\n\t"
-            "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
-            "shf.r.wrap.b32 z, %12, %12, %13;\n\t"
-            "lop3.b32 key, z, 0x80, %11, 0xEA;\n\t"
-            "setp.gt.and.u32 pf, key, %0, pf;\n\t"
-            "@pf mad.lo.u32 %0, key, %9, 0;\n\t"
-            "}"
-            : "+r"(best)
-            : "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.y), "r"(rg), "r"(rc), "r"(rm), "r"(negone), "r"(0u - negone),
-              "r"(ntol), "r"(b.z), "r"(pzb), "r"(b.w));
-    } else if (RES == 4 && CLS == 1) {  // 12: no zone-preference bit
-        asm("{\n\t"
-            ".reg .pred pf;\n\t"
-            ".reg .b32 m, d1, d2, d3, d4, d5;\n\t"
-            "mad.lo.s32 d1, %5, %8, %1;\n\t"
-            "mad.lo.s32 d2, %6, %8, %2;\n\t"
-            "mad.lo.s32 d3, %7, %8, %3;\n\t"
-            "mul.lo.u32 d4, %12, %13;\n\t"
-            "mul.lo.u32 d5, %14, %15;\n\t"
-            "and.b32 m, %4, %10;\n\t"
-            "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t"
-            "setp.eq.u32 pf, m, 0;\n\t"
-            "lop3.b32 d1, d1, d4, d5, 0xFE;\n\t"
-            "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
-            "setp.gt.and.u32 pf, %11, %0, pf;\n\t"
-            "@pf mad.lo.u32 %0, %11, %9, 0;\n\t"
-            "}"
-            : "+r"(best)
-            : "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.y), "r"(rg), "r"(rc), "r"(rm), "r"(negone), "r"(0u - negone),
-              "r"(ntol), "r"(b.z), "r"(nsku), "r"(a.w), "r"(nzone), "r"(b.x));
+    const uint4 a = make_uint4(na.w, nb.x, nb.y, na.x), b = make_uint4(na.y, na.z, nb.z, nb.w);
+    if (RES == 4) {
+        eval_pair4<CLS, 2>(na, nb, rg, rc, rm, nsku, nzone, ntol, pzb, best, negone, 0u - negone);
     } else if (RES == 0) {
         asm("{\n\t"
             ".reg .pred pf;\n\t"
@@ -314,28 +349,6 @@ __device__ __forceinline__ void eval_pair(const uint4 &a, const uint4 &b, uint32
             "mad.lo.s32 d3, %14, %16, %4;\n\t"
             "setp.eq.u32 pf, m, 0;\n\t"
             "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t"
-            "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
-            "shf.r.wrap.b32 z, %11, %11, %7;\n\t"
-            "lop3.b32 key, z, 0x80, %15, 0xEA;\n\t"
-            "setp.gt.and.u32 pf, key, %0, pf;\n\t"
-            "@pf mad.lo.u32 %0, key, %17, 0;\n\t"
-            "}"
-            : "+r"(best)
-            : "r"(a.w), "r"(a.x), "r"(a.y), "r"(a.z), "r"(b.x), "r"(b.y), "r"(b.w), "r"(nsku), "r"(nzone),
-              "r"(ntol), "r"(pzb), "r"(rg), "r"(rc), "r"(rm), "r"(b.z), "r"(negone), "r"(0u - negone));
-    } else if (RES == 4) {
-        asm("{\n\t"
-            ".reg .pred pf;\n\t"
-            ".reg .b32 m, z, key, d1, d2, d3, d4, d5;\n\t"
-            "mad.lo.s32 d1, %12, %16, %2;\n\t"
-            "mad.lo.s32 d2, %13, %16, %3;\n\t"
-            "mad.lo.s32 d3, %14, %16, %4;\n\t"
-            "mul.lo.u32 d4, %8, %1;\n\t"
-            "mul.lo.u32 d5, %9, %5;\n\t"
-            "and.b32 m, %6, %10;\n\t"
-            "lop3.b32 d1, d1, d2, d3, 0xFE;\n\t"
-            "setp.eq.u32 pf, m, 0;\n\t"
-            "lop3.b32 d1, d1, d4, d5, 0xFE;\n\t"
             "setp.ge.and.s32 pf, d1, 0, pf;\n\t"
             "shf.r.wrap.b32 z, %11, %11, %7;\n\t"
             "lop3.b32 key, z, 0x80, %15, 0xEA;\n\t"
@@ -416,7 +429,8 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
                                                     unsigned long long *__restrict__ best_key, uint32_t n_nodes,
                                                     int use_atomic, uint32_t negone, int cls_force,
                                                     const uint32_t *__restrict__ spod,
-                                                    const uint32_t *__restrict__ posof) {
+                                                    const uint32_t *__restrict__ posof,
+                                                    const uint32_t *__restrict__ tunion_ptr) {
     // kStages-deep ring of node tiles.  full[b]: the TMA copy into buffer b has landed (one
     // arrival + its byte count); empty[b]: all 8 warps are done reading buffer b (one arrival per
     // warp).  No __syncthreads in the tile loop: a warp may run a tile ahead of its slowest sibling.
@@ -472,14 +486,37 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
             rg[j] = 0x7FFFFFFFu; rc[j] = rm[j] = 0; nsku[j] = nzone[j] = 0; ntol[j] = 0xFFFFFFFFu; pzb[j] = 0; rot[j] = 0;
         }
     }
-    // Class of this warp's pods (see eval_pair): which clauses can be left out of the inner loop.
-    uint32_t wcls = 3;
+    // Class of this warp's pods (see eval_pair4): which clauses can be left out of the inner loop.
+    // wv = CLS | TT << 2.  Idle lanes fit every variant (their request exceeds any free count).
+    uint32_t wv = 3u | (2u << 2);
+    uint32_t rg5[PPT];  // RES = 4: the GPU request in the two forms eval_pair4 takes (rg[] itself holds the other)
+    // The multiplier of the predicated "best = key" mad, one copy per pod the compiler cannot tell
+    // apart: with a shared one, two pods whose key is the node's own word (no preference clause)
+    // share ONE multiply and each gets an ALU select instead -- half an instruction more per eval.
+    uint32_t one[PPT];
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        rg5[j] = ep4_request(rg[j], true);
+        if (RES == 4) rg[j] = ep4_request(rg[j], false);
+        // (all of these are 1 for negone = 0xFFFFFFFF, which is what the host passes)
+        one[j] = j == 0 ? 0u - negone : j == 1 ? negone * negone : j == 2 ? negone >> 31 : negone & 1u;
+    }
     if (RES == 4) {
+        const uint32_t tunion = __ldg(tunion_ptr);
         uint32_t mine = 0;
 #pragma unroll
-        for (int j = 0; j < PPT; ++j) mine |= ((nsku[j] | nzone[j]) ? 1u : 0u) | (pzb[j] ? 2u : 0u);
-        wcls = __reduce_or_sync(0xFFFFFFFFu, mine);
-        if (cls_force >= 0 && cls_force < 4) wcls = (uint32_t)cls_force;  // timing experiments only
+        for (int j = 0; j < PPT; ++j) {
+            mine |= ((nsku[j] | nzone[j]) ? 1u : 0u) | (pzb[j] ? 2u : 0u);
+            if (pos[j] != 0xFFFFFFFFu) mine |= 4u << taint_class(ntol[j], tunion);
+        }
+        const uint32_t w = __reduce_or_sync(0xFFFFFFFFu, mine);
+        const uint32_t tset = w >> 2;  // bit t: some pod of the warp has taint class t
+        const uint32_t wtt = ((tset & 4u) || (tset & 3u) == 3u) ? 2u : ((tset & 2u) ? 1u : 0u);
+        wv = (w & 3u) | (wtt << 2);
+        // timing experiments only (results are wrong): 0..11 forces CLS | TT << 2; 16 only rules the
+        // taint specialisation out (results stay right)
+        if (cls_force >= 0 && cls_force < 12) wv = (uint32_t)cls_force;
+        if (cls_force == 16) wv |= 2u << 2, wv &= ~(1u << 2);
     }
 
     for (uint32_t t = t0; t < t1; ++t) {
@@ -502,7 +539,17 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
 #pragma unroll
             for (int j = 0; j < PPT; ++j) gx |= (rrel[j] - g) < kGroup;
             if (!__any_sync(0xFFFFFFFFu, gx)) {  // common case: 64 evals per pod, no checks at all
-#define K8S_GROUP(CLS)                                                                                           \
+#define K8S_GROUP(CLS, TT)                                                                                       \
+    _Pragma("unroll 1") for (uint32_t kb = g; kb < g + kGroup; kb += 16) {                                       \
+        _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
+            const uint4 b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                                                   \
+            const uint4 a = ep4_needs_first_half<CLS, TT>() ? ldrec<PPT>(&tl[2 * (kb + i)]) : b;                 \
+            _Pragma("unroll") for (int j = 0; j < PPT; ++j)                                                      \
+                eval_pair4<CLS, TT>(a, b, TT == 1 ? rg5[j] : rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j],    \
+                                    pzb[j], best[j], negone, one[j]);                                            \
+        }                                                                                                        \
+    }
+#define K8S_GROUP_RES(CLS)                                                                                       \
     _Pragma("unroll 1") for (uint32_t kb = g; kb < g + kGroup; kb += 16) {                                       \
         _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
             const uint4 a = ldrec<PPT>(&tl[2 * (kb + i)]), b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                \
@@ -510,15 +557,25 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
                 eval_pair<RES, CLS>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j], negone); \
         }                                                                                                        \
     }
-                if (RES != 4 || wcls == 3) {
-                    K8S_GROUP(3)
-                } else if (wcls == 0) {
-                    K8S_GROUP(0)
-                } else if (wcls == 2) {
-                    K8S_GROUP(2)
+                if (RES != 4) {
+                    K8S_GROUP_RES(3)
                 } else {
-                    K8S_GROUP(1)
+                    switch (wv) {
+                    case 0: K8S_GROUP(0, 0) break;
+                    case 1: K8S_GROUP(1, 0) break;
+                    case 2: K8S_GROUP(2, 0) break;
+                    case 3: K8S_GROUP(3, 0) break;
+                    case 4: K8S_GROUP(0, 1) break;
+                    case 5: K8S_GROUP(1, 1) break;
+                    case 6: K8S_GROUP(2, 1) break;
+                    case 7: K8S_GROUP(3, 1) break;
+                    case 8: K8S_GROUP(0, 2) break;
+                    case 9: K8S_GROUP(1, 2) break;
+                    case 10: K8S_GROUP(2, 2) break;
+                    default: K8S_GROUP(3, 2) break;
+                    }
                 }
+#undef K8S_GROUP_RES
 #undef K8S_GROUP
             } else {
 #pragma unroll 1
@@ -537,6 +594,8 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
     }
                         // (not with four pods per thread: on wide node tables few groups come this
                         // way, and the extra code cost config 4 10 % -- registers spilled)
+                        // (and the taint clause stays in: these chunks are a few per cent of the evals)
+                        const uint32_t wcls = wv & 3u;
                         if (RES != 4 || PPT >= 4 || wcls == 3) {
                             K8S_CHUNK(3)
                         } else if (wcls == 0) {
@@ -1420,6 +1479,9 @@ int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
     // and the one-launch admission, which compacts it every round next to the active list.
     const bool ordered = st.want_order && st.score_res == 4 && coop_admission(ctx) && ctx->tune.order != 0 && st.m > 0;
     st.order_valid = false;
+    if (st.n)  // which taints occur at all: decides how each pod's toleration clause is scored
+        K8S_LAUNCH(ctx, taint_union_kernel, ceil_div(st.n, 256), 256, 0, s, st.node_cols.as<uint32_t>() + 6 * (size_t)st.n,
+                   st.n, st.counters.as<uint32_t>() + kTaintUnion);
     if (st.m) {
         uint32_t *spod = st.order[0].as<uint32_t>(), *posof = st.inv[0].as<uint32_t>(), *slotof = st.inv[1].as<uint32_t>();
         uint32_t *keys = st.sort_keys.as<uint32_t>();
@@ -1427,7 +1489,7 @@ int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
                    st.policy_flags, st.score_res == 4 ? 1 : 0, st.podq.as<PodQ>(), st.assign.as<int32_t>(),
                    st.active[0].as<uint32_t>(), st.counters.as<uint32_t>(), ordered ? keys : nullptr, spod, posof);
         if (ordered) {
-            int rc = sort_pairs(ctx, s, keys, spod, st.m, 10, st.sort);  // by (class, rot bucket), pod order inside
+            int rc = sort_pairs(ctx, s, keys, spod, st.m, 12, st.sort);  // by (class, rot bucket), pod order inside
             if (rc) return rc;
             K8S_LAUNCH(ctx, slot_init_kernel, ceil_div(st.m, 256), 256, 0, s, spod, st.m, slotof);
             st.order_valid = true;
@@ -1515,7 +1577,7 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
 #define K8S_SCORE(P, R, B)                                                                                         \
     K8S_LAUNCH(ctx, (score_kernel<P, R, B>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
                st.active[st.cur].as<uint32_t>(), sm, bk, st.n, use_atomic, 0xFFFFFFFFu, ctx->tune.force_cls, view.spod,  \
-               view.posof)
+               view.posof, st.counters.as<uint32_t>() + kTaintUnion)
     // third argument: resident CTAs per SM the register budget is set for (measured best per variant)
     if (ppt == 4) K8S_SCORE(4, 4, 3);
     else if (ppt == 2 && res >= 4) K8S_SCORE(2, 4, 4);

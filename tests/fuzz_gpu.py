@@ -40,7 +40,7 @@ def random_nodes(rng, n):
                 free_mib=(free * rng.choice([28672, 243200])).astype(np.uint32), cap_gpu=cap,
                 sku_id=rng.integers(0, rng.choice([1, 2, 32]), n).astype(np.uint32),
                 zone_id=rng.integers(0, rng.choice([1, 3, 32]), n).astype(np.uint32),
-                taint_mask=np.where(rng.random(n) < 0.1, rng.integers(1, 8, n), 0).astype(np.uint32),
+                taint_mask=np.where(rng.random(n) < rng.choice([0.0, 0.1, 0.5]), rng.integers(1, rng.choice([2, 8]), n), 0).astype(np.uint32),
                 flags=(rng.random(n) > 0.03).astype(np.uint32))
 
 
@@ -52,7 +52,8 @@ def random_pods(rng, m):
     return dict(req_gpu=g, req_mcpu=(g * 4000).astype(np.uint32), req_mib=(g * 28672).astype(np.uint32),
                 sku_mask=np.full(m, NONE, np.uint32) if alike else anymask(0.3),
                 zone_mask=np.full(m, NONE, np.uint32) if alike else anymask(0.2),
-                tol_mask=np.zeros(m, np.uint32) if alike else rng.integers(0, 8, m).astype(np.uint32),
+                tol_mask=np.zeros(m, np.uint32) if alike else
+                (rng.integers(0, 8, m) if rng.random() < 0.5 else rng.choice([0, 0xFFFFFFFF], m)).astype(np.uint32),
                 pref_zone=np.full(m, NONE, np.uint32) if alike else
                 np.where(rng.random(m) < 0.5, rng.integers(0, 32, m), NONE).astype(np.uint32),
                 priority=np.zeros(m, np.uint32))
@@ -69,6 +70,8 @@ def case_place(rng, ctx):
     env = dict(res=int(rng.choice([0, 1, 2, 3, 4, 4, 4, 4])), ppt=int(rng.choice([1, 2, 4])), coop=int(rng.choice([0, 1, 1])),
                order=int(rng.choice([0, 1, 1])),  # order: scoring order sorted by pod class (RES 4 + one-launch admission)
                slot_admit=int(rng.choice([0, 1, 1])))  # slot admission where its domain holds, else the sort
+    if rng.random() < 0.2:  # toleration clause always evaluated (no taint-class specialisation)
+        env["force_cls"] = 16
     if rng.random() < 0.5:
         env["splits"] = int(rng.integers(1, 9))
     if rng.random() < 0.5:  # few CTAs in the single-launch admission: every CTA loops over several tiles

@@ -201,7 +201,7 @@ def test_place_single_launch_admission(ctx, name, grid):
         assert np.array_equal(got[k], g[k]), k
     assert (got["rounds"], got["placed"], got["evals"]) == (int(g["rounds"]), int(g["placed"]), int(g["evals"]))
     # two launches per round, plus the once-per-run table preparation (pod and node records, the
-    # 10-bit sort of the scoring order: 2 passes x histogram / scan / scatter, slot table, count)
+    # taint union, 12-bit sort of the scoring order: 2 passes x histogram / scan / scatter, slot table, count)
     assert got["kernel_launches"] <= 2 * got["rounds"] + 16
 
 
@@ -213,6 +213,39 @@ def test_place_class_sorted_scoring_order(ctx, orc, synth, order, n, m, coop_gri
     result is the oracle's: short and long lists, few CTAs (many tiles per CTA in the partition)."""
     nodes, pods = synth.gen_nodes(n, config_id=5), synth.gen_pods(m, config_id=5)
     ctx.set_tuning(order=order, coop_grid=coop_grid)
+    same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
+
+
+@pytest.mark.parametrize("force", [None, 16])
+@pytest.mark.parametrize("case", ["all_or_nothing", "partial", "no_taints", "high_bits", "everything_tainted"])
+def test_toleration_classes(ctx, orc, synth, case, force):
+    """The scoring kernel leaves the toleration clause out for warps whose pods tolerate every
+    taint that occurs (or none of them: those read free GPUs from a field that is -1 on tainted
+    nodes) and takes the free-GPU test from the key word.  Every mix against the oracle, next to
+    the kernel with that specialisation ruled out (force_cls = 16): partial tolerations (clause
+    evaluated), no taint at all, taint bit 31, requests of 0 and beyond any node, unschedulable
+    nodes with free capacity."""
+    rng = np.random.default_rng(hash(case) % 1000)
+    n, m = 1100, 9000
+    nodes, pods = synth.gen_nodes(n, config_id=5), synth.gen_pods(m, config_id=5)
+    taints = {"all_or_nothing": [0, 0, 0, 1, 2, 3], "partial": [0, 0, 1, 2, 4, 7], "no_taints": [0],
+              "high_bits": [0, 0, 0x80000000, 0x80000001, 0x40000000], "everything_tainted": [1, 2, 3]}[case]
+    nodes["taint_mask"] = rng.choice(np.array(taints, np.uint32), n).astype(np.uint32)
+    union = int(np.bitwise_or.reduce(nodes["taint_mask"]))
+    tols = {"all_or_nothing": [0, 0, union, 0xFFFFFFFF], "partial": [0, 1, 2, 3, 5, 7, 0xFFFFFFFF],
+            "no_taints": [0, 1, 0xFFFFFFFF], "high_bits": [0, 0x80000000, 0xC0000001, 1],
+            "everything_tainted": [0, 1, 2, 3]}[case]
+    pods["tol_mask"] = rng.choice(np.array(tols, np.uint32), m).astype(np.uint32)
+    pods["req_gpu"] = pods["req_gpu"].copy()
+    pods["req_gpu"][::97] = 0
+    pods["req_gpu"][5::101] = 0x8000
+    pods["req_gpu"][7::103] = 0x7FFFFFFF
+    nodes["flags"] = (rng.random(n) > 0.1).astype(np.uint32)  # unschedulable nodes keep their free capacity
+    ctx.set_tuning(force_cls=force)
+    ctx.place_upload(nodes, pods)
+    free = (nodes["free_gpu"], nodes["free_mcpu"], nodes["free_mib"])
+    want = orc.score_round(nodes, free, pods, np.arange(m, dtype=np.uint32), flags=0, nthreads=NCPU)
+    assert np.array_equal(ctx.score_once(0), want)
     same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
 
 
