@@ -50,6 +50,8 @@ constexpr uint32_t kSlotsPerNode = 8;  // slot admission (admit_coop_kernel): fi
 // 2 = some node has more than kSlotsPerNode free GPUs
 constexpr int kSlotVeto = 5;
 constexpr int kTaintUnion = 6;  // counters[6]: OR of every node's taint mask (per run, before pod_prep)
+constexpr int kLikeRuns = 7;    // counters[7]: how many distinct (class, hash) values the pods' sort keys hold
+constexpr uint32_t kLikeBits = 12, kLikeMinRun = 1024;
 
 __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -73,13 +75,15 @@ __device__ __forceinline__ uint32_t taint_class(uint32_t ntol, uint32_t tunion) 
 }
 
 // Also, when the run keeps a scoring order (see "scoring order" below): the pod's sort key
-// (eval_pair4 class, CLS | TT << 2, << 8 | which 256th of the node table rot(p) falls into), its own index as the
+// (eval_pair4 class, CLS | TT << 2; optionally a hash of the pod's masks and preferred zone; where in
+// the node table rot(p) falls -- 24 bits), its own index as the
 // sort payload, and posof[p] = p (every pod starts active at its own position).
 __global__ void __launch_bounds__(256) pod_prep_kernel(const uint32_t *__restrict__ cols, uint32_t m, uint32_t n_nodes,
                                                        uint32_t policy, int mul_masks, PodQ *__restrict__ podq,
                                                        int32_t *__restrict__ assign, uint32_t *__restrict__ active,
                                                        uint32_t *__restrict__ err, uint32_t *__restrict__ sort_key,
-                                                       uint32_t *__restrict__ sort_val, uint32_t *__restrict__ posof) {
+                                                       uint32_t *__restrict__ sort_val, uint32_t *__restrict__ posof,
+                                                       uint32_t hash_bits, uint32_t *__restrict__ seen) {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= m) return;
     PodQ q;
@@ -105,12 +109,33 @@ __global__ void __launch_bounds__(256) pod_prep_kernel(const uint32_t *__restric
     assign[p] = K8SGPU_ASSIGN_PENDING;
     active[p] = p;
     if (sort_key) {
-        const uint32_t cls = ((q.nsku | q.nzone) ? 1u : 0u) | (q.pzb ? 2u : 0u) | (taint_class(q.ntol, err[kTaintUnion]) << 2);
-        const uint32_t bucket = n_nodes ? (uint32_t)(((unsigned long long)q.rot << 8) / n_nodes) : 0u;  // 0 .. 255
-        sort_key[p] = (cls << 8) | bucket;
+        const uint32_t tt = taint_class(q.ntol, err[kTaintUnion]);
+        const uint32_t cls = ((q.nsku | q.nzone) ? 1u : 0u) | (q.pzb ? 2u : 0u) | (tt << 2);
+        // pods that agree on the words eval_pair4_u2 shares sort together (12 hash bits inside the class)
+        uint32_t h = q.nsku * 0x9E3779B1u ^ q.nzone * 0x85EBCA77u ^ q.pzb * 0xC2B2AE3Du ^ (tt == 2u ? q.ntol : 0u) * 0x27D4EB2Fu;
+        h ^= h >> 15;
+        h *= 0x2C1B3C6Du;
+        h ^= h >> 12;
+        // 20 bits under the class: hash_bits of the hash, the rest says where in the node table rot(p) falls
+        const uint32_t rb = 20u - hash_bits;
+        const uint32_t where = n_nodes ? (uint32_t)(((unsigned long long)q.rot << rb) / n_nodes) : 0u;
+        const uint32_t hh = hash_bits ? h >> (32u - hash_bits) : 0u;
+        sort_key[p] = (cls << 20) | (hh << rb) | where;
+        if (seen) {  // count the distinct (class, hash) values: one atomic per value, then plain reads
+            uint32_t *sn = seen + ((cls << kLikeBits) | hh);
+            if (*(volatile uint32_t *)sn == 0u && atomicExch(sn, 1u) == 0u) atomicAdd(err + kLikeRuns, 1u);
+        }
         sort_val[p] = p;
         posof[p] = p;
     }
+}
+
+// The hash in the sort key pays while the runs of like pods stay long (see round_begin): with
+// fewer than kLikeMinRun pods per distinct value on average it is cleared again, which leaves
+// (class, the top 8 bits of where rot(p) falls).
+__global__ void like_hash_fix_kernel(uint32_t *__restrict__ sort_key, uint32_t m, const uint32_t *__restrict__ counters) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < m && (unsigned long long)counters[kLikeRuns] * kLikeMinRun > m) sort_key[p] &= ~(((1u << kLikeBits) - 1u) << (20u - kLikeBits));
 }
 
 __device__ __forceinline__ NodeQ make_nodeq(const uint32_t *__restrict__ cols, const uint32_t *__restrict__ freec,
@@ -289,6 +314,72 @@ __device__ __forceinline__ void eval_pair4(const uint4 &a, const uint4 &b, uint3
 #undef K8S_EP4_T
 }
 
+// Two pods of ONE thread against a node, when the two agree on their masks, preferred zone and
+// (TT = 2) tolerations -- the scoring order sorts like pods together, so almost every thread
+// qualifies.  What depends on the node and on those shared words alone is computed once: the
+// mask / toleration test becomes one predicate (plain AND tests on un-mirrored masks: up to three
+// terms, one LOP3 each), the key one funnel shift + LOP3; per pod remain the three resource
+// differences, their OR, the sign test, the compare and the predicated update (7 instructions).
+// One asm body for both pods, because the shared predicate cannot leave it.
+//   %0 %1 best | %2 sku_bit %3 zone_bit %4 taint | %5 free_mcpu %6 free_mib %7 khi %8 zrot
+//   %9 %10 rq | %11 %12 rc | %13 %14 rm | %15 sku mask %16 zone mask (complements, plain and
+//   bit-reversed like the node words) %17 ntol %18 pzb | %19 runtime -1 | %20 %21 runtime 1
+#define K8S_EP4U(FREEW, SHARED, SIGN0, SIGN1, PREF, KEY)                                                       \
+    asm("{\n\t"                                                                                                \
+        ".reg .pred pf0, pf1, pm;\n\t"                                                                         \
+        ".reg .b32 m, z, key, x1, x2, x3, y1, y2, y3;\n\t"                                                     \
+        "mad.lo.s32 x1, %9, %19, " FREEW ";\n\t"                                                               \
+        "mad.lo.s32 y1, %10, %19, " FREEW ";\n\t"                                                              \
+        "mad.lo.s32 x2, %11, %19, %5;\n\t"                                                                     \
+        "mad.lo.s32 y2, %12, %19, %5;\n\t"                                                                     \
+        "mad.lo.s32 x3, %13, %19, %6;\n\t"                                                                     \
+        "mad.lo.s32 y3, %14, %19, %6;\n\t" SHARED "lop3.b32 x1, x1, x2, x3, 0xFE;\n\t"                         \
+        "lop3.b32 y1, y1, y2, y3, 0xFE;\n\t" SIGN0 SIGN1 PREF "setp.gt.and.u32 pf0, " KEY ", %0, pf0;\n\t"      \
+        "setp.gt.and.u32 pf1, " KEY ", %1, pf1;\n\t"                                                           \
+        "@pf0 mad.lo.u32 %0, " KEY ", %20, 0;\n\t"                                                             \
+        "@pf1 mad.lo.u32 %1, " KEY ", %21, 0;\n\t"                                                             \
+        "}"                                                                                                    \
+        : "+r"(best0), "+r"(best1)                                                                             \
+        : "r"(o_sku), "r"(o_zone), "r"(o_taint), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w), "r"(rq0), "r"(rq1),  \
+          "r"(rc0), "r"(rc1), "r"(rm0), "r"(rm1), "r"(o_msku), "r"(o_mzone), "r"(o_ntol), "r"(o_pzb),         \
+          "r"(negone), "r"(one0), "r"(one1))
+#define K8S_EP4U_MASK "and.b32 m, %16, %3;\n\tlop3.b32 m, %15, %2, m, 0xEA;\n\t"
+#define K8S_EP4U_TOL_MORE "lop3.b32 m, %4, %17, m, 0xEA;\n\t"
+#define K8S_EP4U_TOL_ONLY "and.b32 m, %4, %17;\n\t"
+#define K8S_EP4U_PM "setp.eq.u32 pm, m, 0;\n\t"
+#define K8S_EP4U_PREF "shf.r.wrap.b32 z, %18, %18, %8;\n\tlop3.b32 key, z, 0x80, %7, 0xEA;\n\t"
+template <int CLS, int TT> __host__ __device__ constexpr bool ep4u_exists() { return CLS != 0 || TT == 2; }
+template <int CLS, int TT>
+__device__ __forceinline__ void eval_pair4_u2(const uint4 &a, const uint4 &b, uint32_t rq0, uint32_t rq1, uint32_t rc0,
+                                              uint32_t rc1, uint32_t rm0, uint32_t rm1, uint32_t msku, uint32_t mzone,
+                                              uint32_t ntol, uint32_t pzb, uint32_t &best0, uint32_t &best1,
+                                              uint32_t negone, uint32_t one0, uint32_t one1) {
+    const uint32_t o_sku = (CLS & 1) ? a.x : b.x, o_zone = (CLS & 1) ? a.y : b.x, o_taint = TT == 2 ? a.z : b.x;
+    const uint32_t o_msku = (CLS & 1) ? msku : rc0, o_mzone = (CLS & 1) ? mzone : rc0, o_ntol = TT == 2 ? ntol : rc0;
+    const uint32_t o_pzb = (CLS & 2) ? pzb : rc0;
+#define K8S_SG0 "setp.ge.s32 pf0, x1, 0;\n\t"
+#define K8S_SG1 "setp.ge.s32 pf1, y1, 0;\n\t"
+#define K8S_SG0P "setp.ge.and.s32 pf0, x1, 0, pm;\n\t"
+#define K8S_SG1P "setp.ge.and.s32 pf1, y1, 0, pm;\n\t"
+#define K8S_EP4U_T(PREF, KEY)                                                                                  \
+    if ((CLS & 1) && TT == 2) K8S_EP4U("%7", K8S_EP4U_MASK K8S_EP4U_TOL_MORE K8S_EP4U_PM, K8S_SG0P, K8S_SG1P, PREF, KEY); \
+    else if ((CLS & 1) && TT == 1) K8S_EP4U("%8", K8S_EP4U_MASK K8S_EP4U_PM, K8S_SG0P, K8S_SG1P, PREF, KEY);   \
+    else if (CLS & 1) K8S_EP4U("%7", K8S_EP4U_MASK K8S_EP4U_PM, K8S_SG0P, K8S_SG1P, PREF, KEY);                \
+    else if (TT == 2) K8S_EP4U("%7", K8S_EP4U_TOL_ONLY K8S_EP4U_PM, K8S_SG0P, K8S_SG1P, PREF, KEY);            \
+    else if (TT == 1) K8S_EP4U("%8", "", K8S_SG0, K8S_SG1, PREF, KEY);                                         \
+    else K8S_EP4U("%7", "", K8S_SG0, K8S_SG1, PREF, KEY)
+    if (CLS & 2) {
+        K8S_EP4U_T(K8S_EP4U_PREF, "key");
+    } else {
+        K8S_EP4U_T("", "%7");
+    }
+#undef K8S_EP4U_T
+#undef K8S_SG0
+#undef K8S_SG1
+#undef K8S_SG0P
+#undef K8S_SG1P
+}
+
 // (RES = 4: rg is ep4_request(req_gpu, false), as the kernel keeps it)
 template <int RES, int CLS = 3>
 __device__ __forceinline__ void eval_pair(const uint4 &na, const uint4 &nb, uint32_t rg, uint32_t rc, uint32_t rm,
@@ -463,7 +554,7 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
     for (int j = 0; j < PPT; ++j) {
         // thread -> pod: the active position itself, or the slot of the round's scoring order
         uint32_t slot;
-        const bool live = slot_of(sm, (blockIdx.x * PPT + j) * 256u + tid, &slot);
+        const bool live = slot_of(sm, (blockIdx.x * 256u + tid) * PPT + j, &slot);  // a thread takes neighbours: like pods, close rot(p)
         uint32_t pod = 0;
         pos[j] = 0xFFFFFFFFu;
         if (live) {
@@ -513,11 +604,21 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
         const uint32_t tset = w >> 2;  // bit t: some pod of the warp has taint class t
         const uint32_t wtt = ((tset & 4u) || (tset & 3u) == 3u) ? 2u : ((tset & 2u) ? 1u : 0u);
         wv = (w & 3u) | (wtt << 2);
-        // timing experiments only (results are wrong): 0..11 forces CLS | TT << 2; 16 only rules the
-        // taint specialisation out (results stay right)
+        // bit 4: in every thread of the warp the two pods share masks, preferred zone and (if the
+        // clause is evaluated) tolerations -- eval_pair4_u2.  An idle second pod takes the first's.
+        if (PPT == 2) {
+            if (pos[1] == 0xFFFFFFFFu) nsku[1] = nsku[0], nzone[1] = nzone[0], pzb[1] = pzb[0], ntol[1] = ntol[0];
+            const bool alike = nsku[0] == nsku[1] && nzone[0] == nzone[1] && pzb[0] == pzb[1] &&
+                               (wtt != 2u || ntol[0] == ntol[1]);
+            if (__all_sync(0xFFFFFFFFu, alike) && ((wv & 3u) != 0u || wtt == 2u) && cls_force != 17) wv |= 16u;
+        }
+        // timing experiments only (results are wrong): 0..11 forces CLS | TT << 2.  Results stay
+        // right with 16 (no taint specialisation, no shared clauses) and 17 (no shared clauses)
         if (cls_force >= 0 && cls_force < 12) wv = (uint32_t)cls_force;
-        if (cls_force == 16) wv |= 2u << 2, wv &= ~(1u << 2);
+        if (cls_force == 16) wv = (wv & 3u) | (2u << 2);
     }
+
+    const uint32_t msku = __brev(nsku[0]), mzone = __brev(nzone[0]);  // eval_pair4_u2: un-mirrored, for AND tests
 
     for (uint32_t t = t0; t < t1; ++t) {
         const uint32_t it = t - t0, buf = it % kStages;
@@ -533,14 +634,50 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
             uint32_t prev[PPT];
 #pragma unroll
             for (int j = 0; j < PPT; ++j) prev[j] = best[j];
-            // Does rot(p) of ANY pod of this warp fall inside this 64-node group?  The vote keeps the
-            // choice warp-uniform, so the two code paths never both run for one warp.
+            // Which of the group's four 16-node blocks hold rot(p) of SOME pod of this warp?  (Warp-
+            // uniform, so the two code paths never both run for one warp.)  Almost always none: the
+            // whole group goes through the class's loop, 64 evals per pod with no checks at all.
+            // Otherwise the runs of blocks without a rot(p) still do -- the same loop, so no second
+            // copy of it competes for the instruction cache -- and each block with one is walked node
+            // by node.  The pods of a warp are neighbours in rot(p) (the scoring order sorts them so),
+            // so a warp meets one or two such groups per pass over the node table.
+            uint32_t xb = 0;
             bool gx = false;
 #pragma unroll
             for (int j = 0; j < PPT; ++j) gx |= (rrel[j] - g) < kGroup;
-            if (!__any_sync(0xFFFFFFFFu, gx)) {  // common case: 64 evals per pod, no checks at all
+            if (__any_sync(0xFFFFFFFFu, gx)) {
+#pragma unroll
+                for (int j = 0; j < PPT; ++j) xb |= (rrel[j] - g) < kGroup ? 1u << ((rrel[j] - g) >> 4) : 0u;
+                xb = __reduce_or_sync(0xFFFFFFFFu, xb);
+            }
+            for (uint32_t k0 = g; k0 < g + kGroup;) {
+                const uint32_t bi = (k0 - g) >> 4;
+                if (xb & (1u << bi)) {  // rare: rot(p) of some pod of this warp falls inside this block
+                    // (a compact loop with branches: written with selects and unrolled it measured
+                    // 5 % slower on config 3)
+#pragma unroll 1
+                    for (uint32_t i = k0; i < k0 + 16u; ++i) {
+                        const uint4 a = tl[2 * i], b = tl[2 * i + 1];
+#pragma unroll
+                        for (int j = 0; j < PPT; ++j) {
+                            if (rrel[j] == i) {  // entering n >= rot: bank the winner so far, lower it
+                                if (best[j] != prev[j])
+                                    bestn[j] = nbase + g + (kGroup - 1u) - ((best[j] & kIdxMask) >> 1);
+                                if (best[j] != 0u) best[j] = (best[j] & ~(kIdxMask | 1u)) - 1u;
+                                prev[j] = best[j];
+                            }
+                            eval_pair<RES>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j],
+                                           negone);
+                        }
+                    }
+                    k0 += 16u;
+                    continue;
+                }
+                // the run of blocks up to the next one that holds a rot(p)
+                const uint32_t later = xb >> bi;  // bit 0 is clear
+                const uint32_t k1 = later ? k0 + ((uint32_t)__ffs((int)later) - 1u) * 16u : g + kGroup;
 #define K8S_GROUP(CLS, TT)                                                                                       \
-    _Pragma("unroll 1") for (uint32_t kb = g; kb < g + kGroup; kb += 16) {                                       \
+    _Pragma("unroll 1") for (uint32_t kb = k0; kb < k1; kb += 16) {                                              \
         _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
             const uint4 b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                                                   \
             const uint4 a = ep4_needs_first_half<CLS, TT>() ? ldrec<PPT>(&tl[2 * (kb + i)]) : b;                 \
@@ -550,17 +687,40 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
         }                                                                                                        \
     }
 #define K8S_GROUP_RES(CLS)                                                                                       \
-    _Pragma("unroll 1") for (uint32_t kb = g; kb < g + kGroup; kb += 16) {                                       \
+    _Pragma("unroll 1") for (uint32_t kb = k0; kb < k1; kb += 16) {                                              \
         _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
             const uint4 a = ldrec<PPT>(&tl[2 * (kb + i)]), b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                \
             _Pragma("unroll") for (int j = 0; j < PPT; ++j)                                                      \
                 eval_pair<RES, CLS>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j], negone); \
         }                                                                                                        \
     }
+#define K8S_GROUP_U(CLS, TT)                                                                                     \
+    _Pragma("unroll 1") for (uint32_t kb = k0; kb < k1; kb += 16) {                                              \
+        _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
+            const uint4 b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                                                   \
+            const uint4 a = ep4_needs_first_half<CLS, TT>() ? ldrec<PPT>(&tl[2 * (kb + i)]) : b;                 \
+            eval_pair4_u2<CLS, TT>(a, b, TT == 1 ? rg5[0] : rg[0], TT == 1 ? rg5[PPT - 1] : rg[PPT - 1], rc[0],  \
+                                   rc[PPT - 1], rm[0], rm[PPT - 1], msku, mzone, ntol[0], pzb[0], best[0],        \
+                                   best[PPT - 1], negone, one[0], one[PPT - 1]);                                 \
+        }                                                                                                        \
+    }
                 if (RES != 4) {
                     K8S_GROUP_RES(3)
+                } else if (PPT == 2 && (wv & 16u)) {
+                    switch (wv & 15u) {
+                    case 1: K8S_GROUP_U(1, 0) break;
+                    case 2: K8S_GROUP_U(2, 0) break;
+                    case 3: K8S_GROUP_U(3, 0) break;
+                    case 5: K8S_GROUP_U(1, 1) break;
+                    case 6: K8S_GROUP_U(2, 1) break;
+                    case 7: K8S_GROUP_U(3, 1) break;
+                    case 8: K8S_GROUP_U(0, 2) break;
+                    case 9: K8S_GROUP_U(1, 2) break;
+                    case 10: K8S_GROUP_U(2, 2) break;
+                    default: K8S_GROUP_U(3, 2) break;
+                    }
                 } else {
-                    switch (wv) {
+                    switch (wv & 15u) {
                     case 0: K8S_GROUP(0, 0) break;
                     case 1: K8S_GROUP(1, 0) break;
                     case 2: K8S_GROUP(2, 0) break;
@@ -576,54 +736,9 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
                     }
                 }
 #undef K8S_GROUP_RES
+#undef K8S_GROUP_U
 #undef K8S_GROUP
-            } else {
-#pragma unroll 1
-                for (uint32_t kb = g; kb < g + kGroup; kb += 8) {
-                    bool cx = false;
-#pragma unroll
-                    for (int j = 0; j < PPT; ++j) cx |= (rrel[j] - kb) < 8u;
-                    if (!__any_sync(0xFFFFFFFFu, cx)) {
-                        // (with ~64 pods per warp and 157 groups of 64 nodes at config 3, four in ten
-                        // groups come through here: these chunks are class-specialised as well)
-#define K8S_CHUNK(CLS)                                                                                           \
-    _Pragma("unroll") for (uint32_t i = 0; i < 8; ++i) {                                                         \
-        const uint4 a = ldrec<PPT>(&tl[2 * (kb + i)]), b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                    \
-        _Pragma("unroll") for (int j = 0; j < PPT; ++j)                                                          \
-            eval_pair<RES, CLS>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j], negone); \
-    }
-                        // (not with four pods per thread: on wide node tables few groups come this
-                        // way, and the extra code cost config 4 10 % -- registers spilled)
-                        // (and the taint clause stays in: these chunks are a few per cent of the evals)
-                        const uint32_t wcls = wv & 3u;
-                        if (RES != 4 || PPT >= 4 || wcls == 3) {
-                            K8S_CHUNK(3)
-                        } else if (wcls == 0) {
-                            K8S_CHUNK(0)
-                        } else if (wcls == 2) {
-                            K8S_CHUNK(2)
-                        } else {
-                            K8S_CHUNK(1)
-                        }
-#undef K8S_CHUNK
-                    } else {  // rare: rot(p) of some pod of this warp falls inside this 8-node chunk
-#pragma unroll 1
-                        for (uint32_t i = 0; i < 8; ++i) {
-                            const uint4 a = tl[2 * (kb + i)], b = tl[2 * (kb + i) + 1];
-#pragma unroll
-                            for (int j = 0; j < PPT; ++j) {
-                                if (rrel[j] == kb + i) {  // entering n >= rot: bank the winner so far, lower it
-                                    if (best[j] != prev[j])
-                                        bestn[j] = nbase + g + (kGroup - 1u) - ((best[j] & kIdxMask) >> 1);
-                                    if (best[j] != 0u) best[j] = (best[j] & ~(kIdxMask | 1u)) - 1u;
-                                    prev[j] = best[j];
-                                }
-                                eval_pair<RES>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j],
-                                               best[j], negone);
-                            }
-                        }
-                    }
-                }
+                k0 = k1;
             }
 #pragma unroll
             for (int j = 0; j < PPT; ++j)
@@ -1445,6 +1560,7 @@ int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_p
     K8S_CUDA(ctx, st.flags.reserve(2 * m * 4 + 16));
     K8S_CUDA(ctx, st.seg.reserve(((size_t)ceil_div(st.m ? st.m : 1u, kSegThreads) + 1) * sizeof(Seg)));
     K8S_CUDA(ctx, st.counters.reserve(64 * 4));
+    K8S_CUDA(ctx, st.like_seen.reserve((size_t)(16u << kLikeBits) * 4));
     {  // scratch of the single-launch admission path, sized for all m pods up front
         const size_t nbmax = ceil_div(st.m ? st.m : 1u, kSortTile);
         K8S_CUDA(ctx, st.sort.keys_alt.reserve(m * 4 + 16));
@@ -1482,14 +1598,26 @@ int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
     if (st.n)  // which taints occur at all: decides how each pod's toleration clause is scored
         K8S_LAUNCH(ctx, taint_union_kernel, ceil_div(st.n, 256), 256, 0, s, st.node_cols.as<uint32_t>() + 6 * (size_t)st.n,
                    st.n, st.counters.as<uint32_t>() + kTaintUnion);
+    // Sorting like pods together (a hash of their masks and preferred zone, under the class) lets a
+    // thread share clauses between its two pods (eval_pair4_u2: config 4 272 against 309 ms,
+    // config 3 4.56 against 4.69), but splits each class into runs whose pods' rot(p) lie further
+    // apart, and every 64-node group that holds some rot(p) of a warp costs it about twice a plain
+    // one: a warp meets 64 / (pods per run) + 64 / N of its groups that way.  So the hash is kept
+    // only while the runs average kLikeMinRun pods (counted by pod_prep, applied by
+    // like_hash_fix_kernel -- no host round trip).  order = 2 + b forces b hash bits.
+    const bool adaptive = ctx->tune.order < 2;
+    const uint32_t hash_bits = adaptive ? kLikeBits : (uint32_t)(ctx->tune.order - 2 > 12 ? 12 : ctx->tune.order - 2);
+    if (st.m && ordered && adaptive) K8S_CUDA(ctx, cudaMemsetAsync(st.like_seen.p, 0, (size_t)(16u << kLikeBits) * 4, s));
     if (st.m) {
         uint32_t *spod = st.order[0].as<uint32_t>(), *posof = st.inv[0].as<uint32_t>(), *slotof = st.inv[1].as<uint32_t>();
         uint32_t *keys = st.sort_keys.as<uint32_t>();
         K8S_LAUNCH(ctx, pod_prep_kernel, ceil_div(st.m, 256), 256, 0, s, st.pod_cols.as<uint32_t>(), st.m, st.n,
                    st.policy_flags, st.score_res == 4 ? 1 : 0, st.podq.as<PodQ>(), st.assign.as<int32_t>(),
-                   st.active[0].as<uint32_t>(), st.counters.as<uint32_t>(), ordered ? keys : nullptr, spod, posof);
+                   st.active[0].as<uint32_t>(), st.counters.as<uint32_t>(), ordered ? keys : nullptr, spod, posof,
+                   hash_bits, ordered && adaptive ? st.like_seen.as<uint32_t>() : nullptr);
         if (ordered) {
-            int rc = sort_pairs(ctx, s, keys, spod, st.m, 12, st.sort);  // by (class, rot bucket), pod order inside
+            if (adaptive) K8S_LAUNCH(ctx, like_hash_fix_kernel, ceil_div(st.m, 256), 256, 0, s, keys, st.m, st.counters.as<uint32_t>());
+            int rc = sort_pairs(ctx, s, keys, spod, st.m, 24, st.sort);  // by (class, like pods, rot bucket), pod order inside
             if (rc) return rc;
             K8S_LAUNCH(ctx, slot_init_kernel, ceil_div(st.m, 256), 256, 0, s, spod, st.m, slotof);
             st.order_valid = true;

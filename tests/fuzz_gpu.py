@@ -70,8 +70,8 @@ def case_place(rng, ctx):
     env = dict(res=int(rng.choice([0, 1, 2, 3, 4, 4, 4, 4])), ppt=int(rng.choice([1, 2, 4])), coop=int(rng.choice([0, 1, 1])),
                order=int(rng.choice([0, 1, 1])),  # order: scoring order sorted by pod class (RES 4 + one-launch admission)
                slot_admit=int(rng.choice([0, 1, 1])))  # slot admission where its domain holds, else the sort
-    if rng.random() < 0.2:  # toleration clause always evaluated (no taint-class specialisation)
-        env["force_cls"] = 16
+    if rng.random() < 0.3:  # 16: toleration clause always evaluated, 17: no clauses shared between a thread's pods
+        env["force_cls"] = int(rng.choice([16, 17]))
     if rng.random() < 0.5:
         env["splits"] = int(rng.integers(1, 9))
     if rng.random() < 0.5:  # few CTAs in the single-launch admission: every CTA loops over several tiles
