@@ -259,7 +259,7 @@ static int group_rounds(k8sgpu_ctx *ctx, const NcclApi *api) {
     while (lead.n_active > 0 && (lead.max_rounds == 0 || lead.rounds < lead.max_rounds)) {
         const uint32_t na = lead.n_active;
         // How the round's scoring slots are shared out.  With the one-launch admission: blocks of
-        // 2048 slots dealt round-robin (the slots are sorted by pod class, cheap classes first, so
+        // 2048 slots dealt round-robin (the slots are sorted by pod class, dearest classes first, so
         // contiguous shares would be unequal work); each rank's proposals are then one contiguous
         // run of `slice` entries in the exchanged array.  With the kernel chain (a test path, no
         // class order): contiguous shares of the active list.

@@ -120,7 +120,8 @@ __global__ void __launch_bounds__(256) pod_prep_kernel(const uint32_t *__restric
         const uint32_t rb = 20u - hash_bits;
         const uint32_t where = n_nodes ? (uint32_t)(((unsigned long long)q.rot << rb) / n_nodes) : 0u;
         const uint32_t hh = hash_bits ? h >> (32u - hash_bits) : 0u;
-        sort_key[p] = (cls << 20) | (hh << rb) | where;
+        // (dearest classes first: the grid's last CTAs, which no other work can hide, are then the cheap ones)
+        sort_key[p] = ((15u - cls) << 20) | (hh << rb) | where;
         if (seen) {  // count the distinct (class, hash) values: one atomic per value, then plain reads
             uint32_t *sn = seen + ((cls << kLikeBits) | hh);
             if (*(volatile uint32_t *)sn == 0u && atomicExch(sn, 1u) == 0u) atomicAdd(err + kLikeRuns, 1u);
@@ -476,7 +477,7 @@ __device__ __forceinline__ void eval_pair(const uint4 &na, const uint4 &nb, uint
 
 // Which scoring slots a launch covers.  One GPU, or the round-at-a-time API: the contiguous range
 // [lo, hi).  A placement group of xw ranks: blocks of kXBlock slots dealt round-robin, rank r
-// taking blocks r, r + xw, ... -- the slots are sorted by pod class (cheap classes first), so
+// taking blocks r, r + xw, ... -- the slots are sorted by pod class (dearest classes first), so
 // contiguous ranges would give the ranks unequal work.  A rank's slots are numbered 0 .. xcnt by
 // their local index jj; in the exchanged proposal array rank r's slot jj sits at r * xcnt + jj.
 constexpr uint32_t kXBlock = 2048;
@@ -500,6 +501,7 @@ __device__ __forceinline__ uint32_t exchange_index(uint32_t s, uint32_t xw, uint
 
 constexpr int kDefaultRes = 4;
 constexpr uint32_t kStages = K8S_STAGES;  // node tiles in flight per CTA
+
 constexpr uint32_t kGroup = 64;        // nodes per index group (index bits 1..6 of the key)
 constexpr uint32_t kIdxMask = 0x7Eu;   // those bits
 
@@ -513,7 +515,11 @@ constexpr uint32_t kIdxMask = 0x7Eu;   // those bits
 // the running best is lowered to just below its own key, which lets a later node with an EQUAL
 // key take over -- exactly "nodes at or after rot come first".  Only the 8-node chunk that
 // contains rot takes the slow path.
-template <int PPT, int RES, int MB>
+// UNR: nodes per trip of the class loops (divides 16).  16 amortises the loop bookkeeping best; 8
+// halves the 22 loop bodies, which matters when CTAs are short-lived and the SM's instruction
+// cache holds many classes at once (measured: config 3, one tile per CTA, 4.49 vs 4.61 ms per
+// placement; config 4, 79 tiles per CTA, 273.9 vs 270.7).
+template <int PPT, int RES, int MB, int UNR = 16>
 __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict__ nodeq, uint32_t n_tiles,
                                                     uint32_t tiles_per_split, const PodQ *__restrict__ podq,
                                                     const uint32_t *__restrict__ active, SlotMap sm,
@@ -677,8 +683,8 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
                 const uint32_t later = xb >> bi;  // bit 0 is clear
                 const uint32_t k1 = later ? k0 + ((uint32_t)__ffs((int)later) - 1u) * 16u : g + kGroup;
 #define K8S_GROUP(CLS, TT)                                                                                       \
-    _Pragma("unroll 1") for (uint32_t kb = k0; kb < k1; kb += 16) {                                              \
-        _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
+    _Pragma("unroll 1") for (uint32_t kb = k0; kb < k1; kb += UNR) {                                              \
+        _Pragma("unroll") for (uint32_t i = 0; i < UNR; ++i) {                                                   \
             const uint4 b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                                                   \
             const uint4 a = ep4_needs_first_half<CLS, TT>() ? ldrec<PPT>(&tl[2 * (kb + i)]) : b;                 \
             _Pragma("unroll") for (int j = 0; j < PPT; ++j)                                                      \
@@ -687,16 +693,16 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
         }                                                                                                        \
     }
 #define K8S_GROUP_RES(CLS)                                                                                       \
-    _Pragma("unroll 1") for (uint32_t kb = k0; kb < k1; kb += 16) {                                              \
-        _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
+    _Pragma("unroll 1") for (uint32_t kb = k0; kb < k1; kb += UNR) {                                              \
+        _Pragma("unroll") for (uint32_t i = 0; i < UNR; ++i) {                                                   \
             const uint4 a = ldrec<PPT>(&tl[2 * (kb + i)]), b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                \
             _Pragma("unroll") for (int j = 0; j < PPT; ++j)                                                      \
                 eval_pair<RES, CLS>(a, b, rg[j], rc[j], rm[j], nsku[j], nzone[j], ntol[j], pzb[j], best[j], negone); \
         }                                                                                                        \
     }
 #define K8S_GROUP_U(CLS, TT)                                                                                     \
-    _Pragma("unroll 1") for (uint32_t kb = k0; kb < k1; kb += 16) {                                              \
-        _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
+    _Pragma("unroll 1") for (uint32_t kb = k0; kb < k1; kb += UNR) {                                              \
+        _Pragma("unroll") for (uint32_t i = 0; i < UNR; ++i) {                                                   \
             const uint4 b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                                                   \
             const uint4 a = ep4_needs_first_half<CLS, TT>() ? ldrec<PPT>(&tl[2 * (kb + i)]) : b;                 \
             eval_pair4_u2<CLS, TT>(a, b, TT == 1 ? rg5[0] : rg[0], TT == 1 ? rg5[PPT - 1] : rg[PPT - 1], rc[0],  \
@@ -1702,12 +1708,14 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     if (timed) K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed], s));
     dim3 grid(xb, splits);
     const int res = st.score_res;  // fixed at round_begin: the pod records are laid out for it
-#define K8S_SCORE(P, R, B)                                                                                         \
-    K8S_LAUNCH(ctx, (score_kernel<P, R, B>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
+#define K8S_SCORE(P, R, B) K8S_SCORE_U(P, R, B, 16)
+#define K8S_SCORE_U(P, R, B, U)                                                                                    \
+    K8S_LAUNCH(ctx, (score_kernel<P, R, B, U>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
                st.active[st.cur].as<uint32_t>(), sm, bk, st.n, use_atomic, 0xFFFFFFFFu, ctx->tune.force_cls, view.spod,  \
                view.posof, st.counters.as<uint32_t>() + kTaintUnion)
     // third argument: resident CTAs per SM the register budget is set for (measured best per variant)
     if (ppt == 4) K8S_SCORE(4, 4, 3);
+    else if (ppt == 2 && res >= 4 && tps <= 4) K8S_SCORE_U(2, 4, 4, 8);  // short-lived CTAs: see UNR
     else if (ppt == 2 && res >= 4) K8S_SCORE(2, 4, 4);
     else if (ppt == 2 && res == 3) K8S_SCORE(2, 3, 5);
     else if (ppt == 2 && res == 2) K8S_SCORE(2, 2, 5);
@@ -1719,6 +1727,7 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     else if (res == 1) K8S_SCORE(1, 1, 6);
     else K8S_SCORE(1, 0, 6);
 #undef K8S_SCORE
+#undef K8S_SCORE_U
     if (timed) {
         K8S_CUDA(ctx, cudaEventRecord(ctx->ev_score[2 * st.timed + 1], s));
         st.timed++;
