@@ -77,6 +77,7 @@ struct PlaceState {
     DevBuf seg;        // segmented-scan block aggregates
     DevBuf flags;      // m u32 (compaction flags / scan output)
     DevBuf counters;   // small u32 block: [0]=error flag, [1]=next active count, [2]=placed
+    DevBuf res_min;    // 2 x 128 u32: per-round resource summary of the node table (resmin_note), by round parity
     DevBuf like_seen;  // 65536 u32: which (class, hash) values occur among the pods (scoring order, per run)
     SortScratch sort;
     DevBuf scan_tmp;

@@ -31,8 +31,9 @@ struct __align__(16) NodeQ {  // what the inner loop reads; rebuilt from the fre
     uint32_t khi;         // 1<<31 | (0x7FFF - free_gpu) << 16 | (255 - cap_gpu) << 8 | (63 - n % 64) << 1
                           // (RES = 4 also takes the free-GPU test from here: see eval_pair4)
     uint32_t zrot;        // bits 0..4: (zone_id - 7) mod 32, rotates the pod's one-hot preferred zone onto bit 7
-                          // bits 5..31: free_gpu, or -1 when the node is not schedulable OR carries a taint
-                          // (eval_pair4 TT = 1; the funnel shift reads only the low five bits)
+                          // (the funnel shift reads only these five bits)
+                          // bits 5..12: min(free_gpu, 127), or -1 when the node is not schedulable (eval R, TT = 0)
+                          // bits 13..31: free_gpu, or -1 when not schedulable OR tainted (TT = 1)
 };
 static_assert(sizeof(NodeQ) == 32, "node record is 32 B: the algorithmic bytes per eval");
 
@@ -52,6 +53,8 @@ constexpr int kSlotVeto = 5;
 constexpr int kTaintUnion = 6;  // counters[6]: OR of every node's taint mask (per run, before pod_prep)
 constexpr int kLikeRuns = 7;    // counters[7]: how many distinct (class, hash) values the pods' sort keys hold
 constexpr uint32_t kLikeBits = 12, kLikeMinRun = 1024;
+constexpr int kResWide = 8;     // counters[8] != 0: some schedulable node has >= kResGpus free GPUs (no resource summary)
+constexpr uint32_t kResGpus = 64;  // the summary below covers free_gpu 0 .. 63
 
 __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -157,7 +160,8 @@ __device__ __forceinline__ NodeQ make_nodeq(const uint32_t *__restrict__ cols, c
         q.taint = taint;
         q.khi = 0x80000000u | ((0x7FFFu - (fg & 0x7FFFu)) << 16) | ((255u - (cap & 255u)) << 8) |
                 ((63u - (i & 63u)) << 1);
-        q.zrot = ((zone - 7u) & 31u) | ((((flags & 1u) && taint == 0u) ? fg : 0xFFFFFFFFu) << 5);
+        q.zrot = ((zone - 7u) & 31u) | ((((flags & 1u) ? min(fg, 127u) : 0xFFu) & 0xFFu) << 5) |
+                 ((((flags & 1u) && taint == 0u) ? fg : 0xFFFFFFFFu) << 13);
     } else {  // padding up to a whole tile: never feasible
         q.free_gpu_s = q.free_mcpu_s = 0xFFFFFFFFu;
         q.free_mib = 0;
@@ -168,11 +172,35 @@ __device__ __forceinline__ NodeQ make_nodeq(const uint32_t *__restrict__ cols, c
     return q;
 }
 
-__global__ void node_prep_kernel(const uint32_t *__restrict__ cols, const uint32_t *__restrict__ freec, uint32_t n,
+// Resource summary of a round's node table: tab[g] = the least free_mcpu, tab[kResGpus + g] the
+// least free_mib, among the schedulable nodes with exactly g free GPUs.  From it the scoring kernel
+// decides, per pod, whether "enough GPUs" already implies "enough CPU and memory" at EVERY node
+// (req_mcpu <= min over g' >= req_gpu of tab[g'], likewise memory): then the two other resource
+// differences of that pod's evals are never negative where the first is not, and are left out.
+// Called by whole warps (one node per lane); one atomic pair per distinct g per warp.
+__device__ __forceinline__ void resmin_note(uint32_t *__restrict__ tab, uint32_t *__restrict__ counters, const NodeQ &q) {
+    const bool sched = q.free_mcpu_s != 0xFFFFFFFFu;
+    uint32_t g = sched ? q.free_gpu_s : 0xFFFFFFFFu;
+    if (sched && g >= kResGpus) {
+        atomicOr(counters + kResWide, 1u);
+        g = 0xFFFFFFFFu;
+    }
+    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, g);
+    const uint32_t mc = __reduce_min_sync(peers, q.free_mcpu_s), mm = __reduce_min_sync(peers, q.free_mib);
+    if (g != 0xFFFFFFFFu && (threadIdx.x & 31u) == (uint32_t)__ffs((int)peers) - 1u) {
+        atomicMin(tab + g, mc);
+        atomicMin(tab + kResGpus + g, mm);
+    }
+}
+
+__global__ void __launch_bounds__(256) node_prep_kernel(const uint32_t *__restrict__ cols, const uint32_t *__restrict__ freec, uint32_t n,
                                  uint32_t n_pad, NodeQ *__restrict__ nodeq, uint32_t *__restrict__ err,
-                                 int validate) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n_pad) nodeq[i] = make_nodeq(cols, freec, n, i, err, validate);
+                                 int validate, uint32_t *__restrict__ resmin) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;  // (n_pad is a multiple of 256: whole warps)
+    if (i >= n_pad) return;
+    const NodeQ q = make_nodeq(cols, freec, n, i, err, validate);
+    nodeq[i] = q;
+    resmin_note(resmin, err, q);
 }
 
 // ------------------------------------------------------------------ TMA bulk copy + mbarrier
@@ -259,8 +287,8 @@ template <int PPT> __device__ __forceinline__ uint4 ldrec(const uint4 *p) { retu
 // The free-GPU test needs no word of its own.  TT != 1: khi holds 0x7FFF - free_gpu in bits 16..30
 // under a set bit 31, so khi + (0x80000000 + (req << 16)) has bit 31 set exactly when
 // 0x7FFF - free + req carries out of the field, i.e. when free < req (rq = minus that constant,
-// req clamped to 0x8000 -- no node has more than 0x7FFF free).  TT = 1: zrot's bits 5..31 hold
-// free_gpu, or -1 on a tainted node; rq = req << 5.  An unschedulable node has free_mcpu = -1.
+// req clamped to 0x8000 -- no node has more than 0x7FFF free).  TT = 1: zrot's bits 13..31 hold
+// free_gpu, or -1 on a tainted node; rq = req << 13.  An unschedulable node has free_mcpu = -1.
 #define K8S_EP4(FREEW, MASKMUL, TAND, TSETP, MASKOR, SIGN, PREF, KEY)                                              \
     asm("{\n\t"                                                                                                    \
         ".reg .pred pf;\n\t"                                                                                       \
@@ -290,7 +318,7 @@ template <int PPT> __device__ __forceinline__ uint4 ldrec(const uint4 *p) { retu
 template <int CLS, int TT> __host__ __device__ constexpr bool ep4_needs_first_half() { return (CLS & 1) || TT == 2; }
 __device__ __forceinline__ uint32_t ep4_request(uint32_t req_gpu, bool tainted_field) {
     const uint32_t r = min(req_gpu, 0x8000u);
-    return tainted_field ? r << 5 : 0u - (0x80000000u + (r << 16));
+    return tainted_field ? r << 13 : 0u - (0x80000000u + (r << 16));
 }
 template <int CLS, int TT>
 __device__ __forceinline__ void eval_pair4(const uint4 &a, const uint4 &b, uint32_t rq, uint32_t rc, uint32_t rm,
@@ -379,6 +407,87 @@ __device__ __forceinline__ void eval_pair4_u2(const uint4 &a, const uint4 &b, ui
 #undef K8S_SG1
 #undef K8S_SG0P
 #undef K8S_SG1P
+}
+
+// R: evals of pods for which, this round, "enough GPUs" implies "enough CPU and memory" at every
+// node (resmin_note).  Only the GPU difference is left: against the field of NodeQ::zrot that is
+// -1 on an unschedulable (TT = 0: bits 5..12, brought to the top by the multiply) or unschedulable
+// or tainted node (TT = 1: bits 13..31).  rq: ep4_request_r.
+//   %0 best | %1 khi %2 zrot | %3 rq | %4 runtime -1 | %5 runtime 1 | %6 runtime 2^19
+template <int TT>
+__device__ __forceinline__ void eval_pair4_r(const uint4 &b, uint32_t rq, uint32_t &best, uint32_t negone,
+                                             uint32_t one, uint32_t k19) {
+    if (TT == 1) {
+        asm("{\n\t"
+            ".reg .pred pf;\n\t"
+            ".reg .b32 d1;\n\t"
+            "mad.lo.s32 d1, %3, %4, %2;\n\t"
+            "setp.ge.s32 pf, d1, 0;\n\t"
+            "setp.gt.and.u32 pf, %1, %0, pf;\n\t"
+            "@pf mad.lo.u32 %0, %1, %5, 0;\n\t"
+            "}"
+            : "+r"(best)
+            : "r"(b.z), "r"(b.w), "r"(rq), "r"(negone), "r"(one), "r"(k19));
+    } else {
+        asm("{\n\t"
+            ".reg .pred pf;\n\t"
+            ".reg .b32 d1;\n\t"
+            "mad.lo.s32 d1, %2, %6, %3;\n\t"
+            "setp.ge.s32 pf, d1, 0;\n\t"
+            "setp.gt.and.u32 pf, %1, %0, pf;\n\t"
+            "@pf mad.lo.u32 %0, %1, %5, 0;\n\t"
+            "}"
+            : "+r"(best)
+            : "r"(b.z), "r"(b.w), "r"(rq), "r"(negone), "r"(one), "r"(k19));
+    }
+}
+// the GPU request in the form eval_pair4_r takes (free_gpu < kResGpus at every node when it runs)
+__device__ __forceinline__ uint32_t ep4_request_r(uint32_t req_gpu, bool tainted_field) {
+    return tainted_field ? min(req_gpu, 0x8000u) << 13 : 0u - (min(req_gpu, kResGpus) << 24);
+}
+// ... and for a thread's two like pods (eval_pair4_u2): masks and preference once per node.
+//   %0 %1 best | %2 sku_bit %3 zone_bit | %4 khi %5 zrot | %6 %7 rq | %8 sku mask %9 zone mask
+//   %10 pzb | %11 runtime -1 | %12 %13 runtime 1 | %14 runtime 2^19
+#define K8S_EP4UR(D0, D1, SHARED, SIGN0, SIGN1, PREF, KEY)                                                     \
+    asm("{\n\t"                                                                                                \
+        ".reg .pred pf0, pf1, pm;\n\t"                                                                         \
+        ".reg .b32 m, z, key, x1, y1;\n\t" D0 D1 SHARED SIGN0 SIGN1 PREF                                       \
+        "setp.gt.and.u32 pf0, " KEY ", %0, pf0;\n\t"                                                           \
+        "setp.gt.and.u32 pf1, " KEY ", %1, pf1;\n\t"                                                           \
+        "@pf0 mad.lo.u32 %0, " KEY ", %12, 0;\n\t"                                                             \
+        "@pf1 mad.lo.u32 %1, " KEY ", %13, 0;\n\t"                                                             \
+        "}"                                                                                                    \
+        : "+r"(best0), "+r"(best1)                                                                             \
+        : "r"(o_sku), "r"(o_zone), "r"(b.z), "r"(b.w), "r"(rq0), "r"(rq1), "r"(o_msku), "r"(o_mzone),         \
+          "r"(o_pzb), "r"(negone), "r"(one0), "r"(one1), "r"(k19))
+template <int CLS, int TT>
+__device__ __forceinline__ void eval_pair4_ur2(const uint4 &a, const uint4 &b, uint32_t rq0, uint32_t rq1,
+                                               uint32_t msku, uint32_t mzone, uint32_t pzb, uint32_t &best0,
+                                               uint32_t &best1, uint32_t negone, uint32_t one0, uint32_t one1,
+                                               uint32_t k19) {
+    const uint32_t o_sku = (CLS & 1) ? a.x : b.z, o_zone = (CLS & 1) ? a.y : b.z;
+    const uint32_t o_msku = (CLS & 1) ? msku : rq0, o_mzone = (CLS & 1) ? mzone : rq0, o_pzb = (CLS & 2) ? pzb : rq0;
+#define K8S_R_D0_T1 "mad.lo.s32 x1, %6, %11, %5;\n\t"
+#define K8S_R_D1_T1 "mad.lo.s32 y1, %7, %11, %5;\n\t"
+#define K8S_R_D0_T0 "mad.lo.s32 x1, %5, %14, %6;\n\t"
+#define K8S_R_D1_T0 "mad.lo.s32 y1, %5, %14, %7;\n\t"
+#define K8S_R_MASK "and.b32 m, %9, %3;\n\tlop3.b32 m, %8, %2, m, 0xEA;\n\tsetp.eq.u32 pm, m, 0;\n\t"
+#define K8S_R_PREF "shf.r.wrap.b32 z, %10, %10, %5;\n\tlop3.b32 key, z, 0x80, %4, 0xEA;\n\t"
+#define K8S_R_SG0 "setp.ge.s32 pf0, x1, 0;\n\t"
+#define K8S_R_SG1 "setp.ge.s32 pf1, y1, 0;\n\t"
+#define K8S_R_SG0P "setp.ge.and.s32 pf0, x1, 0, pm;\n\t"
+#define K8S_R_SG1P "setp.ge.and.s32 pf1, y1, 0, pm;\n\t"
+#define K8S_EP4UR_T(SHARED, S0, S1, PREF, KEY)                                                                 \
+    if (TT == 1) K8S_EP4UR(K8S_R_D0_T1, K8S_R_D1_T1, SHARED, S0, S1, PREF, KEY);                               \
+    else K8S_EP4UR(K8S_R_D0_T0, K8S_R_D1_T0, SHARED, S0, S1, PREF, KEY)
+    if (CLS == 1) {
+        K8S_EP4UR_T(K8S_R_MASK, K8S_R_SG0P, K8S_R_SG1P, "", "%4");
+    } else if (CLS == 2) {
+        K8S_EP4UR_T("", K8S_R_SG0, K8S_R_SG1, K8S_R_PREF, "key");
+    } else {
+        K8S_EP4UR_T(K8S_R_MASK, K8S_R_SG0P, K8S_R_SG1P, K8S_R_PREF, "key");
+    }
+#undef K8S_EP4UR_T
 }
 
 // (RES = 4: rg is ep4_request(req_gpu, false), as the kernel keeps it)
@@ -527,12 +636,16 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
                                                     int use_atomic, uint32_t negone, int cls_force,
                                                     const uint32_t *__restrict__ spod,
                                                     const uint32_t *__restrict__ posof,
-                                                    const uint32_t *__restrict__ tunion_ptr) {
+                                                    const uint32_t *__restrict__ ctr,
+                                                    const uint32_t *__restrict__ resmin) {
     // kStages-deep ring of node tiles.  full[b]: the TMA copy into buffer b has landed (one
     // arrival + its byte count); empty[b]: all 8 warps are done reading buffer b (one arrival per
     // warp).  No __syncthreads in the tile loop: a warp may run a tile ahead of its slowest sibling.
     __shared__ __align__(128) uint4 tile[kStages][kNodeTile * 2];
     __shared__ __align__(8) uint64_t full[kStages], empty[kStages];
+    // ressuf[0][g]: the least free_mcpu among the schedulable nodes with >= g free GPUs (resmin_note),
+    // ressuf[1][g]: the least free_mib; [kResGpus]: no such node
+    __shared__ uint32_t ressuf[2][kResGpus + 1];
     const int tid = threadIdx.x;
     const uint32_t t0 = blockIdx.y * tiles_per_split;
     const uint32_t t1 = min(t0 + tiles_per_split, n_tiles);
@@ -545,6 +658,22 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
             mbar_init(&empty[b], 256 / 32);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (RES == 4 && PPT == 2 && tid >= 32 && tid < 64) {  // warp 1: suffix minima of the round's resource summary
+        const uint32_t lane = tid - 32;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            uint32_t lo = __ldg(resmin + k * kResGpus + lane), hi = __ldg(resmin + k * kResGpus + 32 + lane);
+#pragma unroll
+            for (uint32_t off = 1; off < 32; off <<= 1) {
+                const uint32_t l2 = __shfl_down_sync(0xFFFFFFFFu, lo, off), h2 = __shfl_down_sync(0xFFFFFFFFu, hi, off);
+                if (lane + off < 32) lo = min(lo, l2), hi = min(hi, h2);
+            }
+            lo = min(lo, __shfl_sync(0xFFFFFFFFu, hi, 0));
+            ressuf[k][lane] = lo;
+            ressuf[k][32 + lane] = hi;
+            if (lane == 0) ressuf[k][kResGpus] = 0xFFFFFFFFu;
+        }
     }
     __syncthreads();
     if (tid == 0) {
@@ -586,6 +715,16 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
     // Class of this warp's pods (see eval_pair4): which clauses can be left out of the inner loop.
     // wv = CLS | TT << 2.  Idle lanes fit every variant (their request exceeds any free count).
     uint32_t wv = 3u | (2u << 2);
+    // R (eval_pair4_r): does "enough GPUs" imply "enough CPU and memory" at every node, for each of my pods?
+    bool implied = RES == 4 && PPT == 2 && __ldg(ctr + kResWide) == 0u;
+    uint32_t rgr0[PPT], rgr1[PPT];  // ... and the request in the forms those evals take
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        const uint32_t g = min(rg[j], kResGpus);
+        if (RES == 4 && PPT == 2) implied = implied && rc[j] <= ressuf[0][g] && rm[j] <= ressuf[1][g];
+        rgr0[j] = ep4_request_r(rg[j], false);
+        rgr1[j] = ep4_request_r(rg[j], true);
+    }
     uint32_t rg5[PPT];  // RES = 4: the GPU request in the two forms eval_pair4 takes (rg[] itself holds the other)
     // The multiplier of the predicated "best = key" mad, one copy per pod the compiler cannot tell
     // apart: with a shared one, two pods whose key is the node's own word (no preference clause)
@@ -599,7 +738,7 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
         one[j] = j == 0 ? 0u - negone : j == 1 ? negone * negone : j == 2 ? negone >> 31 : negone & 1u;
     }
     if (RES == 4) {
-        const uint32_t tunion = __ldg(tunion_ptr);
+        const uint32_t tunion = __ldg(ctr + kTaintUnion);
         uint32_t mine = 0;
 #pragma unroll
         for (int j = 0; j < PPT; ++j) {
@@ -618,13 +757,18 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
                                (wtt != 2u || ntol[0] == ntol[1]);
             if (__all_sync(0xFFFFFFFFu, alike) && ((wv & 3u) != 0u || wtt == 2u) && cls_force != 17) wv |= 16u;
         }
+        // bit 5: and for every pod of the warp the CPU and memory clauses are implied (R)
+        if (PPT == 2 && __all_sync(0xFFFFFFFFu, implied) && wtt < 2u && ((wv & 3u) == 0u || (wv & 16u)) &&
+            cls_force != 18 && cls_force != 16)
+            wv |= 32u;
         // timing experiments only (results are wrong): 0..11 forces CLS | TT << 2.  Results stay
-        // right with 16 (no taint specialisation, no shared clauses) and 17 (no shared clauses)
+        // right with 16 (no taint specialisation, nothing shared, no R), 17 (nothing shared), 18 (no R)
         if (cls_force >= 0 && cls_force < 12) wv = (uint32_t)cls_force;
         if (cls_force == 16) wv = (wv & 3u) | (2u << 2);
     }
 
     const uint32_t msku = __brev(nsku[0]), mzone = __brev(nzone[0]);  // eval_pair4_u2: un-mirrored, for AND tests
+    const uint32_t k19 = one[0] << 19;                                   // eval_pair4_r: a runtime 2^19
 
     for (uint32_t t = t0; t < t1; ++t) {
         const uint32_t it = t - t0, buf = it % kStages;
@@ -710,8 +854,37 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
                                    best[PPT - 1], negone, one[0], one[PPT - 1]);                                 \
         }                                                                                                        \
     }
+#define K8S_GROUP_R(TT) /* (short bodies: always 16 nodes per trip) */                                           \
+    _Pragma("unroll 1") for (uint32_t kb = k0; kb < k1; kb += 16) {                                              \
+        _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
+            const uint4 b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                                                   \
+            _Pragma("unroll") for (int j = 0; j < PPT; ++j)                                                      \
+                eval_pair4_r<TT>(b, TT == 1 ? rgr1[j] : rgr0[j], best[j], negone, one[j], k19);                  \
+        }                                                                                                        \
+    }
+#define K8S_GROUP_UR(CLS, TT)                                                                                    \
+    _Pragma("unroll 1") for (uint32_t kb = k0; kb < k1; kb += 16) {                                              \
+        _Pragma("unroll") for (uint32_t i = 0; i < 16; ++i) {                                                    \
+            const uint4 b = ldrec<PPT>(&tl[2 * (kb + i) + 1]);                                                   \
+            const uint4 a = (CLS & 1) ? ldrec<PPT>(&tl[2 * (kb + i)]) : b;                                       \
+            eval_pair4_ur2<CLS, TT>(a, b, TT == 1 ? rgr1[0] : rgr0[0], TT == 1 ? rgr1[PPT - 1] : rgr0[PPT - 1],  \
+                                    msku, mzone, pzb[0], best[0], best[PPT - 1], negone, one[0], one[PPT - 1],   \
+                                    k19);                                                                        \
+        }                                                                                                        \
+    }
                 if (RES != 4) {
                     K8S_GROUP_RES(3)
+                } else if (PPT == 2 && (wv & 32u)) {
+                    switch (wv & 7u) {
+                    case 0: K8S_GROUP_R(0) break;
+                    case 1: K8S_GROUP_UR(1, 0) break;
+                    case 2: K8S_GROUP_UR(2, 0) break;
+                    case 3: K8S_GROUP_UR(3, 0) break;
+                    case 4: K8S_GROUP_R(1) break;
+                    case 5: K8S_GROUP_UR(1, 1) break;
+                    case 6: K8S_GROUP_UR(2, 1) break;
+                    default: K8S_GROUP_UR(3, 1) break;
+                    }
                 } else if (PPT == 2 && (wv & 16u)) {
                     switch (wv & 15u) {
                     case 1: K8S_GROUP_U(1, 0) break;
@@ -743,6 +916,8 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
                 }
 #undef K8S_GROUP_RES
 #undef K8S_GROUP_U
+#undef K8S_GROUP_R
+#undef K8S_GROUP_UR
 #undef K8S_GROUP
                 k0 = k1;
             }
@@ -1121,6 +1296,7 @@ struct AdmitArgs {
     NodeQ *nodeq;
     uint32_t *counters;                           // [1] <- next active count
     uint32_t na, n_nodes, n_pad;
+    uint32_t *resmin_done, *resmin_next;  // resource summaries (resmin_note): this round's (cleared here), the next round's (built here)
     int bits;
     unsigned long long *prof;  // optional: %globaltimer at each phase boundary (CTA 0), else null
     uint32_t *mailbox;         // mapped host memory: {seq, next active count, error flags}
@@ -1139,6 +1315,8 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = threadIdx.x, cta = blockIdx.x, G = gridDim.x;
     prof_mark(a, 0);
+    // the summary this round's scoring read is done with: empty it for the round after the next
+    if (cta == 0 && tid < 2 * kResGpus) a.resmin_done[tid] = 0xFFFFFFFFu;
     const uint32_t na = a.na, N = a.n_nodes;
     const uint32_t nb = (na + kSortTile - 1) / kSortTile;
 
@@ -1485,8 +1663,11 @@ __global__ void __launch_bounds__(256) admit_coop_kernel(AdmitArgs a) {
     }
     // the next round's packed node records, and its (shorter) key array cleared: one stream
     // operation fewer between this kernel and the next scoring launch
-    for (uint32_t i = cta * 256 + tid; i < a.n_pad; i += G * 256)
-        a.nodeq[i] = make_nodeq(a.node_cols, a.freec, N, i, nullptr, 0);
+    for (uint32_t i = cta * 256 + tid; i < a.n_pad; i += G * 256) {  // (whole warps: n_pad is a multiple of 256)
+        const NodeQ q = make_nodeq(a.node_cols, a.freec, N, i, nullptr, 0);
+        a.nodeq[i] = q;
+        resmin_note(a.resmin_next, a.counters, q);
+    }
     for (uint32_t i = cta * 256 + tid; i < na; i += G * 256) a.best_key_clear[i] = 0ull;
     prof_mark(a, 8);
 }
@@ -1567,6 +1748,7 @@ int place_upload(k8sgpu_ctx *ctx, const k8sgpu_node_table *nodes, const k8sgpu_p
     K8S_CUDA(ctx, st.seg.reserve(((size_t)ceil_div(st.m ? st.m : 1u, kSegThreads) + 1) * sizeof(Seg)));
     K8S_CUDA(ctx, st.counters.reserve(64 * 4));
     K8S_CUDA(ctx, st.like_seen.reserve((size_t)(16u << kLikeBits) * 4));
+    K8S_CUDA(ctx, st.res_min.reserve(2 * 2 * kResGpus * 4));
     {  // scratch of the single-launch admission path, sized for all m pods up front
         const size_t nbmax = ceil_div(st.m ? st.m : 1u, kSortTile);
         K8S_CUDA(ctx, st.sort.keys_alt.reserve(m * 4 + 16));
@@ -1594,6 +1776,7 @@ int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
     st.score_res = kDefaultRes;  // which eval_pair variant (see its comment); all are bit-identical
     if (ctx->tune.res >= 0) st.score_res = ctx->tune.res;
     K8S_CUDA(ctx, cudaMemsetAsync(st.counters.p, 0, 64 * 4, s));
+    K8S_CUDA(ctx, cudaMemsetAsync(st.res_min.p, 0xFF, 2 * 2 * kResGpus * 4, s));
     K8S_CUDA(ctx, cudaMemsetAsync(st.slots.p, 0xFF, ((size_t)st.n + 1) * kSlotsPerNode * 4, s));  // every node's slots empty
     if (st.n)
         K8S_CUDA(ctx, cudaMemcpyAsync(st.free_cols.p, st.node_cols.p, 3 * (size_t)st.n * 4, cudaMemcpyDeviceToDevice, s));
@@ -1645,10 +1828,12 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     if (xw > 1 && (lo != 0 || hi != st.n_active || xrank >= xw))
         return fail(ctx, K8SGPU_E_ARG, "score: a group round covers the whole active list");
     // node records from the current free columns (validated on the first round)
+    uint32_t *resmin = st.res_min.as<uint32_t>() + (st.rounds & 1u) * 2 * kResGpus;  // this round's summary
     if (prep) {
+        if (st.rounds) K8S_CUDA(ctx, cudaMemsetAsync(resmin, 0xFF, 2 * kResGpus * 4, s));
         K8S_LAUNCH(ctx, node_prep_kernel, ceil_div(st.n_pad, 256), 256, 0, s, st.node_cols.as<uint32_t>(),
                    st.free_cols.as<uint32_t>(), st.n, st.n_pad, st.nodeq.as<NodeQ>(), st.counters.as<uint32_t>(),
-                   st.rounds == 0 ? 1 : 0);
+                   st.rounds == 0 ? 1 : 0, resmin);
         st.nodeq_stale = false;
     }
     SlotMap sm;
@@ -1712,7 +1897,7 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
 #define K8S_SCORE_U(P, R, B, U)                                                                                    \
     K8S_LAUNCH(ctx, (score_kernel<P, R, B, U>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
                st.active[st.cur].as<uint32_t>(), sm, bk, st.n, use_atomic, 0xFFFFFFFFu, ctx->tune.force_cls, view.spod,  \
-               view.posof, st.counters.as<uint32_t>() + kTaintUnion)
+               view.posof, st.counters.as<uint32_t>(), resmin)
     // third argument: resident CTAs per SM the register budget is set for (measured best per variant)
     if (ppt == 4) K8S_SCORE(4, 4, 3);
     else if (ppt == 2 && res >= 4 && tps <= 4) K8S_SCORE_U(2, 4, 4, 8);  // short-lived CTAs: see UNR
@@ -1838,6 +2023,8 @@ int round_admit_coop_launch(k8sgpu_ctx *ctx, cudaStream_t s, const int32_t *prop
     a.na = na;
     a.n_nodes = st.n;
     a.n_pad = st.n_pad;
+    a.resmin_done = st.res_min.as<uint32_t>() + (st.rounds & 1u) * 2 * kResGpus;
+    a.resmin_next = st.res_min.as<uint32_t>() + ((st.rounds + 1u) & 1u) * 2 * kResGpus;
     a.bits = key_bits(st.n);
     a.prof = nullptr;
     const bool want_prof = ctx->tune.coop_prof != 0;

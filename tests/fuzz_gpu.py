@@ -36,8 +36,12 @@ def random_nodes(rng, n):
     caps = [1, 2, 4, 8, 16] if rng.random() < 0.5 else [1, 2, 4, 8]
     cap = rng.choice(caps, n).astype(np.uint32) if skew > 0.2 else np.full(n, 8, np.uint32)
     free = (rng.integers(0, 17, n) % (cap + 1)).astype(np.uint32) if skew > 0.1 else cap.copy()
-    return dict(free_gpu=free, free_mcpu=(free * rng.choice([4000, 12000])).astype(np.uint32),
-                free_mib=(free * rng.choice([28672, 243200])).astype(np.uint32), cap_gpu=cap,
+    # (CPU / memory per GPU: the same everywhere, or short on some nodes -- whether enough GPUs implies
+    # enough of both decides which evals the scoring kernel runs)
+    per_cpu = rng.choice([4000, 12000]) if rng.random() < 0.6 else rng.choice([1500, 4000, 12000], n)
+    per_mib = rng.choice([28672, 243200]) if rng.random() < 0.6 else rng.choice([9000, 28672, 243200], n)
+    return dict(free_gpu=free, free_mcpu=(free * per_cpu).astype(np.uint32),
+                free_mib=(free * per_mib).astype(np.uint32), cap_gpu=cap,
                 sku_id=rng.integers(0, rng.choice([1, 2, 32]), n).astype(np.uint32),
                 zone_id=rng.integers(0, rng.choice([1, 3, 32]), n).astype(np.uint32),
                 taint_mask=np.where(rng.random(n) < rng.choice([0.0, 0.1, 0.5]), rng.integers(1, rng.choice([2, 8]), n), 0).astype(np.uint32),
@@ -71,7 +75,7 @@ def case_place(rng, ctx):
                order=int(rng.choice([0, 1, 1])),  # order: scoring order sorted by pod class (RES 4 + one-launch admission)
                slot_admit=int(rng.choice([0, 1, 1])))  # slot admission where its domain holds, else the sort
     if rng.random() < 0.3:  # 16: toleration clause always evaluated, 17: no clauses shared between a thread's pods
-        env["force_cls"] = int(rng.choice([16, 17]))
+        env["force_cls"] = int(rng.choice([16, 17, 18]))  # 18: CPU / memory differences never left out
     if rng.random() < 0.5:
         env["splits"] = int(rng.integers(1, 9))
     if rng.random() < 0.5:  # few CTAs in the single-launch admission: every CTA loops over several tiles

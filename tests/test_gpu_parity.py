@@ -249,6 +249,42 @@ def test_toleration_classes(ctx, orc, synth, case, force):
     same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
 
 
+@pytest.mark.parametrize("force", [None, 18])
+@pytest.mark.parametrize("case", ["implied", "cpu_scarce", "mem_scarce_some", "mixed_requests", "wide_node", "zero_gpu"])
+def test_resource_implication(ctx, orc, synth, case, force):
+    """Each round the library summarises the node table (least free CPU / memory among the nodes
+    with >= g free GPUs) and leaves the CPU and memory differences out of the evals of pods for
+    which enough GPUs implies enough of both at every node.  Tables where that holds for all pods,
+    for none, for some, where it stops holding as nodes fill up, with a node beyond the summary's
+    64 GPUs, and with pods asking for 0 GPUs -- against the oracle, and against the kernel with
+    the shortcut ruled out (force_cls = 18)."""
+    rng = np.random.default_rng(len(case))
+    n, m = 900, 12000
+    nodes, pods = synth.gen_nodes(n, config_id=5), synth.gen_pods(m, config_id=5)
+    nodes = {k: v.copy() for k, v in nodes.items()}
+    pods = {k: v.copy() for k, v in pods.items()}
+    if case == "cpu_scarce":
+        nodes["free_mcpu"] = (nodes["free_mcpu"] // 3).astype(np.uint32)
+    elif case == "mem_scarce_some":
+        tight = rng.random(n) < 0.2
+        nodes["free_mib"] = np.where(tight, nodes["free_mib"] // 2, nodes["free_mib"]).astype(np.uint32)
+    elif case == "mixed_requests":
+        pods["req_mcpu"] = (pods["req_gpu"] * rng.choice([1000, 4000, 13000], m)).astype(np.uint32)
+        pods["req_mib"] = (pods["req_gpu"] * rng.choice([1024, 28672, 300000], m)).astype(np.uint32)
+    elif case == "wide_node":
+        nodes["free_gpu"][3], nodes["cap_gpu"][3] = 200, 255
+        nodes["free_mcpu"][3], nodes["free_mib"][3] = 100, 100
+    elif case == "zero_gpu":
+        pods["req_gpu"][::5] = 0
+        pods["req_mcpu"][::5] = rng.choice([0, 500, 50_000], len(pods["req_gpu"][::5])).astype(np.uint32)
+    ctx.set_tuning(force_cls=force)
+    ctx.place_upload(nodes, pods)
+    free = (nodes["free_gpu"], nodes["free_mcpu"], nodes["free_mib"])
+    want = orc.score_round(nodes, free, pods, np.arange(m, dtype=np.uint32), flags=0, nthreads=NCPU)
+    assert np.array_equal(ctx.score_once(0), want)
+    same_placement(ctx.place(nodes, pods), orc.place(nodes, pods, nthreads=NCPU))
+
+
 @pytest.mark.parametrize("slot_admit", [0, 1])
 @pytest.mark.parametrize("case", ["hetero", "ties_rot0", "zero_gpu_pod", "big_node", "one_node", "coop_grid_1"])
 def test_place_slot_admission(ctx, orc, synth, slot_admit, case):
