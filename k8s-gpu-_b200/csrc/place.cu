@@ -1852,8 +1852,11 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     if (cnt == 0) return K8SGPU_OK;
     const uint32_t n_tiles = st.n_pad / kNodeTile;
     // Grid shape.  The kernel is bound by the ALU pipe and the issue slots, so what matters is an
-    // even spread over the 148 SMs and a short tail: aim for ~64 CTAs per SM (one node tile per
-    // CTA at config 3), which measured 3-4 % faster than ~20 (profiles/r01_sweep_res4_ppt.txt).
+    // even spread over the 148 SMs, a short tail, and enough node tiles per CTA to pay for a CTA's
+    // start-up (a tenth of a one-tile CTA's instructions since the loops got short): aim for ~128
+    // CTAs per SM but at least two tiles per CTA.  Measured (profiles/r02_order_knobs.txt):
+    // config 3, 40 tiles: 20 splits 3.55 ms, 40 3.62, 10 3.73; config 4, 391 tiles: 10 splits
+    // 181.2 ms, 5 182.3, 3 185.1.
     const uint32_t sms = (uint32_t)ctx->sm_count;
     // Pods per thread: two share every shared-memory read of a node record, which is what makes
     // the 7-ALU variant (RES = 4) pay -- with one pod per thread it is issue bound.  Four per thread
@@ -1864,8 +1867,10 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     if (ctx->tune.ppt >= 1) ppt = ctx->tune.ppt >= 4 ? 4 : ctx->tune.ppt >= 2 ? 2 : 1;
     if (ppt == 4 && st.score_res != 4) ppt = 2;
     const uint32_t xb = ceil_div(cnt, 256u * ppt);
-    uint32_t splits = ceil_div(64u * sms, xb);
-    if (splits > n_tiles) splits = n_tiles;
+    uint32_t splits = ceil_div(128u * sms, xb);
+    uint32_t cap = n_tiles / 2u;
+    if ((uint64_t)xb * cap < 4ull * sms) cap = n_tiles;  // (few pods: the machine is not full otherwise)
+    if (splits > cap) splits = cap;
     if (ctx->tune.splits >= 1) splits = (uint32_t)ctx->tune.splits;
     if (splits < 1) splits = 1;
     if (splits > n_tiles) splits = n_tiles;
