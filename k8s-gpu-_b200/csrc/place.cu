@@ -637,7 +637,7 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
                                                     const uint32_t *__restrict__ spod,
                                                     const uint32_t *__restrict__ posof,
                                                     const uint32_t *__restrict__ ctr,
-                                                    const uint32_t *__restrict__ resmin) {
+                                                    const uint32_t *__restrict__ resmin, uint32_t big_rows) {
     // kStages-deep ring of node tiles.  full[b]: the TMA copy into buffer b has landed (one
     // arrival + its byte count); empty[b]: all 8 warps are done reading buffer b (one arrival per
     // warp).  No __syncthreads in the tile loop: a warp may run a tile ahead of its slowest sibling.
@@ -647,8 +647,11 @@ __global__ void __launch_bounds__(256, MB) score_kernel(const NodeQ *__restrict_
     // ressuf[1][g]: the least free_mib; [kResGpus]: no such node
     __shared__ uint32_t ressuf[2][kResGpus + 1];
     const int tid = threadIdx.x;
-    const uint32_t t0 = blockIdx.y * tiles_per_split;
-    const uint32_t t1 = min(t0 + tiles_per_split, n_tiles);
+    // grid.y: big_rows splits of tiles_per_split node tiles each, then one split per remaining tile
+    // (short CTAs that the hardware dispatches last: they fill the launch's final wave finely)
+    const uint32_t t0 = blockIdx.y < big_rows ? blockIdx.y * tiles_per_split
+                                              : big_rows * tiles_per_split + (blockIdx.y - big_rows);
+    const uint32_t t1 = min(t0 + (blockIdx.y < big_rows ? tiles_per_split : 1u), n_tiles);
     constexpr uint32_t kTileBytes = kNodeTile * sizeof(NodeQ);
 
     if (tid == 0) {
@@ -1881,6 +1884,22 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
         tps = ceil_div(n_tiles, splits);
         splits = ceil_div(n_tiles, tps);
     }
+    // The last wave.  With CTAs of a few tiles the launch is a handful of waves over the resident
+    // slots (4 per SM), and the SMs that run out of work first idle for up to a whole CTA (ncu,
+    // config 3, 20 splits of 2 tiles: SM sub-partitions active 86 % of the elapsed cycles).  So the
+    // last tiles -- about a wave and a half of CTAs -- are given one CTA each.
+    uint32_t big_rows = splits;
+    if (tps >= 2 && tps <= 4 && ctx->tune.splits < 1) {
+        uint32_t small = ceil_div(6u * sms, xb);  // tiles handled one per CTA
+        if (small >= n_tiles) {
+            small = n_tiles;
+        } else {
+            small += (n_tiles - small) % tps;  // the rest in whole splits
+        }
+        big_rows = (n_tiles - small) / tps;
+        if (big_rows + small <= 65535u) splits = big_rows + small;
+        else big_rows = splits;
+    }
     const int use_atomic = splits > 1;
     unsigned long long *bk = st.best_key.as<unsigned long long>();
     if (use_atomic && !(st.best_cleared_len >= ((st.order_valid || xw > 1) ? st.n_active : hi))) {  // (the single-launch admission leaves it cleared)
@@ -1902,7 +1921,7 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
 #define K8S_SCORE_U(P, R, B, U)                                                                                    \
     K8S_LAUNCH(ctx, (score_kernel<P, R, B, U>), grid, 256, 0, s, st.nodeq.as<NodeQ>(), n_tiles, tps, st.podq.as<PodQ>(), \
                st.active[st.cur].as<uint32_t>(), sm, bk, st.n, use_atomic, 0xFFFFFFFFu, ctx->tune.force_cls, view.spod,  \
-               view.posof, st.counters.as<uint32_t>(), resmin)
+               view.posof, st.counters.as<uint32_t>(), resmin, big_rows)
     // third argument: resident CTAs per SM the register budget is set for (measured best per variant)
     if (ppt == 4) K8S_SCORE(4, 4, 3);
     else if (ppt == 2 && res >= 4 && tps <= 4) K8S_SCORE_U(2, 4, 4, 8);  // short-lived CTAs: see UNR

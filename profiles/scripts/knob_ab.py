@@ -7,9 +7,9 @@ from k8sgpu_b200 import capi, synth
 cfg = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 n, m = (10_000, 100_000) if cfg == 3 else (100_000, 1_000_000)
 nodes, pods = synth.gen_nodes(n, cfg), synth.gen_pods(m, cfg)
-SETS = [dict(), dict(splits=20), dict(splits=14), dict(splits=10), dict(splits=8), dict()]
+SETS = [dict(), dict(splits=20), dict(splits=40), dict()]
 if cfg == 4:
-    SETS = [dict(), dict(splits=10), dict(splits=8), dict(splits=4), dict(splits=3)]
+    SETS = [dict(), dict(splits=10)]
 with capi.Context(0) as c:
     c.place_upload(nodes, pods)
     for kn in SETS:
