@@ -179,9 +179,11 @@ int k8sgpu_group_info(const k8sgpu_ctx *ctx, int *world, int *rank, int *nlocal,
 int k8sgpu_host_alloc(size_t bytes, void **out);
 int k8sgpu_host_free(void *p);
 
-/* Developer and test knobs by name ("res", "ppt", "splits", "coop", "coop_grid", "rec_path",
- * "rec_grid", "rec_segments", "coop_prof", "rec_prof", "exchange", "shard_admit"; -1 = automatic).
- * Every setting gives bit-identical results: they select kernel variants and launch shapes.  The
+/* Developer and test knobs by name ("res", "ppt", "splits", "order", "force_cls" (16 / 17 / 18
+ * only), "slot_admit", "coop", "coop_grid", "rec_path", "rec_grid", "rec_segments", "coop_prof",
+ * "rec_prof", "exchange", "shard_upload"; -1 = automatic; README.md lists what each selects).
+ * Every setting gives bit-identical results: they select kernel variants and launch shapes
+ * ("force_cls" below 12 is the exception: timing experiments only, results are wrong).  The
  * K8SGPU_<NAME> environment variables seed them once, inside k8sgpu_create; nothing reads the
  * environment afterwards.  No reference counterpart. */
 int k8sgpu_set_tuning(k8sgpu_ctx *ctx, const char *key, int value);
