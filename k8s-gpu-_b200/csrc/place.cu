@@ -313,7 +313,7 @@ template <int PPT> __device__ __forceinline__ uint4 ldrec(const uint4 *p) { retu
 // TT: the taint clause -- 2: tested (and + setp); 0: left out (every pod of the warp tolerates every
 // taint any node carries); 1: left out, free GPUs read from the field that is -1 on a tainted node
 // (every pod of the warp tolerates none of the taints that occur).
-// Instructions per eval: 12 - 3 [no masks] - 2 [no preference] - 2 [TT < 2], and with CLS bit 0
+// Instructions per eval: 14 - 3 [no masks] - 2 [no preference] - 2 [TT < 2], and with CLS bit 0
 // clear and TT < 2 the first half of the node record is not even loaded.
 template <int CLS, int TT> __host__ __device__ constexpr bool ep4_needs_first_half() { return (CLS & 1) || TT == 2; }
 __device__ __forceinline__ uint32_t ep4_request(uint32_t req_gpu, bool tainted_field) {
@@ -622,7 +622,7 @@ constexpr uint32_t kIdxMask = 0x7Eu;   // those bits
 // wins; after each 64-node group the index bits of the running best are saturated, so a later
 // group needs a strictly larger key; and at the one point where the scan crosses n == rot(p)
 // the running best is lowered to just below its own key, which lets a later node with an EQUAL
-// key take over -- exactly "nodes at or after rot come first".  Only the 8-node chunk that
+// key take over -- exactly "nodes at or after rot come first".  Only a 16-node block that
 // contains rot takes the slow path.
 // UNR: nodes per trip of the class loops (divides 16).  16 amortises the loop bookkeeping best; 8
 // halves the 22 loop bodies, which matters when CTAs are short-lived and the SM's instruction
@@ -1809,7 +1809,7 @@ int round_begin(k8sgpu_ctx *ctx, const k8sgpu_policy *policy, cudaStream_t s) {
                    hash_bits, ordered && adaptive ? st.like_seen.as<uint32_t>() : nullptr);
         if (ordered) {
             if (adaptive) K8S_LAUNCH(ctx, like_hash_fix_kernel, ceil_div(st.m, 256), 256, 0, s, keys, st.m, st.counters.as<uint32_t>());
-            int rc = sort_pairs(ctx, s, keys, spod, st.m, 24, st.sort);  // by (class, like pods, rot bucket), pod order inside
+            int rc = sort_pairs(ctx, s, keys, spod, st.m, 24, st.sort);  // by (class, like pods, where rot(p) falls), pod order inside
             if (rc) return rc;
             K8S_LAUNCH(ctx, slot_init_kernel, ceil_div(st.m, 256), 256, 0, s, spod, st.m, slotof);
             st.order_valid = true;
@@ -1861,11 +1861,10 @@ int round_score(k8sgpu_ctx *ctx, uint32_t lo, uint32_t hi, int32_t *d_best, cuda
     // config 3, 40 tiles: 20 splits 3.55 ms, 40 3.62, 10 3.73; config 4, 391 tiles: 10 splits
     // 181.2 ms, 5 182.3, 3 185.1.
     const uint32_t sms = (uint32_t)ctx->sm_count;
-    // Pods per thread: two share every shared-memory read of a node record, which is what makes
-    // the 7-ALU variant (RES = 4) pay -- with one pod per thread it is issue bound.  Four per thread
-    // used to win on wide node tables (fewer 64-node groups contain some pod's rot(p)); since the
-    // loops are class-specialised two win everywhere (config 4: 377 vs 411 ms per placement), so
-    // four is a knob only.
+    // Pods per thread: two share every shared-memory read of a node record and, when they are
+    // alike, the clauses that depend on the node and on what they have in common (eval_pair4_u2,
+    // eval_pair4_ur2; only the two-pod kernel has those loops).  Four per thread is a knob: 80
+    // registers, three CTAs per SM (config 4: 355 vs 272 ms per placement when last measured).
     int ppt = st.score_res == 4 ? 2 : 1;
     if (ctx->tune.ppt >= 1) ppt = ctx->tune.ppt >= 4 ? 4 : ctx->tune.ppt >= 2 ? 2 : 1;
     if (ppt == 4 && st.score_res != 4) ppt = 2;
